@@ -181,6 +181,13 @@ typedef struct SrtSceneDesc {
     int32_t n_bvhs;
     const int32_t* bvh_items; /* group indices */
     int32_t n_bvh_items;
+    /* [n_bvh_items][6] = min xyz, max xyz: each leaf's OWN reference box, i.e. what
+     * leaf->bounding_box(0, 1, box) returns (every bvh_node in the reference is built with the
+     * time range (0, 1): Raytracing_n.cpp:274-709).  The reference tree's node boxes are
+     * surrounding_box unions of these (bvh.h:115-118, aabb.h:54-62); they are un-padded and
+     * decide which leaves a ray can reach at all, so they cross the boundary
+     * verbatim instead of being re-derived. */
+    const float* bvh_item_boxes;
     const SrtMedium* media;
     int32_t n_media;
 
@@ -317,6 +324,12 @@ int srt_render_image(SrtScene* scene, const SrtRenderParams* params, uint8_t* rg
 int srt_render_counted(SrtScene* scene, const SrtRenderParams* params, float* accum_rgb_device,
                        SrtCounters* out);
 int srt_counters_get(const SrtContext* ctx, SrtCounters* out);
+
+/* brdf::lookup_brdf_val (brdf.h:190-214) on MERL table `table` of the scene for n angle
+ * quadruples.  angles: [n][4] = theta_in, fi_in, theta_out, fi_out (doubles); rgb: [n][3].
+ * Host or device pointers.  (brdfmaterial::scatter evaluates this and discards the result,
+ * material.h:231-232; the entry point exists so the index arithmetic can be checked.) */
+int srt_merl_lookup(SrtScene* scene, int32_t table, const double* angles, int64_t n, double* rgb);
 
 /* Block the calling host thread until the context's stream is idle. */
 int srt_context_synchronize(SrtContext* ctx);

@@ -1,0 +1,32 @@
+// srt_bvh_build.h — host-side acceleration-structure builders (run once per srt_scene_create).
+//
+//   build_wide_bvh : binned-SAH binary tree over item boxes, collapsed to the 4-wide WideNode4
+//                    layout the traversal kernels read (srt_types.h).  This replaces the
+//                    reference's random-axis median split (bvh.h:96-119) as the tree that is
+//                    actually WALKED; it decides nothing about results.
+//   build_ref_tree : the reference's OWN tree shape over the leaves in their in-order sequence
+//                    (median split n/2, bvh.h:104-114) with its un-padded surrounding_box unions
+//                    (aabb.h:54-62), kept only as boxes: the kernels replay a candidate's ancestor
+//                    chain through it so that exactly the leaves the reference can reach are
+//                    reported.
+#ifndef SRT_BVH_BUILD_H
+#define SRT_BVH_BUILD_H
+
+#include <vector>
+
+#include "srt_types.h"
+
+struct WideBvh {
+    std::vector<WideNode4> nodes;  // nodes[0] is the root; child indices are relative to it
+    std::vector<int32_t> order;    // leaf slot -> item index
+    float sah_cost = 0.f;
+};
+
+// boxes: [n][6] = min xyz, max xyz (already padded by the caller).  n >= 1.
+void build_wide_bvh(const float* boxes, int n, WideBvh& out);
+
+// item_boxes: [n][6] reference leaf boxes in the reference tree's in-order leaf sequence.
+// out[0] is the root; child indices are relative to out[0].
+void build_ref_tree(const float* item_boxes, int n, std::vector<RefNode>& out);
+
+#endif

@@ -71,6 +71,7 @@ class SrtSceneDesc(C.Structure):
         ("groups", C.c_void_p), ("n_groups", C.c_int32),
         ("bvhs", C.c_void_p), ("n_bvhs", C.c_int32),
         ("bvh_items", C.c_void_p), ("n_bvh_items", C.c_int32),
+        ("bvh_item_boxes", C.c_void_p),
         ("media", C.c_void_p), ("n_media", C.c_int32),
         ("prims", C.c_void_p), ("n_prims", C.c_int32),
         ("spheres", C.c_void_p), ("n_spheres", C.c_int32),
@@ -126,6 +127,7 @@ class FlatScene:
     groups: np.ndarray = field(default_factory=lambda: np.zeros(0, GROUP_DT))
     bvhs: np.ndarray = field(default_factory=lambda: np.zeros(0, BVH_DT))
     bvh_items: np.ndarray = field(default_factory=lambda: np.zeros(0, np.int32))
+    bvh_item_boxes: np.ndarray = field(default_factory=lambda: np.zeros((0, 6), np.float32))
     media: np.ndarray = field(default_factory=lambda: np.zeros(0, MEDIUM_DT))
     prims: np.ndarray = field(default_factory=lambda: np.zeros(0, PRIM_DT))
     spheres: np.ndarray = field(default_factory=lambda: np.zeros((0, 4), np.float32))
@@ -160,6 +162,9 @@ class FlatScene:
         d.groups, d.n_groups = ptr(self.groups), len(self.groups)
         d.bvhs, d.n_bvhs = ptr(self.bvhs), len(self.bvhs)
         d.bvh_items, d.n_bvh_items = ptr(self.bvh_items), len(self.bvh_items)
+        if len(self.bvh_item_boxes) != len(self.bvh_items):
+            raise ValueError("bvh_item_boxes must hold one box per bvh item")
+        d.bvh_item_boxes = ptr(self.bvh_item_boxes)
         d.media, d.n_media = ptr(self.media), len(self.media)
         d.prims, d.n_prims = ptr(self.prims), len(self.prims)
         d.spheres, d.n_spheres = ptr(self.spheres), len(self.spheres)
@@ -205,6 +210,7 @@ class FlatScene:
         self.groups = _arr(self.groups, GROUP_DT)
         self.bvhs = _arr(self.bvhs, BVH_DT)
         self.bvh_items = _arr(self.bvh_items, np.int32)
+        self.bvh_item_boxes = _arr(self.bvh_item_boxes, np.float32, (6,))
         self.media = _arr(self.media, MEDIUM_DT)
         self.prims = _arr(self.prims, PRIM_DT)
         self.spheres = _arr(self.spheres, np.float32, (4,))
@@ -243,6 +249,7 @@ class FlatScene:
         fs.groups = rd(d.groups, d.n_groups, GROUP_DT)
         fs.bvhs = rd(d.bvhs, d.n_bvhs, BVH_DT)
         fs.bvh_items = rd(d.bvh_items, d.n_bvh_items, np.int32)
+        fs.bvh_item_boxes = rd(d.bvh_item_boxes, d.n_bvh_items, np.float32, (6,))
         fs.media = rd(d.media, d.n_media, MEDIUM_DT)
         fs.prims = rd(d.prims, d.n_prims, PRIM_DT)
         fs.spheres = rd(d.spheres, d.n_spheres, np.float32, (4,))
@@ -269,7 +276,7 @@ class FlatScene:
         return fs
 
     # ---- persistence (tests/golden) -----------------------------------------------------------
-    _ARRAYS = ("entries", "ops", "groups", "bvhs", "bvh_items", "media", "prims", "spheres", "msph", "rects",
+    _ARRAYS = ("entries", "ops", "groups", "bvhs", "bvh_items", "bvh_item_boxes", "media", "prims", "spheres", "msph", "rects",
                "tri_pos", "tri_nrm", "tri_uv", "lights", "materials", "textures", "camera")
 
     def save(self, path, with_images=True):
@@ -340,6 +347,7 @@ _SIGNATURES = {
     "srt_render_counted": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p, C.POINTER(SrtCounters)]),
     "srt_counters_get": (C.c_int, [C.c_void_p, C.POINTER(SrtCounters)]),
     "srt_sobol_points_u32": (C.c_int, [C.c_uint32, C.c_void_p]),
+    "srt_merl_lookup": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -38,6 +38,7 @@ struct SrtFlatScene {
     std::vector<SrtGroup> groups;
     std::vector<SrtBvh> bvhs;
     std::vector<int32_t> bvh_items;
+    std::vector<float> bvh_item_boxes;  // [n_bvh_items][6]
     std::vector<SrtMedium> media;
     std::vector<SrtPrim> prims;
     std::vector<float> spheres, msph, rects, tri_pos, tri_nrm, tri_uv;
@@ -82,6 +83,7 @@ struct SrtFlatScene {
         d.n_bvhs = (int32_t)bvhs.size();
         d.bvh_items = bvh_items.data();
         d.n_bvh_items = (int32_t)bvh_items.size();
+        d.bvh_item_boxes = bvh_item_boxes.data();
         d.media = media.data();
         d.n_media = (int32_t)media.size();
         d.prims = prims.data();
@@ -435,6 +437,25 @@ inline bool flatten_entry(SrtFlatScene& fs, const hitable* h, std::vector<SrtXfo
             int32_t g = add_group(fs, leaf, false);
             if (g < 0) return false;
             fs.bvh_items.push_back(g);
+            aabb lb;  // the leaf's own box as the reference tree saw it (bvh.h:115-117)
+            if (!leaf->bounding_box(0, 1, lb)) return fail(fs, "bvh_node leaf without a bounding box");
+            float row[6];
+            put3(row, lb._min);
+            put3(row + 3, lb._max);
+            fs.bvh_item_boxes.insert(fs.bvh_item_boxes.end(), row, row + 6);
+        }
+        {  // every reference bvh_node is built over the time range (0, 1); a root box that is not
+           // the union of the leaves' (0, 1) boxes means another range was used
+            float u[6] = {3.4e38f, 3.4e38f, 3.4e38f, -3.4e38f, -3.4e38f, -3.4e38f};
+            const float* bx = fs.bvh_item_boxes.data() + 6 * (size_t)b.first_item;
+            for (int k = 0; k < b.item_count; k++)
+                for (int a = 0; a < 3; a++) {
+                    if (bx[6 * k + a] < u[a]) u[a] = bx[6 * k + a];
+                    if (bx[6 * k + 3 + a] > u[3 + a]) u[3 + a] = bx[6 * k + 3 + a];
+                }
+            for (int a = 0; a < 3; a++)
+                if (u[a] != root->box._min.e[a] || u[3 + a] != root->box._max.e[a])
+                    return fail(fs, "bvh_node was not built over the time range (0, 1)");
         }
         fs.bvhs.push_back(b);
         SrtEntry e;

@@ -229,11 +229,20 @@ class isotropic(material):  # material.h:359-369
         self.albedo = a
 
 
+class FlattenError(ValueError):
+    """An object graph shape the flattener / backend does not cover (SRT_E_UNSUPPORTED)."""
+
+
 # ---- hitables -------------------------------------------------------------------------------------
 class hitable:
     def box_min(self) -> np.ndarray:
         """bounding_box(0, 0, box).Min() — the bvh_node constructor's sort key (bvh.h:21-55)."""
-        raise NotImplementedError(type(self).__name__)
+        raise FlattenError(f"unsupported bvh_node leaf: {type(self).__name__}")
+
+    def ref_box(self) -> np.ndarray:
+        """bounding_box(0, 1, box) as [min xyz, max xyz] float32 — the leaf box the reference
+        bvh_node unions into its node boxes (bvh.h:115-118)."""
+        raise FlattenError(f"unsupported bvh_node leaf: {type(self).__name__}")
 
 
 class sphere(hitable):  # sphere.h:17-30
@@ -242,6 +251,9 @@ class sphere(hitable):  # sphere.h:17-30
 
     def box_min(self):  # sphere.h:32-35
         return self.center - self.radius
+
+    def ref_box(self):
+        return np.concatenate([self.center - self.radius, self.center + self.radius]).astype(f32)
 
 
 class env_sphere(sphere):  # env_sphere.h:7-25
@@ -260,6 +272,12 @@ class moving_sphere(hitable):  # moving_sphere.h:4-17
     def box_min(self):  # moving_sphere.h:53-58 at t0 = t1 = 0
         return self.center(f32(0)) - self.radius
 
+    def ref_box(self):  # moving_sphere.h:53-58 at (t0, t1) = (0, 1)
+        c0, c1 = self.center(f32(0)), self.center(f32(1))
+        lo = np.minimum(c0 - self.radius, c1 - self.radius)
+        hi = np.maximum(c0 + self.radius, c1 + self.radius)
+        return np.concatenate([lo, hi]).astype(f32)
+
 
 def _pad(k, sign):  # aarect.h:12 `k - 0.0001` is evaluated in double and narrowed by vec3's constructor
     return f32(float(k) + sign * 0.0001)
@@ -272,6 +290,9 @@ class xy_rect(hitable):  # aarect.h:5-35
     def box_min(self):
         return np.array([self.x0, self.y0, _pad(self.k, -1)], f32)
 
+    def ref_box(self):
+        return np.array([self.x0, self.y0, _pad(self.k, -1), self.x1, self.y1, _pad(self.k, +1)], f32)
+
     def row(self):
         return [self.x0, self.x1, self.y0, self.y1, self.k]
 
@@ -283,6 +304,9 @@ class xz_rect(hitable):  # aarect.h:37-64
     def box_min(self):
         return np.array([self.x0, _pad(self.k, -1), self.z0], f32)
 
+    def ref_box(self):
+        return np.array([self.x0, _pad(self.k, -1), self.z0, self.x1, _pad(self.k, +1), self.z1], f32)
+
     def row(self):
         return [self.x0, self.x1, self.z0, self.z1, self.k]
 
@@ -293,6 +317,9 @@ class yz_rect(hitable):  # aarect.h:66-94
 
     def box_min(self):
         return np.array([_pad(self.k, -1), self.y0, self.z0], f32)
+
+    def ref_box(self):
+        return np.array([_pad(self.k, -1), self.y0, self.z0, _pad(self.k, +1), self.y1, self.z1], f32)
 
     def row(self):
         return [self.y0, self.y1, self.z0, self.z1, self.k]
@@ -315,6 +342,10 @@ class triangle(hitable):  # triangle.h:9-106
     def box_min(self):  # triangle.h:53-68
         return np.minimum(np.minimum(self.p0, self.p1), self.p2)
 
+    def ref_box(self):
+        return np.concatenate([np.minimum(np.minimum(self.p0, self.p1), self.p2),
+                               np.maximum(np.maximum(self.p0, self.p1), self.p2)]).astype(f32)
+
 
 def _uv3(uv):
     uv = list(np.asarray(uv, f32).reshape(-1))
@@ -327,6 +358,9 @@ class flip_normals(hitable):  # aarect.h:149-171
 
     def box_min(self):
         return self.ptr.box_min()
+
+    def ref_box(self):
+        return self.ptr.ref_box()
 
 
 class box(hitable):  # box.h:5-33
@@ -344,6 +378,9 @@ class box(hitable):  # box.h:5-33
 
     def box_min(self):  # box.h:10-13
         return self.pmin
+
+    def ref_box(self):
+        return np.concatenate([self.pmin, self.pmax]).astype(f32)
 
 
 class translate(hitable):  # hitable.h:35-61
@@ -378,6 +415,9 @@ class hitable_list(hitable):  # hitable_list.h:7-19
 
     def box_min(self):  # hitable_list.h:35-52 unions list[0] with itself list_size times
         return self.list[0].box_min()
+
+    def ref_box(self):
+        return self.list[0].ref_box()
 
 
 def _ref_sorted_order(keys: np.ndarray) -> np.ndarray:
@@ -542,9 +582,6 @@ class camera:  # camera.h:33-48
 
 
 # ---- flattening (same rules, same emission order as host/srt_flatten.hpp) ---------------------------
-class FlattenError(ValueError):
-    pass
-
 
 class _Flattener:
     def __init__(self):
@@ -553,7 +590,7 @@ class _Flattener:
         self.spheres, self.msph, self.rects = [], [], []
         # prims / groups / bvh items / triangles are kept as chunks (numpy blocks) with running
         # counts, so that array-form meshes (triangle_soup) are appended in one piece
-        self.prim_chunks, self.group_chunks, self.item_chunks = [], [], []
+        self.prim_chunks, self.group_chunks, self.item_chunks, self.item_box_chunks = [], [], [], []
         self.n_prims = self.n_groups = self.n_items = self.n_tris = 0
         self.tri_pos, self.tri_nrm, self.tri_uv = [], [], []
         self.images, self.merl = [], []
@@ -685,6 +722,10 @@ class _Flattener:
         gr = np.zeros(n, ffi.GROUP_DT)
         gr["first_prim"], gr["prim_count"] = np.arange(self.n_prims, self.n_prims + n), 1
         self.item_chunks.append(np.arange(self.n_groups, self.n_groups + n, dtype=np.int32))
+        ps = h.pos[order]
+        self.item_box_chunks.append(np.concatenate(
+            [np.minimum(np.minimum(ps[:, 0:3], ps[:, 3:6]), ps[:, 6:9]),
+             np.maximum(np.maximum(ps[:, 0:3], ps[:, 3:6]), ps[:, 6:9])], 1).astype(f32))
         self.prim_chunks.append(pr)
         self.group_chunks.append(gr)
         self.tri_pos.append(h.pos[order])
@@ -735,6 +776,7 @@ class _Flattener:
                     if not self.is_groupable(leaf):
                         raise FlattenError(f"unsupported bvh_node leaf: {type(leaf).__name__}")
                     self.item_chunks.append(np.array([self.add_group(leaf, False)], np.int32))
+                    self.item_box_chunks.append(leaf.ref_box().reshape(1, 6))
                     self.n_items += 1
                 count = len(leaves)
             self.bvhs.append((first, count))
@@ -798,6 +840,8 @@ def flatten(world: hitable, hlist: Optional[hitable], cam: camera) -> ffi.FlatSc
     fs.prims = _cat(fl.prim_chunks, ffi.PRIM_DT)
     fs.groups = _cat(fl.group_chunks, ffi.GROUP_DT)
     fs.bvh_items = _cat(fl.item_chunks, np.int32)
+    fs.bvh_item_boxes = (np.concatenate(fl.item_box_chunks).astype(f32) if fl.item_box_chunks
+                         else np.zeros((0, 6), f32))
     fs.bvhs = rows(fl.bvhs, ffi.BVH_DT)
     fs.media = rows(fl.media, ffi.MEDIUM_DT)
     fs.spheres = np.array(fl.spheres, f32).reshape(-1, 4)

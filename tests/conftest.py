@@ -1,0 +1,39 @@
+import os
+import sys
+
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+GOLDEN = os.path.join(ROOT, "tests", "golden")
+
+
+def pytest_configure(config):
+    config.addinivalue_line("markers", "gpu: needs a CUDA device (run on the B200 box)")
+
+
+@pytest.fixture(scope="session")
+def backend_lib():
+    """libsrt_b200.so, built in-tree if missing (nvcc cross-compiles without a GPU)."""
+    import __graft_entry__ as g
+    g.build_backend()
+    from simple_raytracing_render_b200 import ffi
+    return ffi.load_backend()
+
+
+@pytest.fixture(scope="session")
+def oracle():
+    from oracle import ref
+    if not ref.available():
+        pytest.skip("oracle/_ref/libsrt_ref.so not built (needs /root/reference)")
+    return ref
+
+
+@pytest.fixture(scope="session")
+def gpu_ctx(backend_lib):
+    from simple_raytracing_render_b200 import render
+    ctx = render.Context(0)
+    yield ctx
+    ctx.close()

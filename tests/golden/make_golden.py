@@ -1,0 +1,64 @@
+"""Generates tests/golden/*.npz from the REAL reference (oracle/_ref/libsrt_ref.so, i.e. the
+unmodified /root/reference translation unit).  Run in the build container:
+
+    python tests/golden/make_golden.py
+
+The vectors pin (a) the reference's generators and closed-form helpers, (b) its closest-hit results
+on its own camera rays for the C1 / C2 scenes, (c) its light pdf, (d) converged float images.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from oracle import ref  # noqa: E402
+from simple_raytracing_render_b200 import scenes  # noqa: E402
+
+
+def kats():
+    L = ref.lib()
+    f, u = ref.kat_pcg32(16)
+    xs = np.linspace(-3, 3, 25).astype(np.float32)
+    ys = np.linspace(-0.999, 0.999, 25).astype(np.float32)
+    cam = scenes.cornell_box_classic(1.0)[2]
+    np.savez(os.path.join(HERE, "kats.npz"),
+             drand48_seed1=ref.kat_drand48(1, 16), pcg_float=f, pcg_u32=u,
+             sobol_8=ref.kat_sobol(8), sobol_1024=ref.kat_sobol(1024),
+             erf_x=xs, erf=np.array([L.ref_kat_erf(float(x)) for x in xs], np.float32),
+             erfinv_x=ys, erfinv=np.array([L.ref_kat_erfinv(float(y)) for y in ys], np.float32),
+             schlick=np.array([L.ref_kat_schlick(c, 1.5) for c in (0.0, 0.25, 0.5, 1.0)], np.float32),
+             r2a=np.array([L.ref_kat_roughness_to_alpha(r) for r in (0.0005, 0.01, 0.05, 0.3, 1.0)], np.float32))
+
+
+def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny):
+    world, hlist, cam = scenes.by_name(name)
+    rs = ref.RefBuilder().realize(world, hlist, cam)
+    mod_ny = nx == ny
+    rays = rs.primary_rays(nx, ny, ns_rays, seed=1, mod_ny=mod_ny)
+    ids, t, rec = rs.trace(rays)
+    rng = np.random.default_rng(7)
+    # secondary-like rays: from hit points towards random directions (un-normalised, as light samples are)
+    hit = ids >= 0
+    o = rec[hit][:, 2:5][:4096]
+    d = rng.normal(size=o.shape).astype(np.float32) * rng.uniform(0.2, 300, size=(len(o), 1)).astype(np.float32)
+    rays2 = np.concatenate([o, d, np.zeros((len(o), 1), np.float32)], 1).astype(np.float32)
+    ids2, t2, rec2 = rs.trace(rays2)
+    od = np.concatenate([o, d], 1).astype(np.float32)
+    lp = rs.light_pdf(od)
+    img, nrays = rs.render_float(img_nx, img_ny, ns_img, mod_ny=img_nx == img_ny)
+    np.savez_compressed(os.path.join(HERE, f"{name}.npz"), nx=nx, ny=ny, ns_rays=ns_rays,
+                        rays=rays, ids=ids, t=t, rec=rec, rays2=rays2, ids2=ids2, t2=t2, rec2=rec2,
+                        light_od=od, light_pdf=lp, img=img / ns_img, img_nx=img_nx, img_ny=img_ny, img_ns=ns_img,
+                        img_rays=nrays)
+    print(name, "hits", int(hit.sum()), "of", len(ids), "img mean", float(img.mean() / ns_img), "rays/path",
+          nrays / (img_nx * img_ny * ns_img))
+
+
+if __name__ == "__main__":
+    kats()
+    scene_vectors("cornell", 64, 64, 2, 1024, 48, 48)
+    scene_vectors("spheres", 96, 64, 2, 1024, 48, 32)
