@@ -253,7 +253,8 @@ typedef struct SrtCounters {
     uint64_t prim_tests;   /* primitive intersection tests */
     uint64_t reject_iters; /* iterations of the while(pdf_val==0) loop, Raytracing_n.cpp:79-83 */
     uint64_t kernel_launches; /* kernels launched by this library on this context so far */
-    uint64_t _reserved;
+    uint64_t culled_rays;  /* continuation rays the reference traces with an all-zero throughput
+                              (they cannot change the sample); the backend does not trace them */
 } SrtCounters;
 
 typedef struct SrtSceneInfo {

@@ -561,8 +561,12 @@ double ref_render_timed(int scene, int nx_, int ny_, int ns_, int max_depth, int
     s_rng = rng();
     finishedPixel = 0;
     isfinished = true;  // suppresses the text dump at :869-878
-    colors = new int*[(size_t)nx_ * ny_];
-    for (size_t i = 0; i < (size_t)nx_ * ny_; i++) colors[i] = nullptr;
+    // renderthread tests `finishedPixel < nx*ny` outside the lock (:817), so up to threads-1 workers
+    // take a curpixel >= nx*ny at the end and store colors[curpixel] past the array (:863): give the
+    // array that much slack instead of touching the reference
+    size_t n_slots = (size_t)nx_ * ny_ + (size_t)threads + 8;
+    colors = new int*[n_slots];
+    for (size_t i = 0; i < n_slots; i++) colors[i] = nullptr;
     auto t0 = std::chrono::steady_clock::now();
     {
         std::vector<std::thread> pool;
@@ -580,6 +584,7 @@ double ref_render_timed(int scene, int nx_, int ny_, int ns_, int max_depth, int
             delete[] colors[i];
         }
     }
+    for (size_t i = (size_t)nx_ * ny_; i < n_slots; i++) delete[] colors[i];
     delete[] colors;
     colors = nullptr;
     nx = keep_nx;

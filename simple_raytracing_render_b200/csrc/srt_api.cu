@@ -755,6 +755,7 @@ int srt_render_counted(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_d
     c->last.prim_tests = h[4];
     c->last.reject_iters = h[5];
     c->last.kernel_launches = c->launches;
+    c->last.culled_rays = h[6];
     if (out) *out = c->last;
     return 0;
 }

@@ -12,7 +12,7 @@
 namespace srt {
 
 struct Counters {  // per-thread tallies of an instrumented launch (SrtCounters)
-    unsigned long long rays, probe_rays, node_visits, prim_tests, reject_iters;
+    unsigned long long rays, probe_rays, node_visits, prim_tests, reject_iters, culled_rays;
 };
 
 template <bool COUNT>

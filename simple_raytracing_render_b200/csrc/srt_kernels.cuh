@@ -76,7 +76,7 @@ __global__ void __launch_bounds__(256) k_render(DScene S, RenderArgs A, const ui
     const int L = A.lanes_per_pixel;
     const int ppw = 32 / L;
     const int n_pixels = A.nx * A.ny;
-    Counters cnt = {0, 0, 0, 0, 0};
+    Counters cnt = {0, 0, 0, 0, 0, 0};
     Tally<COUNT> tl{&cnt};
     unsigned long long paths = 0;
 
@@ -121,6 +121,7 @@ __global__ void __launch_bounds__(256) k_render(DScene S, RenderArgs A, const ui
         atomicAdd(&counters[3], cnt.node_visits);
         atomicAdd(&counters[4], cnt.prim_tests);
         atomicAdd(&counters[5], cnt.reject_iters);
+        atomicAdd(&counters[6], cnt.culled_rays);
     }
 }
 

@@ -396,7 +396,10 @@ SRT_DEV V3 trace_path(const DScene& S, Ray r, int max_depth, Philox& rng, Tally<
         r = scattered;
         depth++;
         // a zero throughput cannot contribute any more: finite * 0 == 0 in the recursive form too
-        if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) break;
+        if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) {
+            if (COUNT) tl.c->culled_rays++;
+            break;
+        }
     }
     return L;
 }

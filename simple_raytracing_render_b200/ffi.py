@@ -97,7 +97,7 @@ class SrtRenderParams(C.Structure):
 class SrtCounters(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("probe_rays", C.c_uint64),
                 ("node_visits", C.c_uint64), ("prim_tests", C.c_uint64), ("reject_iters", C.c_uint64),
-                ("kernel_launches", C.c_uint64), ("_reserved", C.c_uint64)]
+                ("kernel_launches", C.c_uint64), ("culled_rays", C.c_uint64)]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_ if not n.startswith("_")}

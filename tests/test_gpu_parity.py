@@ -1,0 +1,160 @@
+"""Parity of the CUDA path (through the C ABI, libsrt_b200.so) with the reference.
+
+Three gates (BASELINE.json:north_star): primary-hit primitive ids bit-exact against the reference's
+world->hit on the same camera rays; hit distance t within 1e-5 relative; converged image within a
+stated relMSE of the reference's CPU render.  The committed golden vectors (tests/golden/*.npz,
+made from the UNMODIFIED reference by tests/golden/make_golden.py) are the fixed anchors; where
+oracle/_ref/libsrt_ref.so travelled to the GPU box the same checks are repeated live at larger
+sizes.  Nothing here reads /root/reference.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLDEN
+from simple_raytracing_render_b200 import ffi, render, scenes, scene as S
+
+pytestmark = pytest.mark.gpu
+
+T_REL_TOL = 1e-5       # north_star: "hit distance t within 1e-5 relative"
+RELMSE_TOL = 1e-3      # north_star: "converged relMSE <= 1e-3 versus the reference"
+
+
+def rel_mse(x, r):
+    """mean over pixels/channels of (x - r)^2 / (r^2 + 1e-2) on linear means."""
+    x, r = np.asarray(x, np.float64), np.asarray(r, np.float64)
+    return float(np.mean((x - r) ** 2 / (r ** 2 + 1e-2)))
+
+
+@pytest.fixture(scope="module", params=["cornell", "spheres"])
+def golden_scene(request, gpu_ctx):
+    name = request.param
+    g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
+    sc = render.Scene.from_objects(gpu_ctx, *scenes.by_name(name))
+    yield name, g, sc
+    sc.close()
+
+
+def _check_hits(gid, gt, rid, rt):
+    assert np.array_equal(gid, rid), f"{int((gid != rid).sum())} of {len(rid)} primitive ids differ"
+    hit = rid >= 0
+    rel = np.abs(gt[hit] - rt[hit]) / np.maximum(np.abs(rt[hit]), 1e-30)
+    assert rel.size == 0 or rel.max() <= T_REL_TOL, f"max relative t error {rel.max():.3e}"
+    return float(rel.max()) if rel.size else 0.0
+
+
+def test_primary_hits_match_golden(golden_scene):
+    name, g, sc = golden_scene
+    gid, gt, grec = sc.trace_closest(g["rays"])
+    _check_hits(gid, gt, g["ids"], g["t"])
+    # the whole hit_record (u, v, p, normal) of hitable.h:17-25
+    hit = g["ids"] >= 0
+    assert np.allclose(grec[hit], g["rec"][hit], rtol=1e-5, atol=1e-4)
+
+
+def test_secondary_hits_match_golden(golden_scene):
+    """Un-normalised directions from surface points (what hitable_pdf samples produce)."""
+    name, g, sc = golden_scene
+    gid, gt, _ = sc.trace_closest(g["rays2"])
+    _check_hits(gid, gt, g["ids2"], g["t2"])
+
+
+def test_light_pdf_matches_golden(golden_scene):
+    name, g, sc = golden_scene
+    got = sc.light_pdf(g["light_od"])
+    want = g["light_pdf"]
+    assert np.array_equal(got == 0, want == 0)
+    assert np.allclose(got, want, rtol=1e-5, atol=0)
+
+
+def test_device_pointers_are_accepted(golden_scene):
+    import torch
+    name, g, sc = golden_scene
+    rays = torch.from_numpy(g["rays"][:4096].copy()).cuda()
+    ids = torch.empty(len(rays), dtype=torch.int32, device="cuda")
+    t = torch.empty(len(rays), dtype=torch.float32, device="cuda")
+    ffi.check(sc.lib, sc.lib.srt_trace_closest(sc.h, rays.data_ptr(), len(rays), ids.data_ptr(), t.data_ptr(), None))
+    sc.ctx.synchronize()
+    assert np.array_equal(ids.cpu().numpy(), g["ids"][:4096])
+
+
+def test_converged_image_relmse_vs_golden(golden_scene):
+    """GPU image at 4x the golden's spp against the reference's single-thread float render."""
+    name, g, sc = golden_scene
+    nx, ny, ns_ref = int(g["img_nx"]), int(g["img_ny"]), int(g["img_ns"])
+    ns = 4 * ns_ref
+    _, accum = sc.render_image(render.render_params(nx, ny, ns), want_accum=True)
+    x = accum / float(ns)
+    r = g["img"]
+    err = rel_mse(x, r)
+    # the golden itself carries Monte-Carlo noise of ns_ref samples; measured split in DESIGN.md §7
+    print(f"{name}: relMSE {err:.3e} (gpu {ns} spp vs reference {ns_ref} spp), means {x.mean():.4f} / {r.mean():.4f}")
+    assert abs(x.mean() - r.mean()) <= 0.02 * r.mean()
+    assert err <= RELMSE_TOL
+
+
+def test_render_is_deterministic_and_shards_add_up(golden_scene):
+    """Sample-range shards: [0, ns) == sum of disjoint ranges up to float summation
+    order; the same range twice is bit-identical."""
+    import torch
+    name, g, sc = golden_scene
+    nx, ny, ns = 96, 64, 32
+    flags = 0
+
+    def run(a, b):
+        buf = torch.zeros(nx * ny * 3, dtype=torch.float32, device="cuda")
+        sc.render(render.render_params(nx, ny, ns, a, b, flags=flags), buf)
+        sc.ctx.synchronize()
+        return buf.cpu().numpy()
+
+    whole, again = run(0, ns), run(0, ns)
+    assert np.array_equal(whole, again)
+    parts = run(0, 8) + run(8, 16) + run(16, 32)
+    assert np.allclose(parts, whole, rtol=1e-4, atol=1e-4)
+    assert np.isfinite(whole).all() and whole.mean() > 0
+
+
+def test_resolve_matches_reference_quantisation(gpu_ctx):
+    """mean -> sqrt -> int(255.99 c) -> clamp (Raytracing_n.cpp:848-862)."""
+    import torch
+    rng = np.random.default_rng(1)
+    n, ns = 4099, 16
+    acc = (rng.uniform(0, 2.5, size=(n, 3)) * ns).astype(np.float32)
+    acc[0] = 0
+    acc[1] = 1e9
+    d = torch.from_numpy(acc).cuda()
+    out = np.zeros((n, 3), np.uint8)
+    gpu_ctx.resolve(d, n, ns, out)
+    k = np.float32(1.0 / ns)
+    c = np.sqrt(acc * k).astype(np.float32)
+    want = np.clip((255.99 * c.astype(np.float64)).astype(np.int64), 0, 255).astype(np.uint8)
+    assert np.array_equal(out, want)
+
+
+def test_counters_are_consistent(golden_scene):
+    import torch
+    name, g, sc = golden_scene
+    nx, ny, ns = 64, 64, 8
+    buf = torch.zeros(nx * ny * 3, dtype=torch.float32, device="cuda")
+    c = sc.render_counted(render.render_params(nx, ny, ns), buf)
+    assert c["paths"] == nx * ny * ns
+    assert c["rays"] >= c["paths"] and c["prim_tests"] > 0
+    # the reference's own rays/path for this scene (golden img_rays) within a few percent
+    ref_rpp = float(g["img_rays"]) / (int(g["img_nx"]) * int(g["img_ny"]) * int(g["img_ns"]))
+    # (the backend does not trace continuation rays whose throughput is exactly zero; it counts them)
+    assert abs((c["rays"] + c["culled_rays"]) / c["paths"] - ref_rpp) < 0.05 * ref_rpp
+
+
+# ---- live oracle (oracle/_ref/libsrt_ref.so travelled with the snapshot) ---------------------------
+@pytest.mark.parametrize("name,nx,ny", [("cornell", 512, 512), ("spheres", 600, 400)])
+def test_primary_hits_match_live_reference_full_size(oracle, gpu_ctx, name, nx, ny):
+    world, hlist, cam = scenes.by_name(name)
+    rs = oracle.RefBuilder().realize(world, hlist, cam)
+    sc = render.Scene.from_desc_address(gpu_ctx, rs.desc_address())  # the C++ flattener's output
+    rays = rs.primary_rays(nx, ny, 1, seed=7, mod_ny=nx == ny)
+    rid, rt, _ = rs.trace(rays, want_rec=False)
+    gid, gt, _ = sc.trace_closest(rays, want_rec=False)
+    worst = _check_hits(gid, gt, rid, rt)
+    print(f"{name} {nx}x{ny}: {len(rid)} rays, ids exact, max rel t err {worst:.2e}")
+    sc.close()
