@@ -264,6 +264,11 @@ typedef struct SrtSceneInfo {
     int64_t device_bytes;    /* total device memory held by the scene */
     float sah_cost;          /* SAH cost of the largest bvh */
     float build_ms;          /* host build time */
+    uint32_t features;       /* which reference classes the scene instantiates (srt_types.h F_*) */
+    int32_t render_variant;  /* render-kernel variant of the last srt_render (-1: none yet) */
+    int32_t render_registers;     /* registers per thread of that variant */
+    int32_t render_blocks_per_sm; /* its resident blocks per SM */
+    int64_t hot_table_bytes; /* entries + instance ops + primitive records + lights */
 } SrtSceneInfo;
 
 typedef struct SrtContext SrtContext;
@@ -334,6 +339,11 @@ int srt_merl_lookup(SrtScene* scene, int32_t table, const double* angles, int64_
 
 /* Block the calling host thread until the context's stream is idle. */
 int srt_context_synchronize(SrtContext* ctx);
+
+/* Self-test of the backend's exact division: counts the operand pairs (a[i], b[i]) for which the
+ * hoisted-reciprocal quotient the kernels use differs from IEEE round-to-nearest a[i] / b[i]
+ * (must be 0).  a, b: device or host pointers to n floats. */
+int srt_selftest_division(SrtContext* ctx, const float* a, const float* b, int64_t n, uint64_t* mismatches);
 
 /* Host-side helpers (no device work): the reference's Sobol table (Raytracing_n.cpp:721-812,
  * D = 2; direction numbers of contents/sobol/new-joe-kuo-6.21201 line 2) as u32 numerators of

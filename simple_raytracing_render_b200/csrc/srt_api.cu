@@ -5,14 +5,16 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <string>
 #include <vector>
 
 #include "srt_bvh_build.h"
 #include "srt_ffi.h"
-#include "srt_kernels.cuh"
+#include "srt_aux_kernels.cuh"
 #include "srt_types.h"
+#include "srt_variants.h"
 
 namespace {
 
@@ -63,6 +65,12 @@ struct SrtScene {
     size_t accum_cap = 0;
     float* h_accum = nullptr;  // pinned staging
     size_t h_accum_cap = 0;
+    float* d_partial = nullptr;  // [n_chunks][n_pixels][3] per-item radiance sums of the last render
+    size_t partial_cap = 0;
+    int variant = -1;        // render-kernel variant this scene runs on
+    int variant_blocks = 0;  // its resident blocks per SM
+    int variant_regs = 0;
+    size_t variant_smem = 0;
 };
 
 namespace {
@@ -126,8 +134,8 @@ struct DevOut {
 
 struct Layout {
     size_t total = 0;
-    size_t add(size_t bytes) {
-        size_t off = (total + 255) & ~(size_t)255;
+    size_t add(size_t bytes, size_t align = 256) {
+        size_t off = (total + align - 1) & ~(align - 1);
         total = off + bytes;
         return off;
     }
@@ -136,7 +144,7 @@ struct Layout {
 void pad_box(float* b) {
     for (int a = 0; a < 3; a++) {
         float m = std::max(std::fabs(b[a]), std::fabs(b[3 + a]));
-        float pad = 1e-5f * std::max(m, b[3 + a] - b[a]) + 1e-7f;
+        float pad = 1e-4f * std::max(m, b[3 + a] - b[a]) + 1e-7f;
         b[a] -= pad;
         b[3 + a] += pad;
     }
@@ -301,6 +309,7 @@ int srt_context_create(int device, void* cuda_stream, SrtContext** out) {
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
     CUDA_TRY(cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMemset(c->d_counters, 0, 8 * sizeof(unsigned long long)));
     *out = c;
     return 0;
 }
@@ -331,6 +340,7 @@ int srt_scene_destroy(SrtScene* s) {
     for (double* p : s->d_merl) cudaFree(p);
     cudaFree(s->d_sobol);
     cudaFree(s->d_accum);
+    cudaFree(s->d_partial);
     if (s->h_accum) cudaFreeHost(s->h_accum);
     delete s;
     return 0;
@@ -421,13 +431,155 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
         }
     }
 
-    // ---- repack small records to 16-byte units ------------------------------------------------
-    std::vector<float4> rects(2 * (size_t)d.n_rects);
-    for (int i = 0; i < d.n_rects; i++) {
-        const float* q = d.rects + 5 * (size_t)i;
-        rects[2 * i] = float4{q[0], q[1], q[2], q[3]};
-        rects[2 * i + 1] = float4{q[4], 0.f, 0.f, 0.f};
+    // ---- flat primitive records (index == primitive id) ------------------------------------------
+    uint32_t feat = 0;
+    auto make_dprim = [&](int type, int index, int material, uint32_t flags) {
+        DPrim p;
+        std::memset(&p, 0, sizeof p);
+        p.type = type;
+        p.material = material;
+        p.flags_aux = flags & SRT_PRIM_FLIP;
+        switch (type) {
+            case SRT_PRIM_SPHERE:
+            case SRT_PRIM_ENV_SPHERE: {
+                const float* q = d.spheres + 4 * (size_t)index;
+                p.g = float4{q[0], q[1], q[2], q[3]};
+                break;
+            }
+            case SRT_PRIM_XY_RECT:
+            case SRT_PRIM_XZ_RECT:
+            case SRT_PRIM_YZ_RECT: {
+                const float* q = d.rects + 5 * (size_t)index;
+                p.g = float4{q[0], q[1], q[2], q[3]};
+                p.k = q[4];
+                break;
+            }
+            default:  // moving sphere / triangle: row of the per-type array
+                p.flags_aux |= (uint32_t)index << 1;
+                break;
+        }
+        return p;
+    };
+    std::vector<char> in_tri_bvh(d.n_prims, 0);
+    for (int bi = 0; bi < d.n_bvhs; bi++) {
+        if (bvhs[bi].kind != BVH_KIND_TRIANGLE) continue;
+        for (int k = 0; k < d.bvhs[bi].item_count; k++)
+            in_tri_bvh[d.groups[d.bvh_items[d.bvhs[bi].first_item + k]].first_prim] = 1;
+        feat |= F_BVH_TRI;
     }
+    for (int bi = 0; bi < d.n_bvhs; bi++) {
+        if (bvhs[bi].kind == BVH_KIND_SPHERE) feat |= F_BVH_SPHERE;
+        if (bvhs[bi].kind == BVH_KIND_GENERIC) feat |= F_BVH_GENERIC;
+    }
+    std::vector<DPrim> dprims(d.n_prims);
+    for (int i = 0; i < d.n_prims; i++) {
+        const SrtPrim& p = d.prims[i];
+        dprims[i] = make_dprim(p.type, p.index, p.material, p.flags);
+        if (p.type == SRT_PRIM_TRIANGLE && !in_tri_bvh[i]) feat |= F_TRI;
+        if (p.type == SRT_PRIM_MOVING_SPHERE) feat |= F_MSPHERE;
+        if (p.type == SRT_PRIM_ENV_SPHERE) feat |= F_ENV;
+    }
+    std::vector<DPrim> dlights(d.n_lights);
+    for (int i = 0; i < d.n_lights; i++) {
+        const SrtLight& L = d.lights[i];
+        if (L.type == SRT_PRIM_NONE) {
+            std::memset(&dlights[i], 0, sizeof(DPrim));
+            dlights[i].type = SRT_PRIM_NONE;
+            dlights[i].material = -1;
+            feat |= F_LIGHT_NONE;
+            continue;
+        }
+        dlights[i] = make_dprim(L.type, L.index, -1, 0);
+        if (L.type == SRT_PRIM_SPHERE) feat |= F_LIGHT_SPHERE;
+        if (L.type == SRT_PRIM_TRIANGLE) feat |= F_LIGHT_TRI;
+        if (L.type == SRT_PRIM_ENV_SPHERE) feat |= F_LIGHT_ENV;
+    }
+
+    // ---- world entries with conservative local-frame bounds -------------------------------------
+    std::vector<DEntry> dentries(d.n_entries);
+    for (int i = 0; i < d.n_entries; i++) {
+        const SrtEntry& e = d.entries[i];
+        DEntry& o = dentries[i];
+        std::memset(&o, 0, sizeof o);
+        o.first_op = e.first_op;
+        o.op_count = e.op_count;
+        o.geom_kind = e.geom_kind;
+        o.geom_index = e.geom_index;
+        o.medium = e.medium;
+        if (e.op_count > 0) feat |= F_XFORM;
+        if (e.medium >= 0) feat |= F_MEDIA;
+        float b[6] = {3.4e38f, 3.4e38f, 3.4e38f, -3.4e38f, -3.4e38f, -3.4e38f};
+        bool boundable = true, honours_t = true;
+        int n_inside = 0;
+        auto add_group = [&](const SrtGroup& g) {
+            for (int k = 0; k < g.prim_count; k++) {
+                const SrtPrim& p = d.prims[g.first_prim + k];
+                float pb[6];
+                if (p.type == SRT_PRIM_ENV_SPHERE || !prim_bounds(d, p, pb)) {
+                    boundable = false;
+                    continue;
+                }
+                if (p.type == SRT_PRIM_TRIANGLE) honours_t = false;  // triangle::hit ignores (t0, t1)
+                pad_box(pb);
+                for (int a = 0; a < 3; a++) {
+                    b[a] = std::min(b[a], pb[a]);
+                    b[3 + a] = std::max(b[3 + a], pb[3 + a]);
+                }
+                n_inside++;
+            }
+        };
+        if (e.geom_kind == SRT_GEOM_GROUP) {
+            const SrtGroup& g = d.groups[e.geom_index];
+            o.first_prim = g.first_prim;
+            o.prim_count = g.prim_count;
+            add_group(g);
+        } else {
+            const SrtBvh& sb = d.bvhs[e.geom_index];
+            for (int k = 0; k < sb.item_count; k++) add_group(d.groups[d.bvh_items[sb.first_item + k]]);
+        }
+        bool finite = n_inside > 0;
+        for (int a = 0; a < 6; a++) finite = finite && std::isfinite(b[a]) && std::fabs(b[a]) < 1e30f;
+        // a bounds test costs about as much as two primitive tests: only worth it above a few
+        if (boundable && finite && (e.geom_kind == SRT_GEOM_BVH || n_inside >= 4)) {
+            o.flags |= DENTRY_CULL;
+            if (honours_t) o.flags |= DENTRY_TCULL;
+            for (int a = 0; a < 3; a++) {
+                o.lo[a] = b[a];
+                o.hi[a] = b[3 + a];
+            }
+        }
+    }
+
+    // ---- materials with their texture heads folded in ---------------------------------------------
+    std::vector<DMaterial> dmats(d.n_materials);
+    for (int i = 0; i < d.n_materials; i++) {
+        const SrtMaterial& m = d.materials[i];
+        DMaterial& o = dmats[i];
+        std::memset(&o, 0, sizeof o);
+        o.type = m.type;
+        o.texture = m.texture;
+        o.tex_type = m.texture >= 0 ? d.textures[m.texture].type : -1;
+        for (int k = 0; k < 4; k++) o.p[k] = m.p[k];
+        if (m.type == SRT_MAT_BRDF || m.type == SRT_MAT_METAL) {
+            for (int k = 0; k < 3; k++) o.c[k] = m.p[k];
+        } else if (o.tex_type == SRT_TEX_CONSTANT) {
+            for (int k = 0; k < 3; k++) o.c[k] = d.textures[m.texture].c[k];
+        }
+        switch (m.type) {
+            case SRT_MAT_ORENNAYAR: feat |= F_ORENNAYAR; break;
+            case SRT_MAT_BECKMANN: feat |= F_BECKMANN; break;
+            case SRT_MAT_METAL: feat |= F_METAL; break;
+            case SRT_MAT_DIELECTRIC: feat |= F_DIELECTRIC; break;
+            case SRT_MAT_ISOTROPIC: feat |= F_MEDIA; break;
+            default: break;
+        }
+    }
+    for (int i = 0; i < d.n_textures; i++) {
+        if (d.textures[i].type == SRT_TEX_CHECKER) feat |= F_TEX_CHECKER;
+        if (d.textures[i].type == SRT_TEX_NOISE) feat |= F_TEX_NOISE;
+        if (d.textures[i].type == SRT_TEX_IMAGE) feat |= F_TEX_IMAGE;
+    }
+
     std::vector<int32_t> perlin_perm;
     if (d.perlin_ranvec) {
         if (!d.perlin_perm_x || !d.perlin_perm_y || !d.perlin_perm_z) return fail(SRT_E_INVALID, "incomplete perlin tables");
@@ -436,7 +588,7 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
         perlin_perm.insert(perlin_perm.end(), d.perlin_perm_z, d.perlin_perm_z + 256);
     }
 
-    // ---- one device allocation -----------------------------------------------------------------
+    // ---- one device allocation; the hot tables first and contiguous (16-byte aligned pieces) -----
     struct Piece {
         const void* src;
         size_t bytes;
@@ -444,15 +596,19 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     };
     std::vector<Piece> pieces;
     Layout lay;
-    auto piece = [&](const void* src, size_t bytes) -> size_t {
-        size_t off = lay.add(bytes);
+    auto piece = [&](const void* src, size_t bytes, size_t align = 256) -> size_t {
+        size_t off = lay.add(bytes, align);
         if (bytes) pieces.push_back(Piece{src, bytes, off});
         return off;
     };
-    size_t o_entries = piece(d.entries, sizeof(SrtEntry) * (size_t)d.n_entries);
-    size_t o_ops = piece(d.ops, sizeof(SrtXformOp) * (size_t)d.n_ops);
+    static_assert(sizeof(DEntry) == 64 && sizeof(DPrim) == 32 && sizeof(SrtXformOp) == 16 && sizeof(DMaterial) == 48,
+                  "record sizes are part of the device layout");
+    size_t o_entries = piece(dentries.data(), sizeof(DEntry) * dentries.size());
+    size_t o_ops = piece(d.ops, sizeof(SrtXformOp) * (size_t)d.n_ops, 16);
+    size_t o_dprims = piece(dprims.data(), sizeof(DPrim) * dprims.size(), 16);
+    size_t o_lights = piece(dlights.data(), sizeof(DPrim) * dlights.size(), 16);
+    size_t hot_end = (lay.total + 15) & ~(size_t)15;
     size_t o_groups = piece(d.groups, sizeof(SrtGroup) * (size_t)d.n_groups);
-    size_t o_prims = piece(d.prims, sizeof(SrtPrim) * (size_t)d.n_prims);
     size_t o_items = piece(d.bvh_items, sizeof(int32_t) * (size_t)d.n_bvh_items);
     size_t o_media = piece(d.media, sizeof(SrtMedium) * (size_t)d.n_media);
     size_t o_bvhs = piece(bvhs.data(), sizeof(DBvh) * bvhs.size());
@@ -460,14 +616,11 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     size_t o_ref = piece(refn.data(), sizeof(RefNode) * refn.size());
     size_t o_rank = piece(leaf_rank.data(), sizeof(int32_t) * leaf_rank.size());
     size_t o_geom = piece(leaf_geom.data(), sizeof(float4) * leaf_geom.size());
-    size_t o_spheres = piece(d.spheres, sizeof(float) * 4 * (size_t)d.n_spheres);
     size_t o_msph = piece(d.msph, sizeof(float) * 9 * (size_t)d.n_msph);
-    size_t o_rects = piece(rects.data(), sizeof(float4) * rects.size());
     size_t o_tpos = piece(d.tri_pos, sizeof(float) * 9 * (size_t)d.n_tris);
     size_t o_tnrm = piece(d.tri_nrm, sizeof(float) * 9 * (size_t)d.n_tris);
     size_t o_tuv = piece(d.tri_uv, sizeof(float) * 6 * (size_t)d.n_tris);
-    size_t o_lights = piece(d.lights, sizeof(SrtLight) * (size_t)d.n_lights);
-    size_t o_mats = piece(d.materials, sizeof(SrtMaterial) * (size_t)d.n_materials);
+    size_t o_mats = piece(dmats.data(), sizeof(DMaterial) * dmats.size());
     size_t o_texs = piece(d.textures, sizeof(SrtTexture) * (size_t)d.n_textures);
     size_t o_pran = piece(d.perlin_ranvec, d.perlin_ranvec ? sizeof(float) * 768 : 0);
     size_t o_pperm = piece(perlin_perm.data(), sizeof(int32_t) * perlin_perm.size());
@@ -496,6 +649,7 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
             return fail(SRT_E_CUDA, "%s: %s", #expr, cudaGetErrorString(e2_));    \
         }                                                                         \
     } while (0)
+    SCENE_TRY(cudaMemsetAsync(s->d_blob, 0, s->blob_bytes, ctx->stream));
     for (const Piece& p : pieces) SCENE_TRY(cudaMemcpyAsync(s->d_blob + p.off, p.src, p.bytes, cudaMemcpyHostToDevice, ctx->stream));
     std::vector<DImage> imgtab(d.n_images);
     for (int i = 0; i < d.n_images; i++) imgtab[i] = DImage{s->d_blob + o_img[i], d.images[i].nx, d.images[i].ny};
@@ -512,10 +666,11 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
 
     DScene& D = s->dev;
     uint8_t* base = s->d_blob;
-    D.entries = (const SrtEntry*)(base + o_entries);
+    D.entries = (const DEntry*)(base + o_entries);
     D.ops = (const SrtXformOp*)(base + o_ops);
+    D.dprims = (const DPrim*)(base + o_dprims);
+    D.lights = (const DPrim*)(base + o_lights);
     D.groups = (const SrtGroup*)(base + o_groups);
-    D.prims = (const SrtPrim*)(base + o_prims);
     D.bvh_items = (const int32_t*)(base + o_items);
     D.media = (const SrtMedium*)(base + o_media);
     D.bvhs = (const DBvh*)(base + o_bvhs);
@@ -523,14 +678,11 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     D.ref_nodes = (const RefNode*)(base + o_ref);
     D.leaf_rank = (const int32_t*)(base + o_rank);
     D.leaf_geom = (const float4*)(base + o_geom);
-    D.spheres = (const float4*)(base + o_spheres);
     D.msph = (const float*)(base + o_msph);
-    D.rects = (const float4*)(base + o_rects);
     D.tri_pos = (const float*)(base + o_tpos);
     D.tri_nrm = (const float*)(base + o_tnrm);
     D.tri_uv = (const float*)(base + o_tuv);
-    D.lights = (const SrtLight*)(base + o_lights);
-    D.materials = (const SrtMaterial*)(base + o_mats);
+    D.materials = (const DMaterial*)(base + o_mats);
     D.textures = (const SrtTexture*)(base + o_texs);
     D.images = (const DImage*)(base + o_imgtab);
     D.perlin_ranvec = (const float*)(base + o_pran);
@@ -543,8 +695,13 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     D.n_materials = d.n_materials;
     D.n_textures = d.n_textures;
     D.n_bvhs = d.n_bvhs;
-    D._pad = 0;
+    D.n_ops = d.n_ops;
+    D.hot_bytes = (uint32_t)(hot_end - o_entries);
+    D.features = feat;
     D.camera = d.camera;
+    (void)o_ops;
+    (void)o_dprims;
+    (void)o_lights;
 
     auto t1 = std::chrono::steady_clock::now();
     s->info.n_prims = d.n_prims;
@@ -563,6 +720,11 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
 int srt_scene_info(const SrtScene* scene, SrtSceneInfo* out) {
     if (!scene || !out) return fail(SRT_E_INVALID, "null argument");
     *out = scene->info;
+    out->features = scene->dev.features;
+    out->render_variant = scene->variant;
+    out->render_registers = scene->variant_regs;
+    out->render_blocks_per_sm = scene->variant_blocks;
+    out->hot_table_bytes = scene->dev.hot_bytes;
     return 0;
 }
 
@@ -629,6 +791,27 @@ int srt_merl_lookup(SrtScene* s, int32_t table, const double* angles, int64_t n,
     return 0;
 }
 
+int srt_selftest_division(SrtContext* c, const float* a, const float* b, int64_t n, uint64_t* mismatches) {
+    if (!c || !mismatches || (n > 0 && (!a || !b))) return fail(SRT_E_INVALID, "null argument");
+    *mismatches = 0;
+    if (n <= 0) return 0;
+    CUDA_TRY(cudaSetDevice(c->device));
+    DevIn ia, ib;
+    int rc;
+    if ((rc = ia.init(a, sizeof(float) * (size_t)n, c->stream))) return rc;
+    if ((rc = ib.init(b, sizeof(float) * (size_t)n, c->stream))) return rc;
+    CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, sizeof(unsigned long long), c->stream));
+    srt::k_check_xdiv<<<(unsigned)((n + 255) / 256), 256, 0, c->stream>>>((const float*)ia.ptr, (const float*)ib.ptr,
+                                                                          (long long)n, c->d_counters);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    unsigned long long h = 0;
+    CUDA_TRY(cudaMemcpyAsync(&h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CUDA_TRY(cudaStreamSynchronize(c->stream));
+    *mismatches = h;
+    return 0;
+}
+
 int srt_sobol_points_u32(uint32_t N, uint32_t* out) {
     // Raytracing_n.cpp:721-812 with D = 2: gray-code order, dimension 1 all m = 1, dimension 2 from
     // line 2 of new-joe-kuo-6.21201 ("2 1 0 1": s = 1, a = 0, m1 = 1).
@@ -690,13 +873,84 @@ int check_params(const SrtRenderParams* p) {
     return 0;
 }
 
-template <bool COUNT>
-int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum) {
+const RenderVariantFn kVariants[SRT_N_VARIANTS] = {srt_render_variant_0, srt_render_variant_1, srt_render_variant_2,
+                                                    srt_render_variant_3, srt_render_variant_4, srt_render_variant_5,
+                                                    srt_render_variant_6};
+constexpr uint32_t kVariantMask[SRT_N_VARIANTS] = {SRT_VARIANT_MASK(0), SRT_VARIANT_MASK(1), SRT_VARIANT_MASK(2),
+                                                   SRT_VARIANT_MASK(3), SRT_VARIANT_MASK(4), SRT_VARIANT_MASK(5),
+                                                   SRT_VARIANT_MASK(6)};
+constexpr int kVariantCounting[SRT_N_VARIANTS] = {SRT_VARIANT_COUNTING(0), SRT_VARIANT_COUNTING(1), SRT_VARIANT_COUNTING(2),
+                                                  SRT_VARIANT_COUNTING(3), SRT_VARIANT_COUNTING(4), SRT_VARIANT_COUNTING(5),
+                                                  SRT_VARIANT_COUNTING(6)};
+constexpr size_t kMaxHotSmem = 64 * 1024;  // above this the hot tables stay in global memory
+
+int env_int(const char* name, int fallback) {
+    const char* v = getenv(name);
+    return v && *v ? atoi(v) : fallback;
+}
+
+// The smallest compiled variant whose mask covers the scene (first match in list order).
+int pick_variant(const SrtScene* s, bool counting) {
+    uint32_t need = s->dev.features & F_ALL_SCENE;
+    bool smem_ok = s->dev.hot_bytes <= kMaxHotSmem && !env_int("SRT_NO_SMEM", 0);
+    int forced = env_int("SRT_VARIANT", -1);
+    for (int v = 0; v < SRT_N_VARIANTS; v++) {
+        if (forced >= 0 && v != forced) continue;
+        if (kVariantCounting[v] != (counting ? 1 : 0)) continue;
+        if ((kVariantMask[v] & F_SMEM_TABLES) && !smem_ok) continue;
+        if ((kVariantMask[v] & need) != need) continue;
+        return v;
+    }
+    return -1;
+}
+
+int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool counting) {
     SrtContext* c = s->ctx;
     int count = p->s_end - p->s_begin;
     if (count == 0) return 0;
     int rc = ensure_sobol(s, (uint32_t)p->s_end);
     if (rc) return rc;
+    int v = pick_variant(s, counting);
+    if (v < 0) return fail(SRT_E_UNSUPPORTED, "no render-kernel variant covers feature mask 0x%x", s->dev.features);
+    size_t smem = (kVariantMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
+
+    RenderLaunch L;
+    L.scene = &s->dev;
+    L.sobol = s->d_sobol;
+    L.counters = c->d_counters;
+    L.smem_bytes = smem;
+    L.stream = c->stream;
+    L.grid = 0;
+    RenderVariantInfo info = {};
+    if (!counting && s->variant == v) {
+        info.blocks_per_sm = s->variant_blocks;
+        info.registers = s->variant_regs;
+    } else {
+        L.args = nullptr;
+        L.out = nullptr;
+        cudaError_t e = kVariants[v](L, &info);
+        if (e != cudaSuccess) return fail(SRT_E_CUDA, "render variant %d: %s", v, cudaGetErrorString(e));
+        if (!counting) {
+            s->variant = v;
+            s->variant_blocks = info.blocks_per_sm;
+            s->variant_regs = info.registers;
+            s->variant_smem = smem;
+        }
+    }
+    int blocks_per_sm = std::max(1, info.blocks_per_sm);
+
+    // work decomposition (srt_kernels.cuh): enough items for ~16 per resident lane
+    long long n_pixels = (long long)p->nx * p->ny;
+    long long resident = (long long)c->sm_count * blocks_per_sm * srt::kRenderThreads;
+    long long want_items = 16 * resident;
+    int n_chunks = 1;
+    while (n_chunks < count && n_pixels * n_chunks < want_items) n_chunks <<= 1;
+    n_chunks = std::min(n_chunks, count);
+    n_chunks = env_int("SRT_CHUNKS", n_chunks);
+    n_chunks = std::max(1, std::min(n_chunks, count));
+    int chunk = (count + n_chunks - 1) / n_chunks;
+    n_chunks = (count + chunk - 1) / chunk;
+
     srt::RenderArgs A;
     A.nx = p->nx;
     A.ny = p->ny;
@@ -705,22 +959,41 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum) {
     A.max_depth = p->max_depth;
     A.seed = p->seed;
     A.mod_ny = (p->flags & SRT_COMPAT_PIXEL_MOD_NY) ? 1 : 0;
-    int L = 1;
-    while (L < count && L < 32) L <<= 1;
-    A.lanes_per_pixel = L;
-    int ppw = 32 / L;
-    long long n_pixels = (long long)p->nx * p->ny;
-    A.n_tiles = (int)((n_pixels + ppw - 1) / ppw);
-    const int threads = 256;
-    int blocks_per_sm = 0;
-    CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&blocks_per_sm, srt::k_render<COUNT>, threads, 0));
-    if (blocks_per_sm < 1) blocks_per_sm = 1;
-    long long want = (A.n_tiles + (threads / 32) - 1) / (threads / 32);
-    int grid = (int)std::min<long long>(want, (long long)c->sm_count * blocks_per_sm);
-    if (grid < 1) grid = 1;
-    srt::k_render<COUNT><<<grid, threads, 0, c->stream>>>(s->dev, A, s->d_sobol, accum, c->d_counters);
+    A.chunk = chunk;
+    A.n_chunks = n_chunks;
+    A.n_items = (unsigned)(n_pixels * n_chunks);
+    A.regen_threshold = std::max(1, std::min(32, env_int("SRT_REGEN", 8)));
+    A.grab = std::max(32, env_int("SRT_GRAB", 128));
+
+    float* out = accum;
+    if (n_chunks > 1) {
+        size_t need = sizeof(float) * 3 * (size_t)n_pixels * n_chunks;
+        if (s->partial_cap < need) {
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            cudaFree(s->d_partial);
+            s->d_partial = nullptr;
+            s->partial_cap = 0;
+            CUDA_TRY(cudaMalloc(&s->d_partial, need));
+            s->partial_cap = need;
+        }
+        out = s->d_partial;
+    }
+    // counters[7] is the work counter
+    CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
+    long long warps_needed = ((long long)A.n_items + 31) / 32;
+    long long blocks_needed = (warps_needed + (srt::kRenderThreads / 32) - 1) / (srt::kRenderThreads / 32);
+    L.args = &A;
+    L.out = out;
+    L.grid = (int)std::max<long long>(1, std::min<long long>(blocks_needed, (long long)c->sm_count * blocks_per_sm));
+    cudaError_t e = kVariants[v](L, nullptr);
     c->launches++;
-    CUDA_TRY(cudaGetLastError());
+    if (e != cudaSuccess) return fail(SRT_E_CUDA, "k_render (variant %d): %s", v, cudaGetErrorString(e));
+    if (n_chunks > 1) {
+        long long nv = 3 * n_pixels;
+        srt::k_sum_partials<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(s->d_partial, n_chunks, nv, accum);
+        c->launches++;
+        CUDA_TRY(cudaGetLastError());
+    }
     return 0;
 }
 
@@ -733,7 +1006,7 @@ int srt_render(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_device) {
     int rc = check_params(p);
     if (rc) return rc;
     CUDA_TRY(cudaSetDevice(s->ctx->device));
-    return launch_render<false>(s, p, accum_rgb_device);
+    return launch_render(s, p, accum_rgb_device, false);
 }
 
 int srt_render_counted(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_device, SrtCounters* out) {
@@ -743,7 +1016,7 @@ int srt_render_counted(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_d
     SrtContext* c = s->ctx;
     CUDA_TRY(cudaSetDevice(c->device));
     CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
-    rc = launch_render<true>(s, p, accum_rgb_device);
+    rc = launch_render(s, p, accum_rgb_device, true);
     if (rc) return rc;
     unsigned long long h[8];
     CUDA_TRY(cudaMemcpyAsync(h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream));
@@ -812,7 +1085,7 @@ int srt_render_image(SrtScene* s, const SrtRenderParams* p, uint8_t* rgb8_host, 
         s->accum_cap = nv;
     }
     CUDA_TRY(cudaMemsetAsync(s->d_accum, 0, sizeof(float) * nv, c->stream));
-    rc = launch_render<false>(s, p, s->d_accum);
+    rc = launch_render(s, p, s->d_accum, false);
     if (rc) return rc;
     if (accum_host) CUDA_TRY(cudaMemcpyAsync(accum_host, s->d_accum, sizeof(float) * nv, cudaMemcpyDeviceToHost, c->stream));
     return srt_resolve(c, s->d_accum, (int64_t)p->nx * p->ny, p->s_end - p->s_begin, rgb8_host);

@@ -1,0 +1,101 @@
+// srt_aux_kernels.cuh — the small __global__ entry points around the render kernel: batch closest
+// hit, light pdf, partial-sum reduction, resolve, MERL lookup, division self-test.  Included by
+// srt_api.cu only.
+#ifndef SRT_AUX_KERNELS_CUH
+#define SRT_AUX_KERNELS_CUH
+
+#include "srt_kernels.cuh"
+
+namespace srt {
+
+// Closest hit for a batch of rays: world->hit(r, 0.001, FLT_MAX, rec) (Raytracing_n.cpp:58).
+__global__ void __launch_bounds__(128) k_trace_closest(DScene S, const float* __restrict__ rays, long long n,
+                                                       int32_t* __restrict__ prim, float* __restrict__ t,
+                                                       float* __restrict__ rec, uint32_t seed) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    View W = global_view(S);
+    const float* q = rays + 7 * i;
+    Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
+    Philox rng;
+    philox_init(rng, seed, (uint32_t)i, (uint32_t)(i >> 32));
+    Tally<false> tl{nullptr};
+    Hit h = world_hit<F_ALL_SCENE>(W, r, 0.001f, kFltMax, rng, tl);
+    if (h.prim < 0) {
+        prim[i] = -1;
+        t[i] = 0.f;
+        if (rec)
+            for (int k = 0; k < 8; k++) rec[8 * i + k] = 0.f;
+        return;
+    }
+    prim[i] = h.prim;
+    t[i] = h.t;
+    if (rec) {
+        HitRecord hr = make_record<F_ALL_SCENE, true>(W, r, h);
+        float* o = rec + 8 * i;
+        o[0] = hr.u;
+        o[1] = hr.v;
+        o[2] = hr.p.x;
+        o[3] = hr.p.y;
+        o[4] = hr.p.z;
+        o[5] = hr.normal.x;
+        o[6] = hr.normal.y;
+        o[7] = hr.normal.z;
+    }
+}
+
+// hitable_list::pdf_value over the light list (hitable_list.h:54-62) for (origin, direction) pairs.
+__global__ void __launch_bounds__(128) k_light_pdf(DScene S, const float* __restrict__ od, long long n,
+                                                   float* __restrict__ out) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    View W = global_view(S);
+    const float* q = od + 6 * i;
+    Tally<false> tl{nullptr};
+    out[i] = S.n_lights > 0 ? light_pdf_value<F_ALL_SCENE>(W, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), tl) : 0.f;
+}
+
+// accum[i] += partial[0][i] + partial[1][i] + ... in fixed order (n_values = 3 * n_pixels).
+__global__ void __launch_bounds__(256) k_sum_partials(const float* __restrict__ partial, int n_chunks, long long n_values,
+                                                      float* __restrict__ accum) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    float s = partial[i];
+    for (int c = 1; c < n_chunks; c++) s += partial[(size_t)c * n_values + i];
+    accum[i] += s;
+}
+
+// mean -> sqrt -> int(255.99 c) -> clamp (Raytracing_n.cpp:848-862)
+__global__ void __launch_bounds__(256) k_resolve(const float* __restrict__ accum, long long n_values, float ns,
+                                                 uint8_t* __restrict__ out) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    float k = (float)(1.0 / (double)ns);  // vec3::operator/=(float): k = 1.0 / t, then e *= k
+    float c = xmul(accum[i], k);
+    c = xsqrt(c);
+    int v = (int)(255.99 * (double)c);
+    v = v > 255 ? 255 : v;
+    v = v < 0 ? 0 : v;
+    out[i] = (uint8_t)v;
+}
+
+__global__ void k_merl_lookup(const double* __restrict__ table, const double* __restrict__ angles, long long n,
+                              double* __restrict__ rgb) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const double* a = angles + 4 * i;
+    merl_lookup(table, a[0], a[1], a[2], a[3], rgb + 3 * i);
+}
+
+// a / b with the hoisted-reciprocal path against the library's __fdiv_rn (tests only)
+__global__ void k_check_xdiv(const float* __restrict__ a, const float* __restrict__ b, long long n,
+                             unsigned long long* __restrict__ mismatches) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    Rcp k = make_rcp(b[i]);
+    float q1 = xdiv(a[i], k), q2 = __fdiv_rn(a[i], b[i]);
+    if (__float_as_uint(q1) != __float_as_uint(q2) && !(q1 != q1 && q2 != q2)) atomicAdd(mismatches, 1ull);
+}
+
+}  // namespace srt
+#endif

@@ -2,7 +2,12 @@
 // / medium containers, wide-BVH traversal with reference-tree replay, hit-record reconstruction.
 //
 // Each routine cites the reference code it restates.  All arithmetic that decides ids or t uses the
-// exact (non-fused) operators of srt_math.cuh.
+// exact (non-fused) operators of srt_math.cuh; conservative pre-tests (entry bounds, wide-BVH boxes,
+// the quotient estimate in rect_hit) may only REJECT what the exact arithmetic would reject too.
+//
+// Everything is templated on the feature mask F (srt_types.h): code for reference classes a scene
+// does not instantiate is not compiled into the variant that renders it, which is what keeps the
+// render kernel inside the instruction cache (profiles/r01_notes.md).
 #ifndef SRT_INTERSECT_CUH
 #define SRT_INTERSECT_CUH
 
@@ -18,12 +23,21 @@ struct Counters {  // per-thread tallies of an instrumented launch (SrtCounters)
 template <bool COUNT>
 struct Tally {
     Counters* c;
-    SRT_DEV void node(int n = 1) {
+    SRT_DEV void node(int n = 1) const {
         if (COUNT) c->node_visits += n;
     }
-    SRT_DEV void prim(int n = 1) {
+    SRT_DEV void prim(int n = 1) const {
         if (COUNT) c->prim_tests += n;
     }
+};
+
+// The scene as a kernel sees it: DScene plus the (possibly shared-memory) hot tables.
+struct View {
+    const DScene& S;
+    const DEntry* entries;
+    const SrtXformOp* ops;
+    const DPrim* dprims;
+    const DPrim* lights;
 };
 
 struct Hit {
@@ -38,23 +52,42 @@ struct HitRecord {  // hitable.h:17-25
     int32_t material;
 };
 
+// A ray in some frame plus the divisor-only halves of the divisions its tests perform.
+struct RayK {
+    Ray r;
+    Rcp kx, ky, kz;  // 1 / direction components (rect tests)
+    Rcp ka;          // 1 / dot(d, d)            (sphere tests)
+    float a;         // dot(d, d)
+};
+SRT_DEV RayK make_rayk(const Ray& r) {
+    RayK q;
+    q.r = r;
+    q.kx = make_rcp(r.d.x);
+    q.ky = make_rcp(r.d.y);
+    q.kz = make_rcp(r.d.z);
+    q.a = dot(r.d, r.d);
+    q.ka = make_rcp(q.a);
+    return q;
+}
+
 // ---- primitives ------------------------------------------------------------------------------
 
 // sphere.h:36-66 (and moving_sphere.h:24-51 with center(time)): returns t only
-SRT_DEV bool sphere_hit(V3 center, float radius, const Ray& r, float t_min, float t_max, float& t) {
+SRT_DEV bool sphere_hit(V3 center, float radius, const RayK& q, float t_min, float t_max, float& t) {
+    const Ray& r = q.r;
     V3 oc = r.o - center;
-    float a = dot(r.d, r.d);
+    float a = q.a;
     float b = dot(oc, r.d);
     float c = xsub(dot(oc, oc), xmul(radius, radius));
     float disc = xsub(xmul(b, b), xmul(a, c));
     if (disc > 0.f) {
         float s = xsqrt(disc);
-        float temp = xdiv(xsub(-b, s), a);
+        float temp = xdiv(xsub(-b, s), q.ka);
         if (temp < t_max && temp > t_min) {
             t = temp;
             return true;
         }
-        temp = xdiv(xadd(-b, s), a);
+        temp = xdiv(xadd(-b, s), q.ka);
         if (temp < t_max && temp > t_min) {
             t = temp;
             return true;
@@ -70,36 +103,51 @@ SRT_DEV V3 msphere_center(const float* m, float time) {
     return c0 + k * (c1 - c0);
 }
 
-// aarect.h:96-147.  axis triple (ka, aa, ab): the constant axis and the two in-plane axes.
-SRT_DEV bool rect_hit(int type, float4 q0, float k, const Ray& r, float t0, float t1, float& t, float& a_out,
-                      float& b_out) {
-    int ka = type == SRT_PRIM_XY_RECT ? 2 : (type == SRT_PRIM_XZ_RECT ? 1 : 0);
-    int aa = type == SRT_PRIM_YZ_RECT ? 1 : 0;
-    int ab = type == SRT_PRIM_XY_RECT ? 1 : 2;
-    float tt = xdiv(xsub(k, comp(r.o, ka)), comp(r.d, ka));
+// aarect.h:96-147 for one orientation: KA = the constant axis, (AA, AB) the in-plane axes.
+//     t = (k - o[KA]) / d[KA];  if (t < t0 || t > t1) return false;
+//     a = o[AA] + t*d[AA]; b = o[AB] + t*d[AB];  if (a < a0 || a > a1 || b < b0 || b > b1) return false;
+// The quotient estimate (within 2 ulp of the rounded quotient when the divisor is in the safe
+// window) rejects planes that are clearly behind the ray or beyond the closest hit so far before
+// the division is completed.
+template <int KA, int AA, int AB>
+SRT_DEV bool rect_hit_axes(float4 g, float k, const RayK& q, float t0, float t1, float& t) {
+    const Ray& r = q.r;
+    const Rcp& kd = KA == 0 ? q.kx : (KA == 1 ? q.ky : q.kz);
+    float num = xsub(k, KA == 0 ? r.o.x : (KA == 1 ? r.o.y : r.o.z));
+    if (kd.safe) {
+        float est = xdiv_estimate(num, kd);
+        // |est - quotient| <= 4e-7 |quotient|; NaN compares false and falls through
+        if (est < t0 - 1e-6f * fabsf(t0) || est > t1 + 1e-6f * fabsf(t1)) return false;
+    }
+    float tt = xdiv(num, kd);
     if (tt < t0 || tt > t1) return false;
-    float a = xadd(comp(r.o, aa), xmul(tt, comp(r.d, aa)));
-    float b = xadd(comp(r.o, ab), xmul(tt, comp(r.d, ab)));
-    if (a < q0.x || a > q0.y || b < q0.z || b > q0.w) return false;
+    float oa = AA == 0 ? r.o.x : (AA == 1 ? r.o.y : r.o.z), da = AA == 0 ? r.d.x : (AA == 1 ? r.d.y : r.d.z);
+    float ob = AB == 0 ? r.o.x : (AB == 1 ? r.o.y : r.o.z), db = AB == 0 ? r.d.x : (AB == 1 ? r.d.y : r.d.z);
+    float a = xadd(oa, xmul(tt, da));
+    float b = xadd(ob, xmul(tt, db));
+    if (a < g.x || a > g.y || b < g.z || b > g.w) return false;
     t = tt;
-    a_out = a;
-    b_out = b;
     return true;
+}
+SRT_DEV bool rect_hit(int type, float4 g, float k, const RayK& q, float t0, float t1, float& t) {
+    if (type == SRT_PRIM_XY_RECT) return rect_hit_axes<2, 0, 1>(g, k, q, t0, t1, t);
+    if (type == SRT_PRIM_XZ_RECT) return rect_hit_axes<1, 0, 2>(g, k, q, t0, t1, t);
+    return rect_hit_axes<0, 1, 2>(g, k, q, t0, t1, t);
 }
 
 // triangle.h:108-188.  Ignores (t0, t1) as the reference does; t is in units of the NORMALISED
 // direction (triangle.h:128).  `(double)x < 0.0001` == `x <= 0.0001f` for float x.
-SRT_DEV bool tri_hit_face(bool front, V3 p0, V3 p1, V3 p2, const Ray& r, float& t, float& u, float& v) {
+// `dir` = r.direction() / r.direction().length(), computed once per ray.
+SRT_DEV bool tri_hit_face(bool front, V3 p0, V3 p1, V3 p2, V3 o, V3 dir, float& t, float& u, float& v) {
     V3 e1 = front ? p1 - p0 : p0 - p1;
     V3 e2 = front ? p2 - p0 : p2 - p1;
-    V3 dir = r.d / length(r.d);
     V3 P = cross(dir, e2);
     float det = dot(e1, P);
     V3 T;
     if (det > 0.f) {
-        T = r.o - p0;
+        T = o - p0;
     } else {
-        T = p0 - r.o;
+        T = p0 - o;
         det = -det;
     }
     if (det <= 0.0001f) return false;
@@ -119,9 +167,10 @@ SRT_DEV bool tri_hit_face(bool front, V3 p0, V3 p1, V3 p2, const Ray& r, float& 
     v = vv;
     return true;
 }
-SRT_DEV bool tri_hit(V3 p0, V3 p1, V3 p2, const Ray& r, bool is_medium, float& t, float& u, float& v) {
-    bool h = tri_hit_face(true, p0, p1, p2, r, t, u, v);
-    if (!h && is_medium) h = tri_hit_face(false, p0, p1, p2, r, t, u, v);  // triangle.h:108-115
+SRT_DEV V3 tri_dir(const Ray& r) { return r.d / length(r.d); }
+SRT_DEV bool tri_hit(V3 p0, V3 p1, V3 p2, V3 o, V3 dir, bool is_medium, float& t, float& u, float& v) {
+    bool h = tri_hit_face(true, p0, p1, p2, o, dir, t, u, v);
+    if (!h && is_medium) h = tri_hit_face(false, p0, p1, p2, o, dir, t, u, v);  // triangle.h:108-115
     return h;
 }
 
@@ -134,58 +183,57 @@ SRT_DEV float env_sphere_t(V3 center, float radius, const Ray& r) {
     return xadd(a, proj);
 }
 
-// One primitive of prims[] against a ray in the primitive's own frame.
-template <bool COUNT>
-SRT_DEV bool prim_hit(const DScene& S, const SrtPrim& pr, const Ray& r, float t_min, float t_max, bool is_medium,
+// One primitive record against a ray in the primitive's own frame.
+template <uint32_t F, bool COUNT>
+SRT_DEV bool prim_hit(const View& W, const DPrim& pr, const RayK& q, float t_min, float t_max, bool is_medium,
                       float& t, Tally<COUNT> tl) {
     tl.prim();
-    switch (pr.type) {
-        case SRT_PRIM_SPHERE: {
-            float4 s = __ldg(&S.spheres[pr.index]);
-            return sphere_hit(v3(s.x, s.y, s.z), s.w, r, t_min, t_max, t);
-        }
-        case SRT_PRIM_MOVING_SPHERE: {
-            const float* m = S.msph + 9 * (size_t)pr.index;
-            return sphere_hit(msphere_center(m, r.time), m[8], r, t_min, t_max, t);
-        }
-        case SRT_PRIM_XY_RECT:
-        case SRT_PRIM_XZ_RECT:
-        case SRT_PRIM_YZ_RECT: {
-            float4 q0 = __ldg(&S.rects[2 * pr.index]);
-            float k = __ldg(&S.rects[2 * pr.index + 1]).x;
-            float a, b;
-            return rect_hit(pr.type, q0, k, r, t_min, t_max, t, a, b);
-        }
-        case SRT_PRIM_TRIANGLE: {
-            const float* p = S.tri_pos + 9 * (size_t)pr.index;
-            float u, v;
-            return tri_hit(v3(p), v3(p + 3), v3(p + 6), r, is_medium, t, u, v);
-        }
-        case SRT_PRIM_ENV_SPHERE: {
-            float4 s = __ldg(&S.spheres[pr.index]);
-            t = env_sphere_t(v3(s.x, s.y, s.z), s.w, r);
-            return true;
-        }
-        default:
-            return false;
+    int type = pr.type;
+    if (type >= SRT_PRIM_XY_RECT && type <= SRT_PRIM_YZ_RECT) return rect_hit(type, pr.g, pr.k, q, t_min, t_max, t);
+    if (type == SRT_PRIM_SPHERE) return sphere_hit(v3(pr.g.x, pr.g.y, pr.g.z), pr.g.w, q, t_min, t_max, t);
+    if ((F & F_TRI) && type == SRT_PRIM_TRIANGLE) {
+        const float* p = W.S.tri_pos + 9 * (size_t)(pr.flags_aux >> 1);
+        float u, v;
+        return tri_hit(v3(p), v3(p + 3), v3(p + 6), q.r.o, tri_dir(q.r), is_medium, t, u, v);
     }
+    if ((F & F_MSPHERE) && type == SRT_PRIM_MOVING_SPHERE) {
+        const float* m = W.S.msph + 9 * (size_t)(pr.flags_aux >> 1);
+        return sphere_hit(msphere_center(m, q.r.time), m[8], q, t_min, t_max, t);
+    }
+    if ((F & F_ENV) && type == SRT_PRIM_ENV_SPHERE) {
+        t = env_sphere_t(v3(pr.g.x, pr.g.y, pr.g.z), pr.g.w, q.r);
+        return true;
+    }
+    return false;
 }
 
-// hitable_list::hit (hitable_list.h:21-33) over one group: in order, t_max narrowed to the last
-// accepted t (the double closest_so_far holds a float value, so the narrowing is exact).
-template <bool COUNT>
-SRT_DEV bool group_hit(const DScene& S, int group, const Ray& r, float t_min, float t_max, bool is_medium, float& t,
-                       int32_t& prim, Tally<COUNT> tl) {
-    SrtGroup g = S.groups[group];
+SRT_DEV DPrim load_prim(const DPrim* p) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+    float4 a = q[0], b = q[1];
+    DPrim r;
+    r.g = a;
+    r.k = b.x;
+    r.type = __float_as_int(b.y);
+    r.material = __float_as_int(b.z);
+    r.flags_aux = __float_as_uint(b.w);
+    return r;
+}
+
+// hitable_list::hit (hitable_list.h:21-33) over prims [first, first + count): in order, t_max
+// narrowed to the last accepted t (the double closest_so_far holds a float value, so the narrowing
+// is exact).
+template <uint32_t F, bool COUNT>
+SRT_DEV bool group_hit(const View& W, int first, int count, const RayK& q, float t_min, float t_max, bool is_medium,
+                       float& t, int32_t& prim, Tally<COUNT> tl) {
     bool any = false;
     float closest = t_max;
-    for (int i = 0; i < g.prim_count; i++) {
-        SrtPrim pr = S.prims[g.first_prim + i];
+    for (int i = 0; i < count; i++) {
+        DPrim pr = load_prim(W.dprims + first + i);
         float tt;
-        if (prim_hit(S, pr, r, t_min, closest, is_medium, tt, tl)) {
+        if (prim_hit<F>(W, pr, q, t_min, closest, is_medium, tt, tl)) {
             any = true;
             closest = tt;
-            prim = g.first_prim + i;
+            prim = first + i;
         }
     }
     t = closest;
@@ -196,9 +244,9 @@ SRT_DEV bool group_hit(const DScene& S, int group, const Ray& r, float t_min, fl
 struct RayInv {
     float ix, iy, iz;
 };
-SRT_DEV bool ref_aabb_hit(const float* lo, const float* hi, const Ray& r, RayInv inv, float tmin, float tmax) {
+SRT_DEV bool ref_aabb_hit(float4 lo, float4 hi, const Ray& r, RayInv inv, float tmin, float tmax) {
     {
-        float t0 = xmul(xsub(lo[0], r.o.x), inv.ix), t1 = xmul(xsub(hi[0], r.o.x), inv.ix);
+        float t0 = xmul(xsub(lo.x, r.o.x), inv.ix), t1 = xmul(xsub(hi.x, r.o.x), inv.ix);
         if (inv.ix < 0.0f) {
             float s = t0;
             t0 = t1;
@@ -209,7 +257,7 @@ SRT_DEV bool ref_aabb_hit(const float* lo, const float* hi, const Ray& r, RayInv
         if (tmax <= tmin) return false;
     }
     {
-        float t0 = xmul(xsub(lo[1], r.o.y), inv.iy), t1 = xmul(xsub(hi[1], r.o.y), inv.iy);
+        float t0 = xmul(xsub(lo.y, r.o.y), inv.iy), t1 = xmul(xsub(hi.y, r.o.y), inv.iy);
         if (inv.iy < 0.0f) {
             float s = t0;
             t0 = t1;
@@ -220,7 +268,7 @@ SRT_DEV bool ref_aabb_hit(const float* lo, const float* hi, const Ray& r, RayInv
         if (tmax <= tmin) return false;
     }
     {
-        float t0 = xmul(xsub(lo[2], r.o.z), inv.iz), t1 = xmul(xsub(hi[2], r.o.z), inv.iz);
+        float t0 = xmul(xsub(lo.z, r.o.z), inv.iz), t1 = xmul(xsub(hi.z, r.o.z), inv.iz);
         if (inv.iz < 0.0f) {
             float s = t0;
             t0 = t1;
@@ -243,8 +291,7 @@ SRT_DEV bool ref_reachable(const RefNode* root, int rank, const Ray& r, RayInv i
         const float4* q = reinterpret_cast<const float4*>(root + idx);
         float4 a = __ldg(q), b = __ldg(q + 1);
         tl.node();
-        float lo[3] = {a.x, a.y, a.z}, hi[3] = {b.x, b.y, b.z};
-        if (!ref_aabb_hit(lo, hi, r, inv, t_min, t_max)) return false;
+        if (!ref_aabb_hit(a, b, r, inv, t_min, t_max)) return false;
         int left = __float_as_int(a.w), right = __float_as_int(b.w);
         if (left < 0) return true;
         int mid = __ldg(&root[idx].mid);
@@ -253,134 +300,150 @@ SRT_DEV bool ref_reachable(const RefNode* root, int rank, const Ray& r, RayInv i
 }
 
 // ---- wide-BVH traversal -------------------------------------------------------------------------
-// Result of a reference `bvh_node::hit(r, t_min, t_max)` (bvh.h:64-93): over all reachable leaves
+// Result of a reference `bvh_node::hit(r, t_min, t_max)` (bvh.h:64-93): over all REACHABLE leaves
 // that hit, the smallest t; on equal t the leaf later in the in-order sequence (the right child
 // wins every `left_rec.t < right_rec.t` tie).  Leaves are tested with the un-narrowed entry
 // (t_min, t_max), as in the reference; OUR tree only orders the search and prunes conservatively.
+//
+// Reachability (the un-padded reference ancestor boxes) fails only for rays grazing a box face, so
+// it is checked for the WINNER only: a pass finds the best candidate strictly after the exclusion
+// bound (ex_t, ex_rank) in the order "smaller t first, then higher rank"; if that candidate turns
+// out unreachable it becomes the new bound and the search repeats.  One pass in all but ~1e-6 of rays.
 constexpr int kStackSize = 48;
 
-template <bool COUNT>
-SRT_DEV bool bvh_hit(const DScene& S, const DBvh& B, const Ray& r, float t_min, float t_max, bool is_medium,
+template <uint32_t F, bool COUNT>
+SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, float t_max, bool is_medium,
                      float& t_out, int32_t& prim_out, Tally<COUNT> tl) {
-    RayInv inv{xdiv(1.0f, r.d.x), xdiv(1.0f, r.d.y), xdiv(1.0f, r.d.z)};
+    const DScene& S = W.S;
+    const Ray& r = q.r;
+    RayInv inv{xdiv(1.0f, q.kx), xdiv(1.0f, q.ky), xdiv(1.0f, q.kz)};
     // pruning scale: triangle t is a distance, box slabs are parametric
-    float len = length(r.d);
-    float tscale = B.kind == BVH_KIND_SPHERE ? 1.0f : (B.kind == BVH_KIND_TRIANGLE ? len : fminf(1.0f, len));
+    float len = xsqrt(q.a);
+    const int kind = (F & F_BVH_GENERIC) || ((F & F_BVH_SPHERE) && (F & F_BVH_TRI))
+                         ? B.kind
+                         : ((F & F_BVH_TRI) ? BVH_KIND_TRIANGLE : BVH_KIND_SPHERE);
+    float tscale = kind == BVH_KIND_SPHERE ? 1.0f : (kind == BVH_KIND_TRIANGLE ? len : fminf(1.0f, len));
     if (!(tscale == tscale)) return false;  // NaN direction: nothing sensible to report
     const WideNode4* nodes = S.wide_nodes + B.node_base;
     const RefNode* ref = S.ref_nodes + B.ref_base;
     const int32_t* ranks = S.leaf_rank + B.leaf_base;
-    float best_t = CUDART_INF_F;
-    int best_rank = -1;
-    int32_t best_prim = -1;
+    V3 tdir = v3(0.f, 0.f, 0.f);
+    if ((F & (F_BVH_TRI | F_BVH_GENERIC)) && kind != BVH_KIND_SPHERE) tdir = tri_dir(r);
 
-    int32_t stack[kStackSize];
-    int sp = 0;
-    int32_t cur = 0;  // >= 0 inner node; < 0 leaf reference packed as ~(first << 3 | count)
-    for (;;) {
-        if (cur >= 0) {
-            const float4* q = reinterpret_cast<const float4*>(nodes + cur);
-            float4 lox = __ldg(q), loy = __ldg(q + 1), loz = __ldg(q + 2);
-            float4 hix = __ldg(q + 3), hiy = __ldg(q + 4), hiz = __ldg(q + 5);
-            int4 child = __ldg(reinterpret_cast<const int4*>(q + 6));
-            int4 count = __ldg(reinterpret_cast<const int4*>(q + 7));
-            tl.node();
-            float tn[4];
-            int32_t ref4[4];
-            const float* LX = &lox.x;
-            const float* LY = &loy.x;
-            const float* LZ = &loz.x;
-            const float* HX = &hix.x;
-            const float* HY = &hiy.x;
-            const float* HZ = &hiz.x;
-            const int* CH = &child.x;
-            const int* CN = &count.x;
-            int nhit = 0;
+    float ex_t = -CUDART_INF_F;
+    int ex_rank = 0x7fffffff;
+    for (;;) {  // passes (see above)
+        float best_t = CUDART_INF_F;
+        int best_rank = -1;
+        int32_t best_prim = -1;
+        int32_t stack[kStackSize];
+        int sp = 0;
+        int32_t cur = 0;  // >= 0 inner node; < 0 leaf reference packed as ~(first << 3 | count)
+        for (;;) {
+            if (cur >= 0) {
+                const float4* nq = reinterpret_cast<const float4*>(nodes + cur);
+                float4 lox = __ldg(nq), loy = __ldg(nq + 1), loz = __ldg(nq + 2);
+                float4 hix = __ldg(nq + 3), hiy = __ldg(nq + 4), hiz = __ldg(nq + 5);
+                int4 child = __ldg(reinterpret_cast<const int4*>(nq + 6));
+                int4 count = __ldg(reinterpret_cast<const int4*>(nq + 7));
+                tl.node();
+                float tn[4];
+                int32_t ref4[4];
+                const float LX[4] = {lox.x, lox.y, lox.z, lox.w}, LY[4] = {loy.x, loy.y, loy.z, loy.w};
+                const float LZ[4] = {loz.x, loz.y, loz.z, loz.w}, HX[4] = {hix.x, hix.y, hix.z, hix.w};
+                const float HY[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, HZ[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
+                const int CH[4] = {child.x, child.y, child.z, child.w}, CN[4] = {count.x, count.y, count.z, count.w};
+                int nhit = 0;
 #pragma unroll
-            for (int i = 0; i < 4; i++) {
-                float ax = (LX[i] - r.o.x) * inv.ix, bx = (HX[i] - r.o.x) * inv.ix;
-                float ay = (LY[i] - r.o.y) * inv.iy, by = (HY[i] - r.o.y) * inv.iy;
-                float az = (LZ[i] - r.o.z) * inv.iz, bz = (HZ[i] - r.o.z) * inv.iz;
-                float n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
-                float f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
-                // conservative: widen the interval by a few ulps before deciding
-                n = n - fabsf(n) * 4e-6f;
-                f = f + fabsf(f) * 4e-6f;
-                bool empty = CH[i] < 0 && CN[i] == 0;
-                // lower bound of any leaf t inside this box, in the leaves' own units
-                float lb = n > 0.0f ? n * tscale : (B.kind == BVH_KIND_TRIANGLE ? 0.0f : n);
-                bool h = !empty && n <= f && f >= fminf(t_min, 0.0f) && lb <= best_t;
-                if (h) {
-                    tn[nhit] = n;
-                    ref4[nhit] = CH[i] >= 0 ? CH[i] : ~(((~CH[i]) << 3) | CN[i]);
-                    nhit++;
+                for (int i = 0; i < 4; i++) {
+                    float ax = (LX[i] - r.o.x) * inv.ix, bx = (HX[i] - r.o.x) * inv.ix;
+                    float ay = (LY[i] - r.o.y) * inv.iy, by = (HY[i] - r.o.y) * inv.iy;
+                    float az = (LZ[i] - r.o.z) * inv.iz, bz = (HZ[i] - r.o.z) * inv.iz;
+                    float n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+                    float f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+                    // conservative: widen the interval by a few ulps before deciding
+                    n = n - fabsf(n) * 4e-6f;
+                    f = f + fabsf(f) * 4e-6f;
+                    bool empty = CH[i] < 0 && CN[i] == 0;
+                    // lower bound of any leaf t inside this box, in the leaves' own units
+                    float lb = n > 0.0f ? n * tscale : (kind == BVH_KIND_TRIANGLE ? 0.0f : n);
+                    bool h = !empty && n <= f && f >= fminf(t_min, 0.0f) && lb <= best_t;
+                    if (h) {
+                        tn[nhit] = n;
+                        ref4[nhit] = CH[i] >= 0 ? CH[i] : ~(((~CH[i]) << 3) | CN[i]);
+                        nhit++;
+                    }
                 }
-            }
-            if (nhit == 0) {
-                if (sp == 0) break;
-                cur = stack[--sp];
+                if (nhit == 0) {
+                    if (sp == 0) break;
+                    cur = stack[--sp];
+                    continue;
+                }
+                // insertion sort by entry distance (nearest first), push the rest far-to-near
+                for (int i = 1; i < nhit; i++) {
+                    float kt = tn[i];
+                    int32_t kr = ref4[i];
+                    int j = i - 1;
+                    while (j >= 0 && tn[j] > kt) {
+                        tn[j + 1] = tn[j];
+                        ref4[j + 1] = ref4[j];
+                        j--;
+                    }
+                    tn[j + 1] = kt;
+                    ref4[j + 1] = kr;
+                }
+                for (int i = nhit - 1; i >= 1; i--)
+                    if (sp < kStackSize) stack[sp++] = ref4[i];
+                cur = ref4[0];
                 continue;
             }
-            // insertion sort by entry distance (nearest first), push the rest far-to-near
-            for (int i = 1; i < nhit; i++) {
-                float kt = tn[i];
-                int32_t kr = ref4[i];
-                int j = i - 1;
-                while (j >= 0 && tn[j] > kt) {
-                    tn[j + 1] = tn[j];
-                    ref4[j + 1] = ref4[j];
-                    j--;
-                }
-                tn[j + 1] = kt;
-                ref4[j + 1] = kr;
-            }
-            for (int i = nhit - 1; i >= 1; i--)
-                if (sp < kStackSize) stack[sp++] = ref4[i];
-            cur = ref4[0];
-            continue;
-        }
-        // leaf
-        {
-            int packed = ~cur;
-            int first = packed >> 3, cnt = packed & 7;
-            for (int s = first; s < first + cnt; s++) {
-                int rank = __ldg(&ranks[s]);
-                float tt;
-                int32_t pp;
-                bool h;
-                if (B.kind == BVH_KIND_SPHERE) {
-                    float4 sp4 = __ldg(&S.leaf_geom[B.geom_base + s]);
-                    tl.prim();
-                    h = sphere_hit(v3(sp4.x, sp4.y, sp4.z), sp4.w, r, t_min, t_max, tt);
-                    pp = -2;  // resolved from the rank at the end
-                } else if (B.kind == BVH_KIND_TRIANGLE) {
-                    const float4* g = S.leaf_geom + B.geom_base + 3 * (size_t)s;
-                    float4 a = __ldg(g), b = __ldg(g + 1), c = __ldg(g + 2);
-                    float u, v;
-                    tl.prim();
-                    h = tri_hit(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), r, is_medium, tt, u, v);
-                    pp = -2;
-                } else {
-                    int group = __ldg(&S.bvh_items[B.first_item + rank]);
-                    h = group_hit(S, group, r, t_min, t_max, is_medium, tt, pp, tl);
-                }
-                if (h && (tt < best_t || (tt == best_t && rank > best_rank))) {
-                    if (ref_reachable(ref, rank, r, inv, t_min, t_max, tl)) {
+            // leaf
+            {
+                int packed = ~cur;
+                int first = packed >> 3, cnt = packed & 7;
+                for (int s = first; s < first + cnt; s++) {
+                    int rank = __ldg(&ranks[s]);
+                    float tt;
+                    int32_t pp;
+                    bool h;
+                    if (kind == BVH_KIND_SPHERE) {
+                        float4 sp4 = __ldg(&S.leaf_geom[B.geom_base + s]);
+                        tl.prim();
+                        h = sphere_hit(v3(sp4.x, sp4.y, sp4.z), sp4.w, q, t_min, t_max, tt);
+                        pp = -2;  // resolved from the rank at the end
+                    } else if (kind == BVH_KIND_TRIANGLE) {
+                        const float4* g = S.leaf_geom + B.geom_base + 3 * (size_t)s;
+                        float4 a = __ldg(g), b = __ldg(g + 1), c = __ldg(g + 2);
+                        float u, v;
+                        tl.prim();
+                        h = tri_hit(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), r.o, tdir, is_medium, tt, u,
+                                    v);
+                        pp = -2;
+                    } else {
+                        SrtGroup g = S.groups[__ldg(&S.bvh_items[B.first_item + rank])];
+                        h = group_hit<F>(W, g.first_prim, g.prim_count, q, t_min, t_max, is_medium, tt, pp, tl);
+                    }
+                    if (h && (tt < best_t || (tt == best_t && rank > best_rank)) &&
+                        (tt > ex_t || (tt == ex_t && rank < ex_rank))) {
                         best_t = tt;
                         best_rank = rank;
                         best_prim = pp;
                     }
                 }
             }
+            if (sp == 0) break;
+            cur = stack[--sp];
         }
-        if (sp == 0) break;
-        cur = stack[--sp];
+        if (best_rank < 0) return false;
+        if (ref_reachable(ref, best_rank, r, inv, t_min, t_max, tl)) {
+            if (best_prim == -2) best_prim = S.groups[S.bvh_items[B.first_item + best_rank]].first_prim;
+            t_out = best_t;
+            prim_out = best_prim;
+            return true;
+        }
+        ex_t = best_t;
+        ex_rank = best_rank;
     }
-    if (best_rank < 0) return false;
-    if (best_prim == -2) best_prim = S.groups[S.bvh_items[B.first_item + best_rank]].first_prim;
-    t_out = best_t;
-    prim_out = best_prim;
-    return true;
 }
 
 // ---- instance transforms (hitable.h:44-52, :109-132, :180-203) -----------------------------------
@@ -435,38 +498,91 @@ SRT_DEV void xform_rec_out(const SrtXformOp& op, V3& p, V3& n) {
     }
 }
 
-SRT_DEV Ray entry_local_ray(const DScene& S, const SrtEntry& e, Ray r) {
-    for (int i = 0; i < e.op_count; i++) r = xform_ray_in(S.ops[e.first_op + i], r);
+SRT_DEV SrtXformOp load_op(const SrtXformOp* p) {
+    float4 v = *reinterpret_cast<const float4*>(p);
+    SrtXformOp o;
+    o.kind = __float_as_int(v.x);
+    o.a = v.y;
+    o.b = v.z;
+    o.c = v.w;
+    return o;
+}
+
+SRT_DEV DEntry load_entry_head(const DEntry* p) {  // the first 32 bytes: ranges, kind, medium, flags
+    const int4* q = reinterpret_cast<const int4*>(p);
+    int4 a = q[0], b = q[1];
+    DEntry e;
+    e.first_prim = a.x;
+    e.prim_count = a.y;
+    e.first_op = a.z;
+    e.op_count = a.w;
+    e.geom_kind = b.x;
+    e.geom_index = b.y;
+    e.medium = b.z;
+    e.flags = (uint32_t)b.w;
+    return e;
+}
+
+template <uint32_t F>
+SRT_DEV Ray entry_local_ray(const View& W, int first_op, int op_count, Ray r) {
+    if (F & F_XFORM)
+        for (int i = 0; i < op_count; i++) r = xform_ray_in(load_op(W.ops + first_op + i), r);
     return r;
 }
 
+// Conservative slab test of a ray against an entry's bounds (local frame).  Returns false only
+// when no primitive below can be hit: the bounds are padded (srt_api.cu: entry_bounds) and the
+// interval is widened by a relative and an origin-scaled margin before the decision.
+SRT_DEV bool entry_bounds_hit(const DEntry* ep, const RayK& q, float t_min, float t_max, bool tcull) {
+    const float4* p = reinterpret_cast<const float4*>(ep);
+    float4 lo = p[2], hi = p[3];
+    const Ray& r = q.r;
+    if (!(q.kx.safe && q.ky.safe && q.kz.safe)) return true;  // axis-parallel or denormal direction
+    float ax = (lo.x - r.o.x) * q.kx.r, bx = (hi.x - r.o.x) * q.kx.r;
+    float ay = (lo.y - r.o.y) * q.ky.r, by = (hi.y - r.o.y) * q.ky.r;
+    float az = (lo.z - r.o.z) * q.kz.r, bz = (hi.z - r.o.z) * q.kz.r;
+    float n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
+    float f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
+    float em = 2e-6f * fmaxf(fmaxf(fabsf(r.o.x * q.kx.r), fabsf(r.o.y * q.ky.r)), fabsf(r.o.z * q.kz.r));
+    n = n - fabsf(n) * 4e-6f - em;
+    f = f + fabsf(f) * 4e-6f + em;
+    if (!(n <= f)) return false;
+    if (f < fminf(t_min, 0.0f)) return false;
+    if (tcull && n > t_max) return false;
+    return true;
+}
+
 // The geometry below an entry's transform chain (group or bvh), without the medium wrapper.
-template <bool COUNT>
-SRT_DEV bool entry_geom_hit(const DScene& S, const SrtEntry& e, const Ray& world_ray, float t_min, float t_max,
-                            bool is_medium, float& t, int32_t& prim, Tally<COUNT> tl) {
-    Ray r = entry_local_ray(S, e, world_ray);
-    if (e.geom_kind == SRT_GEOM_GROUP) return group_hit(S, e.geom_index, r, t_min, t_max, is_medium, t, prim, tl);
-    DBvh B = S.bvhs[e.geom_index];
-    return bvh_hit(S, B, r, t_min, t_max, is_medium, t, prim, tl);
+template <uint32_t F, bool COUNT>
+SRT_DEV bool entry_geom_hit(const View& W, const DEntry* ep, const DEntry& e, const Ray& world_ray, float t_min,
+                            float t_max, bool is_medium, float& t, int32_t& prim, Tally<COUNT> tl) {
+    Ray lr = entry_local_ray<F>(W, e.first_op, e.op_count, world_ray);
+    RayK q = make_rayk(lr);
+    if ((e.flags & DENTRY_CULL) && !is_medium && !entry_bounds_hit(ep, q, t_min, t_max, (e.flags & DENTRY_TCULL) != 0))
+        return false;
+    if (!(F & (F_BVH_SPHERE | F_BVH_TRI | F_BVH_GENERIC)) || e.geom_kind == SRT_GEOM_GROUP)
+        return group_hit<F>(W, e.first_prim, e.prim_count, q, t_min, t_max, is_medium, t, prim, tl);
+    DBvh B = W.S.bvhs[e.geom_index];
+    return bvh_hit<F>(W, B, q, t_min, t_max, is_medium, t, prim, tl);
 }
 
 // constant_medium::hit (constant_medium.h:19-50): two boundary hits, then an exponential
 // free-flight distance.  The dead debug draw at :20 is not reproduced (counter RNG).
-template <bool COUNT>
-SRT_DEV bool medium_hit(const DScene& S, const SrtEntry& e, const Ray& r, float t_min, float t_max, Philox& rng,
-                        float& t, Tally<COUNT> tl) {
+template <uint32_t F, bool COUNT>
+SRT_DEV bool medium_hit(const View& W, const DEntry* ep, const DEntry& e, const Ray& r, float t_min, float t_max,
+                        Philox& rng, float& t, Tally<COUNT> tl) {
     float t1, t2;
     int32_t p1, p2;
-    if (!entry_geom_hit(S, e, r, -kFltMax, kFltMax, true, t1, p1, tl)) return false;
+    if (!entry_geom_hit<F>(W, ep, e, r, -kFltMax, kFltMax, true, t1, p1, tl)) return false;
     float t_min2 = (float)((double)t1 + 0.0001);
-    if (!entry_geom_hit(S, e, r, t_min2, kFltMax, true, t2, p2, tl)) return false;
+    if (!entry_geom_hit<F>(W, ep, e, r, t_min2, kFltMax, true, t2, p2, tl)) return false;
     if (t1 < t_min) t1 = t_min;
     if (t2 > t_max) t2 = t_max;
     if (t1 >= t2) return false;
     if (t1 < 0.f) t1 = 0.f;
     float len = length(r.d);
     float distance_inside = xmul(xsub(t2, t1), len);
-    float density = S.media[e.medium].density;
+    float density = W.S.media[e.medium].density;
     float hit_distance = (float)(-(double)xdiv(1.0f, density) * log(rand_d(rng)));
     if (hit_distance < distance_inside) {
         t = xadd(t1, xdiv(hit_distance, len));
@@ -476,23 +592,31 @@ SRT_DEV bool medium_hit(const DScene& S, const SrtEntry& e, const Ray& r, float 
 }
 
 // world->hit(r, t_min, t_max, rec) (Raytracing_n.cpp:58): the top-level hitable_list.
-template <bool COUNT>
-SRT_DEV Hit world_hit(const DScene& S, const Ray& r, float t_min, float t_max, Philox& rng, Tally<COUNT> tl) {
+template <uint32_t F, bool COUNT>
+SRT_DEV Hit world_hit(const View& W, const Ray& r, float t_min, float t_max, Philox& rng, Tally<COUNT> tl) {
     Hit h;
     h.prim = -1;
     h.entry = -1;
     h.t = t_max;
     float closest = t_max;
-    for (int ei = 0; ei < S.n_entries; ei++) {
-        SrtEntry e = S.entries[ei];
+    RayK qw = make_rayk(r);  // for entries without a transform chain
+    const int n = W.S.n_entries;
+    for (int ei = 0; ei < n; ei++) {
+        const DEntry* ep = W.entries + ei;
+        DEntry e = load_entry_head(ep);
         float t;
         int32_t prim = -1;
         bool got;
-        if (e.medium >= 0) {
-            got = medium_hit(S, e, r, t_min, closest, rng, t, tl);
-            prim = S.n_prims + e.medium;
+        if ((F & F_MEDIA) && e.medium >= 0) {
+            got = medium_hit<F>(W, ep, e, r, t_min, closest, rng, t, tl);
+            prim = W.S.n_prims + e.medium;
+        } else if (e.op_count == 0 && e.geom_kind == SRT_GEOM_GROUP) {
+            // fast path: untransformed list of primitives shares the world-frame ray constants
+            if ((e.flags & DENTRY_CULL) && !entry_bounds_hit(ep, qw, t_min, closest, (e.flags & DENTRY_TCULL) != 0))
+                continue;
+            got = group_hit<F>(W, e.first_prim, e.prim_count, qw, t_min, closest, false, t, prim, tl);
         } else {
-            got = entry_geom_hit(S, e, r, t_min, closest, false, t, prim, tl);
+            got = entry_geom_hit<F>(W, ep, e, r, t_min, closest, false, t, prim, tl);
         }
         if (got) {
             closest = t;
@@ -513,78 +637,71 @@ SRT_DEV void get_sphere_uv(V3 p, float& u, float& v) {
     v = (float)(((double)theta + kPi / 2.0) / kPi);
 }
 
-// Re-runs the winning primitive's test to fill u, v, p, normal exactly as its hit() does, then
-// unwinds flip_normals and the instance chain (aarect.h:152-159, hitable.h:44-52, :109-132).
-template <bool WANT_UV>
-SRT_DEV HitRecord make_record(const DScene& S, const Ray& world_ray, const Hit& h) {
+// Re-runs the winning primitive's arithmetic to fill u, v, p, normal exactly as its hit() does,
+// then unwinds flip_normals and the instance chain (aarect.h:152-159, hitable.h:44-52, :109-132).
+template <uint32_t F, bool WANT_UV>
+SRT_DEV HitRecord make_record(const View& W, const Ray& world_ray, const Hit& h) {
+    const DScene& S = W.S;
     HitRecord rec;
     rec.t = h.t;
     rec.u = rec.v = 0.f;
     rec.material = -1;
-    if (h.prim >= S.n_prims) {  // constant_medium.h:39-44
+    if ((F & F_MEDIA) && h.prim >= S.n_prims) {  // constant_medium.h:39-44
         rec.p = point_at(world_ray, h.t);
         rec.normal = v3(1.f, 0.f, 0.f);
         rec.material = S.media[h.prim - S.n_prims].phase_material;
         return rec;
     }
-    SrtEntry e = S.entries[h.entry];
-    Ray r = entry_local_ray(S, e, world_ray);
-    SrtPrim pr = S.prims[h.prim];
+    DEntry e = load_entry_head(W.entries + h.entry);
+    Ray r = entry_local_ray<F>(W, e.first_op, e.op_count, world_ray);
+    DPrim pr = load_prim(W.dprims + h.prim);
     rec.material = pr.material;
-    switch (pr.type) {
-        case SRT_PRIM_SPHERE:
-        case SRT_PRIM_ENV_SPHERE: {
-            float4 s = __ldg(&S.spheres[pr.index]);
-            V3 c = v3(s.x, s.y, s.z);
-            rec.p = point_at(r, h.t);
-            V3 q = (rec.p - c) / s.w;
-            if (WANT_UV) get_sphere_uv(q, rec.u, rec.v);
-            rec.normal = pr.type == SRT_PRIM_SPHERE ? q : (c - rec.p) / s.w;
-            break;
-        }
-        case SRT_PRIM_MOVING_SPHERE: {
-            const float* m = S.msph + 9 * (size_t)pr.index;
-            rec.p = point_at(r, h.t);
-            rec.normal = (rec.p - msphere_center(m, r.time)) / m[8];
-            break;
-        }
-        case SRT_PRIM_XY_RECT:
-        case SRT_PRIM_XZ_RECT:
-        case SRT_PRIM_YZ_RECT: {
-            float4 q0 = __ldg(&S.rects[2 * pr.index]);
-            int aa = pr.type == SRT_PRIM_YZ_RECT ? 1 : 0;
-            int ab = pr.type == SRT_PRIM_XY_RECT ? 1 : 2;
+    int type = pr.type;
+    if (type >= SRT_PRIM_XY_RECT && type <= SRT_PRIM_YZ_RECT) {
+        int aa = type == SRT_PRIM_YZ_RECT ? 1 : 0;
+        int ab = type == SRT_PRIM_XY_RECT ? 1 : 2;
+        if (WANT_UV) {
             float a = xadd(comp(r.o, aa), xmul(h.t, comp(r.d, aa)));
             float b = xadd(comp(r.o, ab), xmul(h.t, comp(r.d, ab)));
-            rec.u = xdiv(xsub(a, q0.x), xsub(q0.y, q0.x));
-            rec.v = xdiv(xsub(b, q0.z), xsub(q0.w, q0.z));
-            rec.p = point_at(r, h.t);
-            rec.normal = pr.type == SRT_PRIM_XY_RECT ? v3(0.f, 0.f, 1.f)
-                                                     : (pr.type == SRT_PRIM_XZ_RECT ? v3(0.f, 1.f, 0.f) : v3(1.f, 0.f, 0.f));
-            break;
+            rec.u = xdiv(xsub(a, pr.g.x), xsub(pr.g.y, pr.g.x));
+            rec.v = xdiv(xsub(b, pr.g.z), xsub(pr.g.w, pr.g.z));
         }
-        case SRT_PRIM_TRIANGLE: {
-            const float* p = S.tri_pos + 9 * (size_t)pr.index;
-            const float* n = S.tri_nrm + 9 * (size_t)pr.index;
-            const float* uv = S.tri_uv + 6 * (size_t)pr.index;
-            V3 p0 = v3(p), p1 = v3(p + 3), p2 = v3(p + 6);
-            float t, u = 0.f, v = 0.f;
-            // a hit found through a medium boundary may be the back-face variant
-            tri_hit(p0, p1, p2, r, true, t, u, v);
-            float w = xsub(xsub(1.0f, u), v);
+        rec.p = point_at(r, h.t);
+        rec.normal = type == SRT_PRIM_XY_RECT ? v3(0.f, 0.f, 1.f)
+                                              : (type == SRT_PRIM_XZ_RECT ? v3(0.f, 1.f, 0.f) : v3(1.f, 0.f, 0.f));
+    } else if (type == SRT_PRIM_SPHERE || ((F & F_ENV) && type == SRT_PRIM_ENV_SPHERE)) {
+        V3 c = v3(pr.g.x, pr.g.y, pr.g.z);
+        rec.p = point_at(r, h.t);
+        V3 qn = (rec.p - c) / pr.g.w;
+        if (WANT_UV) get_sphere_uv(qn, rec.u, rec.v);
+        rec.normal = type == SRT_PRIM_SPHERE ? qn : (c - rec.p) / pr.g.w;
+    } else if ((F & (F_TRI | F_BVH_TRI)) && type == SRT_PRIM_TRIANGLE) {
+        size_t row = pr.flags_aux >> 1;
+        const float* p = S.tri_pos + 9 * row;
+        const float* n = S.tri_nrm + 9 * row;
+        V3 p0 = v3(p), p1 = v3(p + 3), p2 = v3(p + 6);
+        float t, u = 0.f, v = 0.f;
+        // a hit found through a medium boundary may be the back-face variant
+        tri_hit(p0, p1, p2, r.o, tri_dir(r), true, t, u, v);
+        float w = xsub(xsub(1.0f, u), v);
+        if (WANT_UV) {
+            const float* uv = S.tri_uv + 6 * row;
             rec.u = xadd(xadd(xmul(w, uv[0]), xmul(u, uv[2])), xmul(v, uv[4]));
             rec.v = xadd(xadd(xmul(w, uv[1]), xmul(u, uv[3])), xmul(v, uv[5]));
-            rec.normal = unit_vector(w * v3(n) + u * v3(n + 3) + v * v3(n + 6));  // FLAT_NORMAL 1, triangle.h:179-183
-            rec.p = w * p0 + u * p1 + v * p2;
-            break;
         }
-        default:
-            rec.p = point_at(r, h.t);
-            rec.normal = v3(0.f, 0.f, 0.f);
-            break;
+        rec.normal = unit_vector(w * v3(n) + u * v3(n + 3) + v * v3(n + 6));  // FLAT_NORMAL 1, triangle.h:179-183
+        rec.p = w * p0 + u * p1 + v * p2;
+    } else if ((F & F_MSPHERE) && type == SRT_PRIM_MOVING_SPHERE) {
+        const float* m = S.msph + 9 * (size_t)(pr.flags_aux >> 1);
+        rec.p = point_at(r, h.t);
+        rec.normal = (rec.p - msphere_center(m, r.time)) / m[8];
+    } else {
+        rec.p = point_at(r, h.t);
+        rec.normal = v3(0.f, 0.f, 0.f);
     }
-    if (pr.flags & SRT_PRIM_FLIP) rec.normal = -rec.normal;
-    for (int i = e.op_count - 1; i >= 0; i--) xform_rec_out(S.ops[e.first_op + i], rec.p, rec.normal);
+    if (pr.flags_aux & SRT_PRIM_FLIP) rec.normal = -rec.normal;
+    if (F & F_XFORM)
+        for (int i = e.op_count - 1; i >= 0; i--) xform_rec_out(load_op(W.ops + e.first_op + i), rec.p, rec.normal);
     return rec;
 }
 

@@ -1,4 +1,4 @@
-// srt_kernels.cuh — the __global__ entry points.
+// srt_kernels.cuh — the render kernel (one instantiation per variant, srt_render_variant.cu).
 #ifndef SRT_KERNELS_CUH
 #define SRT_KERNELS_CUH
 
@@ -12,106 +12,156 @@ struct RenderArgs {
     int max_depth;
     uint32_t seed;
     int mod_ny;           // SRT_COMPAT_PIXEL_MOD_NY
-    int lanes_per_pixel;  // power of two <= 32
-    int n_tiles;          // warp tiles of 32 / lanes_per_pixel pixels
+    int chunk;            // Sobol indices per work item
+    int n_chunks;         // work items per pixel
+    unsigned n_items;     // n_pixels * n_chunks
+    int regen_threshold;  // idle lanes in a warp that trigger a regeneration phase
+    int grab;             // work items a warp takes from the global counter at a time
 };
 
-// Closest hit for a batch of rays: world->hit(r, 0.001, FLT_MAX, rec) (Raytracing_n.cpp:58).
-__global__ void __launch_bounds__(128) k_trace_closest(DScene S, const float* __restrict__ rays, long long n,
-                                                       int32_t* __restrict__ prim, float* __restrict__ t,
-                                                       float* __restrict__ rec, uint32_t seed) {
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float* q = rays + 7 * i;
-    Ray r{v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), q[6]};
-    Philox rng;
-    philox_init(rng, seed, (uint32_t)i, (uint32_t)(i >> 32));
-    Tally<false> tl{nullptr};
-    Hit h = world_hit(S, r, 0.001f, kFltMax, rng, tl);
-    if (h.prim < 0) {
-        prim[i] = -1;
-        t[i] = 0.f;
-        if (rec)
-            for (int k = 0; k < 8; k++) rec[8 * i + k] = 0.f;
-        return;
-    }
-    prim[i] = h.prim;
-    t[i] = h.t;
-    if (rec) {
-        HitRecord hr = make_record<true>(S, r, h);
-        float* o = rec + 8 * i;
-        o[0] = hr.u;
-        o[1] = hr.v;
-        o[2] = hr.p.x;
-        o[3] = hr.p.y;
-        o[4] = hr.p.z;
-        o[5] = hr.normal.x;
-        o[6] = hr.normal.y;
-        o[7] = hr.normal.z;
-    }
-}
+constexpr int kRenderThreads = 256;
 
-// hitable_list::pdf_value over the light list (hitable_list.h:54-62) for (origin, direction) pairs.
-__global__ void __launch_bounds__(128) k_light_pdf(DScene S, const float* __restrict__ od, long long n,
-                                                   float* __restrict__ out) {
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const float* q = od + 6 * i;
-    Tally<false> tl{nullptr};
-    out[i] = S.n_lights > 0 ? light_pdf_value(S, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), tl) : 0.f;
-}
+SRT_DEV View global_view(const DScene& S) { return View{S, S.entries, S.ops, S.dprims, S.lights}; }
 
-// The sample loop of renderthread (Raytracing_n.cpp:826-848) for every pixel, as a persistent grid:
-// each warp takes tiles of 32 / L consecutive pixels; the L lanes of a pixel split its Sobol
-// indices [s_begin, s_end) (lane l takes s_begin + l, + L, ...), so a warp's primary rays are
-// nearly identical (coherent traversal) and a pixel's sum is reduced by a fixed shuffle tree:
-// bit-reproducible, no atomics.  accum[curpixel] += sum of de_nan(color(...)).
-template <bool COUNT>
-__global__ void __launch_bounds__(256) k_render(DScene S, RenderArgs A, const uint32_t* __restrict__ sobol,
-                                               float* __restrict__ accum, unsigned long long* __restrict__ counters) {
+// The sample loop of renderthread (Raytracing_n.cpp:826-848) and color() (:55-106) for every pixel,
+// as a persistent grid of autonomous warps:
+//
+//   * a WORK ITEM is `chunk` consecutive Sobol indices of one pixel; items are numbered pixel-major
+//     (item = pixel * n_chunks + c) and handed out in increasing order, `grab` at a time per warp
+//     from one global counter, so the lanes of a warp work on neighbouring pixels;
+//   * every lane owns one item and one path at a time.  A warp iteration traces ONE ray and shades
+//     ONE bounce for all its live paths; lanes whose path ended wait until `regen_threshold` lanes are
+//     idle, then all of them start their next path together (or fetch their next item with one
+//     ballot / popc rank — no atomics inside the warp);
+//   * a finished item writes its radiance sum to its own slot — out[(c * n_pixels + pixel) * 3] —
+//     so the image is bit-reproducible: no float atomics, one writer per address;
+//     k_sum_partials then adds the n_chunks slots of a pixel in fixed order into the caller's
+//     accumulation buffer (with n_chunks == 1 the kernel adds into it directly).
+//
+// The hot tables of the scene (entries, instance ops, primitive records, lights) are staged into
+// shared memory when the variant has F_SMEM_TABLES: every lane of a warp reads the same record at
+// the same time, which is a broadcast from shared memory.
+template <uint32_t F, bool COUNT>
+__global__ void __launch_bounds__(kRenderThreads, 2)
+    k_render(DScene S, RenderArgs A, const uint32_t* __restrict__ sobol, float* __restrict__ out,
+             unsigned long long* __restrict__ counters) {
+    extern __shared__ float4 smem_hot[];
+    const DEntry* entries = S.entries;
+    const SrtXformOp* ops = S.ops;
+    const DPrim* dprims = S.dprims;
+    const DPrim* lights = S.lights;
+    if (F & F_SMEM_TABLES) {
+        const float4* src = reinterpret_cast<const float4*>(S.entries);
+        const unsigned n16 = S.hot_bytes >> 4;
+        for (unsigned i = threadIdx.x; i < n16; i += blockDim.x) smem_hot[i] = __ldg(src + i);
+        __syncthreads();
+        const char* base = reinterpret_cast<const char*>(smem_hot);
+        const char* g0 = reinterpret_cast<const char*>(S.entries);
+        entries = reinterpret_cast<const DEntry*>(base);
+        ops = reinterpret_cast<const SrtXformOp*>(base + (reinterpret_cast<const char*>(S.ops) - g0));
+        dprims = reinterpret_cast<const DPrim*>(base + (reinterpret_cast<const char*>(S.dprims) - g0));
+        lights = reinterpret_cast<const DPrim*>(base + (reinterpret_cast<const char*>(S.lights) - g0));
+    }
+    View W{S, entries, ops, dprims, lights};
+
+    const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    const int warps_per_block = blockDim.x >> 5;
-    const int warp_global = blockIdx.x * warps_per_block + (threadIdx.x >> 5);
-    const int total_warps = gridDim.x * warps_per_block;
-    const int L = A.lanes_per_pixel;
-    const int ppw = 32 / L;
+    const unsigned lt_mask = (1u << lane) - 1u;
     const int n_pixels = A.nx * A.ny;
+    unsigned long long* work_counter = counters + 7;
+
     Counters cnt = {0, 0, 0, 0, 0, 0};
     Tally<COUNT> tl{&cnt};
     unsigned long long paths = 0;
 
-    for (int tile = warp_global; tile < A.n_tiles; tile += total_warps) {
-        int pixel = tile * ppw + lane / L;
-        int sl = lane % L;
-        V3 col = v3(0.f, 0.f, 0.f);
-        if (pixel < n_pixels) {
-            int i = pixel % (A.mod_ny ? A.ny : A.nx);  // Raytracing_n.cpp:827-828
-            int j = A.ny - 1 - (pixel / A.nx);
-            for (int s = A.s_begin + sl; s < A.s_end; s += L) {
-                // float u = float(samplepoints[s][0] + i) / float(nx)   (Raytracing_n.cpp:834-835)
+    // per-lane item and path state
+    bool has_item = false, alive = false;
+    int pixel = 0, chunk_id = 0, s_next = 0, s_stop = 0;
+    V3 sum = v3(0.f, 0.f, 0.f);
+    Path P;
+    P.depth = 0;
+    Philox rng;
+    // warp-uniform range of items
+    unsigned w_cur = 0, w_end = 0;
+    bool exhausted = false;
+
+    for (;;) {
+        unsigned dead = __ballot_sync(FULL, !alive);
+        if (dead == FULL || __popc(dead) >= A.regen_threshold) {
+            // ---- regeneration phase ---------------------------------------------------------------
+            bool item_done = !alive && has_item && s_next >= s_stop;
+            if (item_done) {
+                float* o = out + 3 * ((size_t)chunk_id * n_pixels + pixel);
+                if (A.n_chunks == 1) {
+                    o[0] += sum.x;
+                    o[1] += sum.y;
+                    o[2] += sum.z;
+                } else {
+                    o[0] = sum.x;
+                    o[1] = sum.y;
+                    o[2] = sum.z;
+                }
+                has_item = false;
+            }
+            bool need_item = !alive && !has_item;
+            unsigned m = __ballot_sync(FULL, need_item);
+            if (m) {
+                if (w_cur == w_end && !exhausted) {
+                    unsigned base = 0;
+                    if (lane == 0) base = (unsigned)atomicAdd(work_counter, (unsigned long long)A.grab);
+                    base = __shfl_sync(FULL, base, 0);
+                    if (base >= A.n_items) {
+                        exhausted = true;
+                    } else {
+                        w_cur = base;
+                        w_end = min(base + (unsigned)A.grab, A.n_items);
+                    }
+                }
+                unsigned avail = w_end - w_cur;
+                unsigned rank = __popc(m & lt_mask);
+                if (need_item && rank < avail) {
+                    unsigned item = w_cur + rank;
+                    pixel = (int)(item / (unsigned)A.n_chunks);
+                    chunk_id = (int)(item - (unsigned)pixel * (unsigned)A.n_chunks);
+                    s_next = A.s_begin + chunk_id * A.chunk;
+                    s_stop = min(s_next + A.chunk, A.s_end);
+                    sum = v3(0.f, 0.f, 0.f);
+                    has_item = true;
+                }
+                w_cur += min((unsigned)__popc(m), avail);
+            }
+            if (!alive && has_item && s_next < s_stop) {
+                // float u = float(samplepoints[s][0] + i) / float(nx)   (Raytracing_n.cpp:827-836)
+                int i = pixel % (A.mod_ny ? A.ny : A.nx);
+                int j = A.ny - 1 - (pixel / A.nx);
+                int s = s_next++;
                 double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
                 double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
                 float u = xdiv((float)(sx + (double)i), (float)A.nx);
                 float v = xdiv((float)(sy + (double)j), (float)A.ny);
-                Philox rng;
                 philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-                Ray r = camera_get_ray(S.camera, u, v, rng);
-                V3 c = de_nan(trace_path(S, r, A.max_depth, rng, tl));
-                col = col + c;
+                P.r = camera_get_ray(S.camera, u, v, rng);
+                P.thr = v3(1.f, 1.f, 1.f);
+                P.L = v3(0.f, 0.f, 0.f);
+                P.depth = 0;
+                alive = true;
                 if (COUNT) paths++;
             }
+            if (!__any_sync(FULL, alive)) {
+                bool pending = __any_sync(FULL, has_item);
+                if (!pending && exhausted && w_cur == w_end) break;
+                continue;
+            }
         }
-        // fixed-order tree over the L lanes of the pixel
-        for (int off = L >> 1; off > 0; off >>= 1) {
-            col.x = xadd(col.x, __shfl_down_sync(0xffffffffu, col.x, off));
-            col.y = xadd(col.y, __shfl_down_sync(0xffffffffu, col.y, off));
-            col.z = xadd(col.z, __shfl_down_sync(0xffffffffu, col.z, off));
-        }
-        if (sl == 0 && pixel < n_pixels) {
-            float* a = accum + 3 * (size_t)pixel;
-            a[0] = xadd(a[0], col.x);
-            a[1] = xadd(a[1], col.y);
-            a[2] = xadd(a[2], col.z);
+        // ---- one ray + one bounce for every live path ---------------------------------------------
+        if (alive) {
+            if (COUNT) cnt.rays++;
+            Hit h = world_hit<F>(W, P.r, 0.001f, kFltMax, rng, tl);
+            if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
+                V3 c = de_nan(P.L);  // col += de_nan(color(...)), Raytracing_n.cpp:841
+                sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
+                alive = false;
+            }
         }
     }
     if (COUNT) {
@@ -123,28 +173,6 @@ __global__ void __launch_bounds__(256) k_render(DScene S, RenderArgs A, const ui
         atomicAdd(&counters[5], cnt.reject_iters);
         atomicAdd(&counters[6], cnt.culled_rays);
     }
-}
-
-// mean -> sqrt -> int(255.99 c) -> clamp (Raytracing_n.cpp:848-862)
-__global__ void __launch_bounds__(256) k_resolve(const float* __restrict__ accum, long long n_values, float ns,
-                                                 uint8_t* __restrict__ out) {
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n_values) return;
-    float k = (float)(1.0 / (double)ns);  // vec3::operator/=(float): k = 1.0 / t, then e *= k
-    float c = xmul(accum[i], k);
-    c = xsqrt(c);
-    int v = (int)(255.99 * (double)c);
-    v = v > 255 ? 255 : v;
-    v = v < 0 ? 0 : v;
-    out[i] = (uint8_t)v;
-}
-
-__global__ void k_merl_lookup(const double* __restrict__ table, const double* __restrict__ angles, long long n,
-                              double* __restrict__ rgb) {
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    const double* a = angles + 4 * i;
-    merl_lookup(table, a[0], a[1], a[2], a[3], rgb + 3 * i);
 }
 
 }  // namespace srt

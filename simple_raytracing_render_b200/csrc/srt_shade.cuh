@@ -1,6 +1,13 @@
-// srt_shade.cuh — textures, materials, light sampling and the path loop: color() of the reference
-// (Raytracing_n.cpp:55-106) restated as an iteration, with the reference's sampling semantics
-//  kept as they are, quirks included.
+// srt_shade.cuh — textures, materials, light sampling and one bounce of color() (the reference's
+// Raytracing_n.cpp:55-106), with the reference's sampling semantics kept as
+// they are, quirks included.
+//
+// Numerics: nothing in this file decides WHICH primitive a ray hits or its t, and the image gate is
+// statistical (relMSE against the reference's converged render), so shading uses fused / fast float
+// arithmetic (namespace fm) and float constants where the reference promotes to double.  What is kept
+// exactly is the STRUCTURE: which random numbers are drawn in which branch, the mixture density, the
+// wrong-hemisphere cosine generator and the `while (pdf_val == 0)` rejection loop, one-sided
+// emission, the specular branch that drops `emitted`, de_nan.
 #ifndef SRT_SHADE_CUH
 #define SRT_SHADE_CUH
 
@@ -38,26 +45,27 @@ SRT_DEV float perlin_turb(const DScene& S, V3 p) {  // perlin.h:48-58, depth 7
     for (int i = 0; i < 7; i++) {
         accum += weight * perlin_noise(S, p);
         weight *= 0.5f;
-        p = p * 2.f;
+        p = fm::scale(p, 2.f);
     }
     return fabsf(accum);
 }
 
+template <uint32_t F>
 SRT_DEV V3 texture_value(const DScene& S, int tex, float u, float v, V3 p) {
     for (int guard = 0; guard < 16 && tex >= 0; guard++) {
         SrtTexture t = S.textures[tex];
         if (t.type == SRT_TEX_CONSTANT) return v3(t.c[0], t.c[1], t.c[2]);  // texture.h:29-31
-        if (t.type == SRT_TEX_CHECKER) {                                     // texture.h:13-19
+        if ((F & F_TEX_CHECKER) && t.type == SRT_TEX_CHECKER) {              // texture.h:13-19
             float sines = sinf(10.f * p.x) * sinf(10.f * p.y) * sinf(10.f * p.z);
             tex = sines < 0.f ? t.b : t.a;
             continue;
         }
-        if (t.type == SRT_TEX_NOISE) {  // texture.h:39-43
+        if ((F & F_TEX_NOISE) && t.type == SRT_TEX_NOISE) {  // texture.h:39-43
             float s = t.c[0];
-            float val = (float)(0.5 * (1.0 + (double)sinf(s * p.z + 5.f * perlin_turb(S, s * p))));
+            float val = 0.5f * (1.0f + sinf(s * p.z + 5.f * perlin_turb(S, fm::scale(p, s))));
             return v3(val, val, val);
         }
-        if (t.type == SRT_TEX_IMAGE) {  // texture.h:58-70: nearest texel, v flipped, 3 channels
+        if ((F & F_TEX_IMAGE) && t.type == SRT_TEX_IMAGE) {  // texture.h:58-70: nearest texel, v flipped, 3 channels
             DImage im = S.images[t.a];
             int i = (int)(u * (float)im.nx);
             int j = (int)((double)((1.f - v) * (float)im.ny) - 0.001);
@@ -66,150 +74,175 @@ SRT_DEV V3 texture_value(const DScene& S, int tex, float u, float v, V3 p) {
             if (i > im.nx - 1) i = im.nx - 1;
             if (j > im.ny - 1) j = im.ny - 1;
             const uint8_t* px = im.data + 3 * (size_t)i + 3 * (size_t)im.nx * j;
-            return v3((float)(px[0] / 255.0), (float)(px[1] / 255.0), (float)(px[2] / 255.0));
+            const float k = 1.0f / 255.0f;
+            return v3((float)px[0] * k, (float)px[1] * k, (float)px[2] * k);
         }
         break;
     }
     return v3(0.f, 0.f, 0.f);
 }
 
-SRT_DEV bool material_needs_uv(const DScene& S, int mat) {
-    if (mat < 0) return false;
-    int tex = S.materials[mat].texture;
-    if (tex < 0) return false;
-    int ty = S.textures[tex].type;
-    return ty == SRT_TEX_IMAGE || ty == SRT_TEX_CHECKER;  // a checker may hold an image
+// albedo / emission of a material at a hit: the constant-texture case is folded into DMaterial
+template <uint32_t F>
+SRT_DEV V3 material_color(const DScene& S, const DMaterial& m, const HitRecord& rec) {
+    if (m.tex_type == SRT_TEX_CONSTANT) return v3(m.c[0], m.c[1], m.c[2]);
+    if (F & (F_TEX_CHECKER | F_TEX_NOISE | F_TEX_IMAGE)) return texture_value<F>(S, m.texture, rec.u, rec.v, rec.p);
+    return v3(0.f, 0.f, 0.f);
+}
+
+template <uint32_t F>
+SRT_DEV bool material_needs_uv(const DMaterial& m) {
+    // a checker may hold an image (texture.h:9-23)
+    return (F & F_TEX_IMAGE) && (m.tex_type == SRT_TEX_IMAGE || m.tex_type == SRT_TEX_CHECKER);
+}
+
+SRT_DEV DMaterial load_material(const DMaterial* p) {
+    const float4* q = reinterpret_cast<const float4*>(p);
+    float4 a = __ldg(q), b = __ldg(q + 1), c = __ldg(q + 2);
+    DMaterial m;
+    m.type = __float_as_int(a.x);
+    m.texture = __float_as_int(a.y);
+    m.tex_type = __float_as_int(a.z);
+    m._pad = 0;
+    m.p[0] = b.x;
+    m.p[1] = b.y;
+    m.p[2] = b.z;
+    m.p[3] = b.w;
+    m.c[0] = c.x;
+    m.c[1] = c.y;
+    m.c[2] = c.z;
+    m._pad2 = 0.f;
+    return m;
 }
 
 // ---- random helpers (material.h:43-50, camera.h:8-14, pdf.h:10-18, sphere.h:7-15) ----------------
 SRT_DEV V3 random_in_unit_sphere(Philox& rng) {
     V3 p;
     do {
-        p = 2.0f * v3(rand_f(rng), rand_f(rng), rand_f(rng)) - v3(1.f, 1.f, 1.f);
-    } while (dot(p, p) >= 1.0f);
+        p = v3(2.0f * rand_f(rng) - 1.f, 2.0f * rand_f(rng) - 1.f, 2.0f * rand_f(rng) - 1.f);
+    } while (fm::dot(p, p) >= 1.0f);
     return p;
 }
 
 SRT_DEV V3 random_cosine_direction(Philox& rng) {  // pdf.h:10-18, the `2 *` on x, y included
     float r1 = rand_f(rng), r2 = rand_f(rng);
-    float phi = (float)(2.0 * kPi * (double)r1);
     float z = sqrtf(1.f - r2);
     float sn, cs;
-    sincosf(phi, &sn, &cs);
-    float sq = sqrtf(r2);
-    return v3(cs * 2.f * sq, sn * 2.f * sq, z);
+    __sincosf(fm::kTwoPi * r1, &sn, &cs);
+    float sq = 2.f * sqrtf(r2);
+    return v3(cs * sq, sn * sq, z);
 }
 
 SRT_DEV V3 random_to_sphere(float radius, float distance_squared, Philox& rng) {
     float r1 = rand_f(rng), r2 = rand_f(rng);
     float z = 1.f + r2 * (sqrtf(1.f - radius * radius / distance_squared) - 1.f);
-    float phi = (float)(2.0 * kPi * (double)r1);
     float sn, cs;
-    sincosf(phi, &sn, &cs);
+    __sincosf(fm::kTwoPi * r1, &sn, &cs);
     float s = sqrtf(1.f - z * z);
     return v3(cs * s, sn * s, z);
 }
 
-// ---- light list: hitable_list::random / pdf_value over hlist (hitable_list.h:54-67) ----------------
-SRT_DEV V3 light_random(const DScene& S, V3 o, Philox& rng) {
-    int index = (int)(rand_d(rng) * (double)S.n_lights);
-    if (index >= S.n_lights) index = S.n_lights - 1;  // drand48 < 1 always; guard only
-    SrtLight L = S.lights[index];
-    switch (L.type) {
-        case SRT_PRIM_XZ_RECT: {  // aarect.h:57-60
-            float4 q = __ldg(&S.rects[2 * L.index]);
-            float k = __ldg(&S.rects[2 * L.index + 1]).x;
-            float x = (float)((double)q.x + rand_d(rng) * (double)xsub(q.y, q.x));
-            float z = (float)((double)q.z + rand_d(rng) * (double)xsub(q.w, q.z));
-            return v3(x, k, z) - o;
-        }
-        case SRT_PRIM_SPHERE: {  // sphere.h:80-86
-            float4 s = __ldg(&S.spheres[L.index]);
-            V3 direction = v3(s.x, s.y, s.z) - o;
-            float d2 = dot(direction, direction);
-            Onb uvw = onb_from_w(direction);
-            return onb_local(uvw, random_to_sphere(s.w, d2, rng));
-        }
-        case SRT_PRIM_ENV_SPHERE: {  // env_sphere.h:40-46
-            float4 s = __ldg(&S.spheres[L.index]);
-            V3 direction = o - v3(s.x, s.y, s.z);
-            float d2 = dot(direction, direction);
-            Onb uvw = onb_from_w(direction);
-            return onb_local(uvw, random_to_sphere(s.w, d2, rng));
-        }
-        case SRT_PRIM_TRIANGLE: {  // triangle.h:89-94
-            const float* p = S.tri_pos + 9 * (size_t)L.index;
-            float u = rand_f(rng);
-            float v = (float)(rand_d(rng) * (double)(1.f - u));
-            V3 pt = v3(p) * (1.f - u - v) + v3(p + 3) * u + v3(p + 6) * v;
-            return pt - o;
-        }
-        default:
-            return v3(1.f, 0.f, 0.f);  // hitable.h:32
-    }
+// onb.h:21-30 in fast arithmetic (shading frames only)
+SRT_DEV Onb onb_fast(V3 n) {
+    Onb b;
+    b.w = fm::normalize(n);
+    V3 a = fabsf(b.w.x) > 0.9f ? v3(0.f, 1.f, 0.f) : v3(1.f, 0.f, 0.f);
+    b.v = fm::normalize(fm::cross(b.w, a));
+    b.u = fm::cross(b.w, b.v);
+    return b;
+}
+SRT_DEV V3 onb_local_fast(const Onb& b, V3 a) {
+    return fm::madd(b.u, a.x, fm::madd(b.v, a.y, fm::scale(b.w, a.z)));
 }
 
-template <bool COUNT>
-SRT_DEV float light_pdf_value(const DScene& S, V3 o, V3 v, Tally<COUNT> tl) {
-    float weight = (float)(1.0 / (double)S.n_lights);
+// ---- light list: hitable_list::random / pdf_value over hlist (hitable_list.h:54-67) ----------------
+template <uint32_t F>
+SRT_DEV V3 light_random(const View& W, V3 o, Philox& rng) {
+    const DScene& S = W.S;
+    int index = 0;
+    float pick = rand_f(rng);  // hitable_list.h:65: int(drand48() * list_size), drawn even for one light
+    if (S.n_lights > 1) {
+        index = (int)(pick * (float)S.n_lights);
+        if (index >= S.n_lights) index = S.n_lights - 1;
+    }
+    DPrim pr = load_prim(W.lights + index);
+    if (pr.type == SRT_PRIM_XZ_RECT) {  // aarect.h:57-60
+        float x = fmaf(rand_f(rng), pr.g.y - pr.g.x, pr.g.x);
+        float z = fmaf(rand_f(rng), pr.g.w - pr.g.z, pr.g.z);
+        return fm::sub(v3(x, pr.k, z), o);
+    }
+    if ((F & (F_LIGHT_SPHERE | F_LIGHT_ENV)) && (pr.type == SRT_PRIM_SPHERE || pr.type == SRT_PRIM_ENV_SPHERE)) {
+        // sphere.h:80-86 / env_sphere.h:40-46 (direction = o - center for the env sphere)
+        V3 c = v3(pr.g.x, pr.g.y, pr.g.z);
+        V3 direction = pr.type == SRT_PRIM_SPHERE ? fm::sub(c, o) : fm::sub(o, c);
+        float d2 = fm::dot(direction, direction);
+        Onb uvw = onb_fast(direction);
+        return onb_local_fast(uvw, random_to_sphere(pr.g.w, d2, rng));
+    }
+    if ((F & F_LIGHT_TRI) && pr.type == SRT_PRIM_TRIANGLE) {  // triangle.h:89-94
+        const float* p = S.tri_pos + 9 * (size_t)(pr.flags_aux >> 1);
+        float u = rand_f(rng);
+        float v = rand_f(rng) * (1.f - u);
+        V3 pt = fm::madd(v3(p), 1.f - u - v, fm::madd(v3(p + 3), u, fm::scale(v3(p + 6), v)));
+        return fm::sub(pt, o);
+    }
+    return v3(1.f, 0.f, 0.f);  // hitable.h:32
+}
+
+// hitable_pdf::value -> hitable_list::pdf_value (pdf.h:162-164, hitable_list.h:54-62): each light
+// shape re-intersects the ray (o, v) with (0.001, FLT_MAX) — these ARE hit tests of the reference
+// shapes and use the exact routines, so that srt_light_pdf reproduces the reference's zero / non-zero
+// pattern bit for bit; the density arithmetic after the hit is in fast float.
+template <uint32_t F, bool COUNT>
+SRT_DEV float light_pdf_value(const View& W, V3 o, V3 v, Tally<COUNT> tl) {
+    const DScene& S = W.S;
+    float weight = 1.0f / (float)S.n_lights;
     float sum = 0.f;
-    Ray r{o, v, 0.f};
+    RayK q = make_rayk(Ray{o, v, 0.f});
     for (int i = 0; i < S.n_lights; i++) {
-        SrtLight L = S.lights[i];
+        DPrim pr = load_prim(W.lights + i);
         float pdf = 0.f;
         if (COUNT) tl.c->probe_rays++;
-        switch (L.type) {
-            case SRT_PRIM_XZ_RECT: {  // aarect.h:45-55
-                float4 q = __ldg(&S.rects[2 * L.index]);
-                float k = __ldg(&S.rects[2 * L.index + 1]).x;
-                float t, a, b;
-                if (rect_hit(SRT_PRIM_XZ_RECT, q, k, r, 0.001f, kFltMax, t, a, b)) {
-                    float area = xmul(xsub(q.y, q.x), xsub(q.w, q.z));
-                    float distance_square = xmul(xmul(t, t), dot(v, v));
-                    float cosine = fabsf(xdiv(v.y, length(v)));  // dot(v, (0,1,0)) / |v|
-                    pdf = xdiv(distance_square, xmul(cosine, area));
-                }
-                break;
+        if (pr.type == SRT_PRIM_XZ_RECT) {  // aarect.h:45-55
+            float t;
+            if (rect_hit_axes<1, 0, 2>(pr.g, pr.k, q, 0.001f, kFltMax, t)) {
+                float area = (pr.g.y - pr.g.x) * (pr.g.w - pr.g.z);
+                float vv = q.a;  // v.squared_length()
+                float distance_square = t * t * vv;
+                float cosine = fabsf(v.y) * rsqrtf(vv);  // |dot(v, (0,1,0))| / |v|
+                pdf = distance_square / (cosine * area);
             }
-            case SRT_PRIM_SPHERE: {  // sphere.h:69-78
-                float4 s = __ldg(&S.spheres[L.index]);
-                V3 c = v3(s.x, s.y, s.z);
-                float t;
-                if (sphere_hit(c, s.w, r, 0.001f, kFltMax, t)) {
-                    V3 co = c - o;
-                    float cos_theta_max = xsqrt(xsub(1.f, xdiv(xmul(s.w, s.w), dot(co, co))));
-                    float solid_angle = (float)(2.0 * kPi * (double)xsub(1.f, cos_theta_max));
-                    pdf = xdiv(1.f, solid_angle);
-                }
-                break;
+        } else if ((F & F_LIGHT_SPHERE) && pr.type == SRT_PRIM_SPHERE) {  // sphere.h:69-78
+            V3 c = v3(pr.g.x, pr.g.y, pr.g.z);
+            float t;
+            if (sphere_hit(c, pr.g.w, q, 0.001f, kFltMax, t)) {
+                V3 co = fm::sub(c, o);
+                float cos_theta_max = sqrtf(1.f - pr.g.w * pr.g.w / fm::dot(co, co));
+                float solid_angle = fm::kTwoPi * (1.f - cos_theta_max);
+                pdf = 1.f / solid_angle;
             }
-            case SRT_PRIM_ENV_SPHERE:
-                pdf = 1.f;  // env_sphere.h:48-50
-                break;
-            case SRT_PRIM_TRIANGLE: {  // triangle.h:70-87
-                const float* p = S.tri_pos + 9 * (size_t)L.index;
-                const float* n = S.tri_nrm + 9 * (size_t)L.index;
-                V3 p0 = v3(p), p1 = v3(p + 3), p2 = v3(p + 6);
-                float t, uu, vv;
-                if (tri_hit(p0, p1, p2, r, false, t, uu, vv)) {
-                    float w = xsub(xsub(1.f, uu), vv);
-                    V3 nrm = unit_vector(w * v3(n) + uu * v3(n + 3) + vv * v3(n + 6));
-                    V3 v01 = p1 - p0, v02 = p2 - p0;
-                    V3 v01n = v01 / length(v01), v02n = v02 / length(v02);
-                    float cos102 = dot(v01n, v02n);
-                    float sin102 = xsqrt(xsub(1.f, xmul(cos102, cos102)));
-                    float h = xmul(length(v02), sin102);
-                    float area = (float)(0.5 * (double)length(v01) * (double)h);
-                    float distance_square = xmul(xmul(t, t), dot(v, v));
-                    float cosine = xdiv(fabsf(dot(v, nrm)), length(v));
-                    pdf = xdiv(distance_square, xmul(cosine, area));
-                }
-                break;
+        } else if ((F & F_LIGHT_ENV) && pr.type == SRT_PRIM_ENV_SPHERE) {
+            pdf = 1.f;  // env_sphere.h:48-50
+        } else if ((F & F_LIGHT_TRI) && pr.type == SRT_PRIM_TRIANGLE) {  // triangle.h:70-87
+            size_t row = pr.flags_aux >> 1;
+            const float* p = S.tri_pos + 9 * row;
+            const float* n = S.tri_nrm + 9 * row;
+            V3 p0 = v3(p), p1 = v3(p + 3), p2 = v3(p + 6);
+            float t, uu, vv;
+            if (tri_hit(p0, p1, p2, o, tri_dir(q.r), false, t, uu, vv)) {
+                float w = 1.f - uu - vv;
+                V3 nrm = fm::normalize(fm::madd(v3(n), w, fm::madd(v3(n + 3), uu, fm::scale(v3(n + 6), vv))));
+                V3 v01 = fm::sub(p1, p0), v02 = fm::sub(p2, p0);
+                float l01 = fm::length(v01), l02 = fm::length(v02);
+                float cos102 = fm::dot(v01, v02) / (l01 * l02);
+                float sin102 = sqrtf(1.f - cos102 * cos102);
+                float area = 0.5f * l01 * l02 * sin102;
+                float distance_square = t * t * q.a;
+                float cosine = fabsf(fm::dot(v, nrm)) * rsqrtf(q.a);
+                pdf = distance_square / (cosine * area);
             }
-            default:
-                pdf = 0.f;
         }
-        sum = xadd(sum, xmul(weight, pdf));
+        sum = fmaf(weight, pdf, sum);
     }
     return sum;
 }
@@ -223,19 +256,22 @@ struct BsdfPdf {
     float stash;  // beckmann_pdf::pdf_value (pdf.h:133-135, :145-150)
 };
 
+template <uint32_t F>
 SRT_DEV V3 bsdf_generate(BsdfPdf& P, V3 wo, Philox& rng) {
-    if (P.kind == SRT_MAT_BECKMANN) return beckmann_generate(P.uvw, P.a, P.b, wo, rng, P.stash);
+    if ((F & F_BECKMANN) && P.kind == SRT_MAT_BECKMANN) return beckmann_generate(P.uvw, P.a, P.b, wo, rng, P.stash);
     V3 g = random_cosine_direction(rng);  // pdf.h:47-56 / :103-112
-    if (dot(-wo, P.n) > 0.f) g.z = -g.z;
-    return onb_local(P.uvw, g);
+    if (fm::dot(wo, P.n) < 0.f) g.z = -g.z;  // dot(-wo, n) > 0: flipped INTO the surface
+    return onb_local_fast(P.uvw, g);
 }
 
+template <uint32_t F>
 SRT_DEV float bsdf_value(const BsdfPdf& P, V3 wo, V3 wi) {
-    if (P.kind == SRT_MAT_BECKMANN) return P.stash;
-    if (P.kind == SRT_MAT_ORENNAYAR) return orennayar_value(P.uvw, P.a, P.b, wo, wi);
-    float cosO = dot(unit_vector(wo), P.n);  // pdf.h:40-45
-    float cosI = dot(unit_vector(wi), P.n);
-    if (cosI * cosO < 0.f) return (float)((double)fabsf(cosI) / kPi);
+    if ((F & F_BECKMANN) && P.kind == SRT_MAT_BECKMANN) return P.stash;
+    if ((F & F_ORENNAYAR) && P.kind == SRT_MAT_ORENNAYAR) return orennayar_value(P.uvw, P.a, P.b, wo, wi);
+    // pdf.h:40-45: cosO = dot(unit(wo), n), cosI = dot(unit(wi), n); only signs and |cosI| matter
+    float dO = fm::dot(wo, P.n);
+    float dI = fm::dot(wi, P.n);
+    if (dI * dO < 0.f) return fabsf(dI) * fm::rlength(wi) * fm::kInvPi;
     return 0.f;
 }
 
@@ -243,15 +279,17 @@ SRT_DEV float bsdf_value(const BsdfPdf& P, V3 wo, V3 wi) {
 SRT_DEV float schlick(float cosine, float ref_idx) {  // material.h:14-19
     float r0 = (1.f - ref_idx) / (1.f + ref_idx);
     r0 = r0 * r0;
-    return r0 + (1.f - r0) * powf(1.f - cosine, 5.f);
+    float m = 1.f - cosine;
+    float m2 = m * m;
+    return r0 + (1.f - r0) * (m2 * m2 * m);
 }
-SRT_DEV V3 reflect(V3 v, V3 n) { return v - (2.f * dot(v, n)) * n; }  // material.h:34-36
-SRT_DEV bool refract(V3 v, V3 n, float ni_over_nt, V3& refracted) {    // material.h:21-32
-    V3 uv = unit_vector(v);
-    float dt = dot(uv, n);
-    float disc = (float)(1.0 - (double)(ni_over_nt * ni_over_nt * (1.f - dt * dt)));
+SRT_DEV V3 reflect(V3 v, V3 n) { return fm::madd(n, -2.f * fm::dot(v, n), v); }  // material.h:34-36
+SRT_DEV bool refract(V3 v, V3 n, float ni_over_nt, V3& refracted) {              // material.h:21-32
+    V3 uv = fm::normalize(v);
+    float dt = fm::dot(uv, n);
+    float disc = 1.0f - ni_over_nt * ni_over_nt * (1.f - dt * dt);
     if (disc > 0.f) {
-        refracted = ni_over_nt * (uv - n * dt) - n * sqrtf(disc);
+        refracted = fm::sub(fm::scale(fm::madd(n, -dt, uv), ni_over_nt), fm::scale(n, sqrtf(disc)));
         return true;
     }
     return false;
@@ -266,145 +304,153 @@ SRT_DEV V3 de_nan(V3 c) {  // Raytracing_n.cpp:47-53
 
 constexpr int kMaxRejectIters = 4096;  // the reference loop is unbounded (Raytracing_n.cpp:79-83)
 
-// color(r, world, light_shape, depth) — one path.  The recursion
+// State of one path between bounces.  color()'s recursion
 //     return emitted + attenuation * scattering_pdf * color(scattered) / pdf_val
-// unrolls to radiance = sum over vertices of (throughput so far) * emitted, with the terminal
-// `vec3(0)` of a miss kept as an explicit `throughput * 0` so that inf/NaN throughputs poison the
-// sample exactly as they do in the recursive form (de_nan then zeroes those channels).
-template <bool COUNT>
-SRT_DEV V3 trace_path(const DScene& S, Ray r, int max_depth, Philox& rng, Tally<COUNT> tl) {
-    V3 L = v3(0.f, 0.f, 0.f);
-    V3 thr = v3(1.f, 1.f, 1.f);
-    int depth = 0;
-    for (;;) {
-        if (COUNT) tl.c->rays++;
-        Hit h = world_hit(S, r, 0.001f, kFltMax, rng, tl);
-        if (h.prim < 0) {
-            L = L + thr * v3(0.f, 0.f, 0.f);
-            break;
-        }
-        HitRecord rec;
-        {
-            int mat_probe = h.prim >= S.n_prims ? -1 : S.prims[h.prim].material;
-            if (material_needs_uv(S, mat_probe))
-                rec = make_record<true>(S, r, h);
-            else
-                rec = make_record<false>(S, r, h);
-        }
-        if (rec.material < 0) break;  // no material: the reference would dereference null
-        SrtMaterial m = S.materials[rec.material];
-        V3 emitted = v3(0.f, 0.f, 0.f);
-        if (m.type == SRT_MAT_DIFFUSE_LIGHT) {  // material.h:348-354
-            if (dot(rec.normal, r.d) < 0.f) emitted = texture_value(S, m.texture, rec.u, rec.v, rec.p);
-            L = L + thr * emitted;  // scatter() returns false: color returns emitted
-            break;
-        }
-        if (!(depth < max_depth)) {
-            L = L + thr * emitted;
-            break;
-        }
-        // specular materials: return attenuation * color(specular_ray) (emitted is dropped)
-        if (m.type == SRT_MAT_METAL) {  // material.h:248-256
-            V3 reflected = reflect(unit_vector(r.d), rec.normal);
-            V3 dir = reflected + m.p[3] * random_in_unit_sphere(rng);
-            thr = thr * v3(m.p[0], m.p[1], m.p[2]);
-            r = Ray{rec.p, dir, 0.f};
-            depth++;
-            continue;
-        }
-        if (m.type == SRT_MAT_DIELECTRIC) {  // material.h:285-324
-            float ref_idx = m.p[0];
-            V3 outward_normal, refracted;
-            V3 reflected = reflect(r.d, rec.normal);
-            float ni_over_nt, cosine, reflect_prob;
-            float dn = dot(r.d, rec.normal);
-            if (dn > 0.f) {
-                outward_normal = -rec.normal;
-                ni_over_nt = ref_idx;
-                cosine = dn / length(r.d);
-            } else {
-                outward_normal = rec.normal;
-                ni_over_nt = (float)(1.0 / (double)ref_idx);
-                cosine = -dn / length(r.d);
-            }
-            if (refract(r.d, outward_normal, ni_over_nt, refracted))
-                reflect_prob = schlick(cosine, ref_idx);
-            else
-                reflect_prob = 1.0f;
-            V3 dir = (rand_d(rng) < (double)reflect_prob) ? reflected : refracted;
-            r = Ray{rec.p, dir, 0.f};
-            depth++;
-            continue;
-        }
-        if (m.type == SRT_MAT_ISOTROPIC) {  // material.h:362-367
-            V3 dir = random_in_unit_sphere(rng);
-            thr = thr * texture_value(S, m.texture, rec.u, rec.v, rec.p);
-            r = Ray{rec.p, dir, 0.f};
-            depth++;
-            continue;
-        }
-        // non-specular: lambertian, orennayar, beckmann, brdfmaterial
-        V3 attenuation;
-        BsdfPdf P;
-        P.n = rec.normal;
-        P.stash = kBeckmannStashInit;
-        if (m.type == SRT_MAT_BRDF) {
-            // material.h:217-236: the MERL value is looked up and discarded, attenuation = albedo,
-            // and srec.pdf_ptr is left unset (the reference then calls through a wild pointer).
-            // Stand-in: the cosine_pdf every other diffuse material gets.  The
-            // discarded lookup has no side effect and is not evaluated here; its arithmetic is
-            // exported for parity through srt_merl_lookup (srt_microfacet.cuh: merl_lookup).
-            attenuation = v3(m.p[0], m.p[1], m.p[2]);
-            P.kind = SRT_MAT_LAMBERTIAN;
-        } else {
-            attenuation = texture_value(S, m.texture, rec.u, rec.v, rec.p);
-            P.kind = m.type;
-            P.a = m.p[0];
-            P.b = m.p[1];
-        }
-        P.uvw = onb_from_w(rec.normal);
-        V3 sdir = v3(0.f, 0.f, 0.f);
-        float pdf_val = 0.f;
-        if (S.n_lights > 0) {  // Raytracing_n.cpp:75-84: mixture_pdf(hitable_pdf, bsdf pdf)
-            int iters = 0;
-            while (pdf_val == 0.f) {
-                if (++iters > kMaxRejectIters) break;
-                if (COUNT) tl.c->reject_iters++;
-                if (rand_d(rng) < 0.5)  // pdf.h:183-189
-                    sdir = light_random(S, rec.p, rng);
-                else
-                    sdir = bsdf_generate(P, r.d, rng);
-                float pl = light_pdf_value(S, rec.p, sdir, tl);
-                float pb = bsdf_value(P, r.d, sdir);
-                pdf_val = (float)(0.5 * (double)pl + 0.5 * (double)pb);  // pdf.h:177-182
-            }
-        } else {  // Raytracing_n.cpp:85-89
-            sdir = bsdf_generate(P, r.d, rng);
-            pdf_val = bsdf_value(P, r.d, sdir);
-        }
-        Ray scattered{rec.p, sdir, r.time};
-        float spdf;
-        if (m.type == SRT_MAT_BECKMANN) {
-            spdf = beckmann_scattering_pdf(rec.normal, m.p[0], m.p[1], r.d, sdir);
-        } else {  // material.h:100-105, :133-137, :207-213
-            float c = dot(rec.normal, unit_vector(sdir));
-            if (c < 0.f) c = 0.f;
-            spdf = (float)((double)c / kPi);
-        }
-        L = L + thr * emitted;
-        thr = ((thr * (attenuation * spdf))) / pdf_val;
-        r = scattered;
-        depth++;
-        // a zero throughput cannot contribute any more: finite * 0 == 0 in the recursive form too
-        if (thr.x == 0.f && thr.y == 0.f && thr.z == 0.f) {
-            if (COUNT) tl.c->culled_rays++;
-            break;
-        }
+// unrolls to radiance = sum over vertices of (throughput so far) * emitted.
+struct Path {
+    Ray r;
+    V3 thr;  // product of attenuation * scattering_pdf / pdf_val so far
+    V3 L;    // radiance gathered so far
+    int depth;
+};
+
+// One level of color() (Raytracing_n.cpp:55-106) for a path whose ray has just been traced to `h`.
+// Returns true when the path continues (P.r is the next ray), false when it has ended (P.L is final).
+template <uint32_t F, bool COUNT>
+SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, Philox& rng, Tally<COUNT> tl) {
+    const DScene& S = W.S;
+    if (h.prim < 0) {
+        // miss: color() returns vec3(0) — kept as `thr * 0` so that an inf / NaN throughput poisons
+        // the sample exactly as in the recursive form (de_nan then zeroes those channels)
+        P.L = fm::madd(P.thr, 0.f, P.L);
+        return false;
     }
-    return L;
+    int mat_index;
+    if ((F & F_MEDIA) && h.prim >= S.n_prims)
+        mat_index = S.media[h.prim - S.n_prims].phase_material;
+    else
+        mat_index = load_prim(W.dprims + h.prim).material;
+    if (mat_index < 0) return false;  // no material: the reference would dereference null
+    DMaterial m = load_material(S.materials + mat_index);
+    HitRecord rec = material_needs_uv<F>(m) ? make_record<F, true>(W, P.r, h) : make_record<F, false>(W, P.r, h);
+    const Ray r = P.r;
+
+    if (m.type == SRT_MAT_DIFFUSE_LIGHT) {  // material.h:348-354: one-sided; scatter() returns false
+        if (fm::dot(rec.normal, r.d) < 0.f) {
+            V3 e = material_color<F>(S, m, rec);
+            P.L = v3(fmaf(P.thr.x, e.x, P.L.x), fmaf(P.thr.y, e.y, P.L.y), fmaf(P.thr.z, e.z, P.L.z));
+        } else {
+            P.L = fm::madd(P.thr, 0.f, P.L);
+        }
+        return false;
+    }
+    if (!(P.depth < max_depth)) {  // Raytracing_n.cpp:63: returns emitted (0 for every non-light)
+        P.L = fm::madd(P.thr, 0.f, P.L);
+        return false;
+    }
+    // specular materials: return attenuation * color(specular_ray) (emitted is dropped, :66-70)
+    if ((F & F_METAL) && m.type == SRT_MAT_METAL) {  // material.h:248-256
+        V3 reflected = reflect(fm::normalize(r.d), rec.normal);
+        V3 dir = fm::madd(random_in_unit_sphere(rng), m.p[3], reflected);
+        P.thr = fm::mul(P.thr, v3(m.c[0], m.c[1], m.c[2]));
+        P.r = Ray{rec.p, dir, 0.f};
+        P.depth++;
+        return true;
+    }
+    if ((F & F_DIELECTRIC) && m.type == SRT_MAT_DIELECTRIC) {  // material.h:285-324
+        float ref_idx = m.p[0];
+        V3 outward_normal, refracted;
+        V3 reflected = reflect(r.d, rec.normal);  // the un-normalised direction, as in the reference
+        float ni_over_nt, cosine, reflect_prob;
+        float dn = fm::dot(r.d, rec.normal);
+        float rl = fm::rlength(r.d);
+        if (dn > 0.f) {
+            outward_normal = fm::neg(rec.normal);
+            ni_over_nt = ref_idx;
+            cosine = dn * rl;  // material.h:299: NOT multiplied by ref_idx
+        } else {
+            outward_normal = rec.normal;
+            ni_over_nt = 1.0f / ref_idx;
+            cosine = -dn * rl;
+        }
+        if (refract(r.d, outward_normal, ni_over_nt, refracted))
+            reflect_prob = schlick(cosine, ref_idx);
+        else
+            reflect_prob = 1.0f;
+        V3 dir = (rand_f(rng) < reflect_prob) ? reflected : refracted;
+        P.r = Ray{rec.p, dir, 0.f};
+        P.depth++;
+        return true;
+    }
+    if ((F & F_MEDIA) && m.type == SRT_MAT_ISOTROPIC) {  // material.h:362-367
+        V3 dir = random_in_unit_sphere(rng);
+        P.thr = fm::mul(P.thr, material_color<F>(S, m, rec));
+        P.r = Ray{rec.p, dir, 0.f};
+        P.depth++;
+        return true;
+    }
+    // non-specular: lambertian, orennayar, beckmann, brdfmaterial
+    V3 attenuation;
+    BsdfPdf B;
+    B.n = rec.normal;
+    B.stash = kBeckmannStashInit;
+    B.a = m.p[0];
+    B.b = m.p[1];
+    if (m.type == SRT_MAT_BRDF) {
+        // material.h:217-236: the MERL value is looked up and discarded, attenuation = albedo, and
+        // srec.pdf_ptr is left unset (the reference then calls through a wild pointer).  Stand-in
+        // (DESIGN.md §5): the cosine_pdf every other diffuse material gets.  The discarded lookup has
+        // no side effect and is not evaluated here; its arithmetic is exported for parity through
+        // srt_merl_lookup (srt_microfacet.cuh: merl_lookup).
+        attenuation = v3(m.c[0], m.c[1], m.c[2]);
+        B.kind = SRT_MAT_LAMBERTIAN;
+    } else {
+        attenuation = material_color<F>(S, m, rec);
+        B.kind = (F & (F_ORENNAYAR | F_BECKMANN)) ? m.type : SRT_MAT_LAMBERTIAN;
+    }
+    B.uvw = onb_fast(rec.normal);
+    V3 sdir = v3(0.f, 0.f, 0.f);
+    float pdf_val = 0.f;
+    if (S.n_lights > 0) {  // Raytracing_n.cpp:75-84: mixture_pdf(hitable_pdf, bsdf pdf)
+        int iters = 0;
+        while (pdf_val == 0.f) {
+            if (++iters > kMaxRejectIters) break;
+            if (COUNT) tl.c->reject_iters++;
+            if (rand_f(rng) < 0.5f)  // pdf.h:183-189
+                sdir = light_random<F>(W, rec.p, rng);
+            else
+                sdir = bsdf_generate<F>(B, r.d, rng);
+            float pl = light_pdf_value<F>(W, rec.p, sdir, tl);
+            float pb = bsdf_value<F>(B, r.d, sdir);
+            pdf_val = 0.5f * pl + 0.5f * pb;  // pdf.h:177-182
+        }
+    } else {  // Raytracing_n.cpp:85-89
+        sdir = bsdf_generate<F>(B, r.d, rng);
+        pdf_val = bsdf_value<F>(B, r.d, sdir);
+    }
+    float spdf;
+    if ((F & F_BECKMANN) && m.type == SRT_MAT_BECKMANN) {
+        spdf = beckmann_scattering_pdf(rec.normal, m.p[0], m.p[1], r.d, sdir);
+    } else {  // material.h:100-105, :133-137, :207-213
+        float c = fm::dot(rec.normal, sdir) * fm::rlength(sdir);
+        if (c < 0.f) c = 0.f;
+        spdf = c * fm::kInvPi;
+    }
+    // emitted is 0 for every scattering material (material.h:89-92)
+    float wgt = spdf / pdf_val;
+    P.thr = fm::mul(P.thr, fm::scale(attenuation, wgt));
+    P.r = Ray{rec.p, sdir, r.time};
+    P.depth++;
+    // a zero throughput cannot contribute any more: finite * 0 == 0 in the recursive form too
+    if (P.thr.x == 0.f && P.thr.y == 0.f && P.thr.z == 0.f) {
+        if (COUNT) tl.c->culled_rays++;
+        return false;
+    }
+    return true;
 }
 
-// camera::get_ray (camera.h:51-59)
+// camera::get_ray (camera.h:51-59).  Exact arithmetic: these rays are what srt_trace_closest is
+// compared on, and the reference normalises the direction with three divisions.
 SRT_DEV Ray camera_get_ray(const SrtCamera& C, float s, float t, Philox& rng) {
     V3 offset = v3(0.f, 0.f, 0.f);
     if (C.lens_radius != 0.f) {
@@ -416,7 +462,7 @@ SRT_DEV Ray camera_get_ray(const SrtCamera& C, float s, float t, Philox& rng) {
         offset = v3(C.u) * rd.x + v3(C.v) * rd.y;
     }
     float time = C.time0;
-    if (C.time1 != C.time0) time = (float)((double)C.time0 + rand_d(rng) * (double)xsub(C.time1, C.time0));
+    if (C.time1 != C.time0) time = fmaf(rand_f(rng), C.time1 - C.time0, C.time0);
     V3 origin = v3(C.origin);
     V3 dir = v3(C.lower_left_corner) + s * v3(C.horizontal) + t * v3(C.vertical) - origin - offset;
     dir = unit_vector(dir);

@@ -1,12 +1,17 @@
 // srt_types.h — device-resident scene layout shared by the host builder and the CUDA kernels.
 //
 // Everything the kernels read lives in ONE device allocation per scene; `DScene` is the table of
-// typed pointers into it (passed to kernels by value, 200-odd bytes of kernel parameters, so every
-// field is a uniform-register load).  Layout rules:
-//   * 16-byte-aligned records read with one vector load: spheres float4, rects 2 x float4,
-//     packed leaf triangles 3 x float4, wide BVH nodes 8 x float4;
-//   * the flattened reference graph (entries / ops / groups / prims) is kept as it came through the
-//     C ABI (include/srt_ffi.h) — it is small and L1/constant-cache resident.
+// typed pointers into it (passed to kernels by value, so every field is a uniform-register load).
+// Layout rules:
+//   * every record the inner loops touch is a whole number of 16-byte units read with vector
+//     loads: DPrim 2 x 16 B (geometry + plane / type / material / flags inline: one load chain per
+//     primitive instead of prims[] -> rects[] / spheres[]), DEntry 4 x 16 B (with conservative
+//     local-frame bounds), DMaterial 3 x 16 B (constant textures folded in), wide BVH nodes
+//     8 x 16 B, packed leaf triangles 3 x 16 B;
+//   * the "hot" tables every ray walks (entries, instance ops, primitive records, lights) are
+//     contiguous at the front of the blob so that a CTA can stage them into shared memory with one
+//     bulk copy (srt_kernels.cuh) when they fit; everything else stays in global memory and is
+//     L1 / L2 resident (no scene of BASELINE.json:configs C1-C4 exceeds the 126 MB L2).
 #ifndef SRT_TYPES_H
 #define SRT_TYPES_H
 
@@ -25,6 +30,75 @@ struct alignas(16) int4 {
 };
 #endif
 
+// ---- kernel specialisation: which reference classes a scene instantiates ------------------------
+// The render kernel is compiled for a few feature masks (srt_variants.h); a scene runs on the
+// smallest variant whose mask covers its own.  Always present: rect / sphere groups, lambertian,
+// brdfmaterial (samples like lambertian, material.h:217-236), diffuse_light, constant_texture,
+// xz_rect lights.
+enum : uint32_t {
+    F_XFORM = 1u << 0,        // translate / rotate_x / rotate_y above a world entry
+    F_BVH_SPHERE = 1u << 1,   // a bvh_node whose leaves are all spheres
+    F_BVH_TRI = 1u << 2,      // a bvh_node whose leaves are all triangles
+    F_BVH_GENERIC = 1u << 3,  // any other bvh_node
+    F_TRI = 1u << 4,          // triangle outside a triangle-only bvh (lists, lights, generic bvh)
+    F_MSPHERE = 1u << 5,      // moving_sphere
+    F_ENV = 1u << 6,          // env_sphere as a world object
+    F_MEDIA = 1u << 7,        // constant_medium (+ isotropic)
+    F_ORENNAYAR = 1u << 8,
+    F_BECKMANN = 1u << 9,
+    F_METAL = 1u << 10,
+    F_DIELECTRIC = 1u << 11,
+    F_TEX_CHECKER = 1u << 12,
+    F_TEX_NOISE = 1u << 13,
+    F_TEX_IMAGE = 1u << 14,
+    F_LIGHT_SPHERE = 1u << 15,
+    F_LIGHT_TRI = 1u << 16,
+    F_LIGHT_ENV = 1u << 17,
+    F_LIGHT_NONE = 1u << 18,  // a light-list element without pdf_value / random (hitable.h:31-32)
+    F_SMEM_TABLES = 1u << 24, // launch option, not a scene property: hot tables staged in smem
+    F_ALL_SCENE = (1u << 19) - 1u
+};
+
+// ---- flat primitive record: 32 B, index in the array == primitive id (SrtSceneDesc.prims) --------
+// rect            : g = (a0, a1, b0, b1), k = plane
+// sphere / env    : g = (cx, cy, cz, r)
+// moving / triangle: aux = row in msph[] / tri_*[]
+struct alignas(16) DPrim {
+    float4 g;
+    float k;
+    int32_t type;      // SRT_PRIM_*
+    int32_t material;  // index into materials[] or -1
+    uint32_t flags_aux;  // bit 0 = SRT_PRIM_FLIP; bits 1.. = aux row (flags_aux >> 1)
+};
+
+// ---- world entry: 64 B --------------------------------------------------------------------------
+enum : uint32_t {
+    DENTRY_CULL = 1u,  // bounds are valid and finite: a ray missing them cannot hit the geometry
+    DENTRY_TCULL = 2u  // every leaf below reports a parametric t and honours (t_min, t_max)
+};
+struct alignas(16) DEntry {
+    int32_t first_prim, prim_count;  // group entries: range in dprims[]
+    int32_t first_op, op_count;
+    int32_t geom_kind, geom_index;   // SRT_GEOM_*; bvhs[] index for SRT_GEOM_BVH
+    int32_t medium;
+    uint32_t flags;                  // DENTRY_*
+    float lo[3];                     // conservative bounds of the geometry in the entry's own frame
+    float _p0;
+    float hi[3];
+    float _p1;
+};
+
+// ---- material with its texture head folded in: 48 B ---------------------------------------------
+struct alignas(16) DMaterial {
+    int32_t type;      // SRT_MAT_*
+    int32_t texture;   // index into textures[] (-1: none)
+    int32_t tex_type;  // SRT_TEX_* of that texture (-1: none); CONSTANT -> c is its colour
+    int32_t _pad;
+    float p[4];        // p0..p3 of SrtMaterial
+    float c[3];        // constant-texture colour, or p0..p2 for brdf / metal albedo
+    float _pad2;
+};
+
 // ---- wide BVH (4-ary, full-precision child boxes, SoA per node; 128 B = 8 x 16 B loads) --------
 // child[i] >= 0            : index of an inner node
 // child[i] <  0, count > 0 : leaf; first = ~child[i] is the first slot of the bvh's leaf arrays
@@ -39,8 +113,8 @@ struct alignas(16) WideNode4 {
 // ---- the reference's own bvh_node tree (bvh.h:96-119), kept only as boxes ---------------------
 // A primitive inside a reference bvh_node is reachable only if every ancestor box passes
 // aabb::hit (aabb.h:33-49) with the entry (t_min, t_max); the reference boxes are un-padded, so
-// this test decides real pixels.  The kernels find candidates with their own SAH
-// tree and then replay the candidate's ancestor chain here.  Node over leaf ranks [lo, lo+n):
+// this test decides real pixels.  The kernels find the winner with their own SAH
+// tree and then replay its ancestor chain here.  Node over leaf ranks [lo, lo+n):
 // n <= 2 -> no children (left = right = -1); else left covers [lo, lo+n/2), right the rest.
 struct alignas(16) RefNode {
     float lo[3];
@@ -76,10 +150,13 @@ struct DImage {
 };
 
 struct DScene {
-    const SrtEntry* entries;
+    // hot tables (contiguous in the blob, in this order; hot_bytes covers all four)
+    const DEntry* entries;
     const SrtXformOp* ops;
+    const DPrim* dprims;
+    const DPrim* lights;  // the light_shape list as primitive records (material = -1)
+    // the rest
     const SrtGroup* groups;
-    const SrtPrim* prims;
     const int32_t* bvh_items;
     const SrtMedium* media;
     const DBvh* bvhs;
@@ -87,21 +164,20 @@ struct DScene {
     const RefNode* ref_nodes;
     const int32_t* leaf_rank;
     const float4* leaf_geom;
-    const float4* spheres;  // [n][1]
     const float* msph;      // [n][9]
-    const float4* rects;    // [n][2] = (a0, a1, b0, b1), (k, 0, 0, 0)
     const float* tri_pos;   // [n][9]
     const float* tri_nrm;   // [n][9]
     const float* tri_uv;    // [n][6]
-    const SrtLight* lights;
-    const SrtMaterial* materials;
+    const DMaterial* materials;
     const SrtTexture* textures;
     const DImage* images;
     const float* perlin_ranvec;  // [256][3]
     const int32_t* perlin_perm;  // [3][256]
     const double* const* merl;
     int32_t n_entries, n_prims, n_lights, n_media;
-    int32_t n_materials, n_textures, n_bvhs, _pad;
+    int32_t n_materials, n_textures, n_bvhs, n_ops;
+    uint32_t hot_bytes;  // bytes from `entries` to the end of `lights` (16-byte multiple)
+    uint32_t features;   // F_* mask of the scene
     SrtCamera camera;
 };
 

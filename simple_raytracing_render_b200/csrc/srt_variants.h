@@ -1,0 +1,65 @@
+// srt_variants.h — the render kernel is compiled once per feature mask, one translation unit per
+// variant (srt_render_variant.cu compiled with -DSRT_VARIANT=<n>), so that the variants build in
+// parallel and each stays small enough for the instruction cache (profiles/r01_notes.md: the
+// all-features kernel was 22 600 SASS instructions and spent 51 % of its warp-cycles waiting for
+// instruction fetch on a scene that executes 2 200 of them).
+#ifndef SRT_VARIANTS_H
+#define SRT_VARIANTS_H
+
+#include <cuda_runtime.h>
+
+#include "srt_types.h"
+
+namespace srt {
+struct RenderArgs;
+}
+
+struct RenderLaunch {
+    const DScene* scene;
+    const srt::RenderArgs* args;
+    const uint32_t* sobol;
+    float* out;
+    unsigned long long* counters;
+    int grid;  // 0: only query (blocks_per_sm, registers)
+    size_t smem_bytes;
+    cudaStream_t stream;
+};
+
+struct RenderVariantInfo {
+    uint32_t features;  // F_* the variant was compiled with (including F_SMEM_TABLES)
+    int counting;       // 1: gathers SrtCounters
+    int blocks_per_sm;  // filled by the launcher from the occupancy calculator
+    int registers;
+};
+
+typedef cudaError_t (*RenderVariantFn)(const RenderLaunch& L, RenderVariantInfo* info);
+
+// scene classes the variants are cut for
+#define SRT_VM_LIST (F_XFORM | F_METAL | F_DIELECTRIC)
+#define SRT_VM_SPHERES (SRT_VM_LIST | F_BVH_SPHERE | F_TEX_CHECKER | F_LIGHT_SPHERE)
+#define SRT_VM_MESH                                                                                     \
+    (SRT_VM_SPHERES | F_BVH_TRI | F_BVH_GENERIC | F_TRI | F_BECKMANN | F_ORENNAYAR | F_TEX_IMAGE | F_LIGHT_TRI | \
+     F_LIGHT_NONE)
+#define SRT_VM_FULL F_ALL_SCENE
+
+// variant n -> (mask, counting)
+#define SRT_N_VARIANTS 7
+#define SRT_VARIANT_MASK(n)                                  \
+    ((n) == 0   ? (SRT_VM_LIST | F_SMEM_TABLES)              \
+     : (n) == 1 ? (SRT_VM_SPHERES | F_SMEM_TABLES)           \
+     : (n) == 2 ? (SRT_VM_MESH | F_SMEM_TABLES)              \
+     : (n) == 3 ? (SRT_VM_FULL | F_SMEM_TABLES)              \
+     : (n) == 4 ? (SRT_VM_MESH)                              \
+     : (n) == 5 ? (SRT_VM_FULL)                              \
+                : (SRT_VM_FULL))
+#define SRT_VARIANT_COUNTING(n) ((n) == 6)
+
+cudaError_t srt_render_variant_0(const RenderLaunch&, RenderVariantInfo*);
+cudaError_t srt_render_variant_1(const RenderLaunch&, RenderVariantInfo*);
+cudaError_t srt_render_variant_2(const RenderLaunch&, RenderVariantInfo*);
+cudaError_t srt_render_variant_3(const RenderLaunch&, RenderVariantInfo*);
+cudaError_t srt_render_variant_4(const RenderLaunch&, RenderVariantInfo*);
+cudaError_t srt_render_variant_5(const RenderLaunch&, RenderVariantInfo*);
+cudaError_t srt_render_variant_6(const RenderLaunch&, RenderVariantInfo*);
+
+#endif

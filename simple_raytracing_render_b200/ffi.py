@@ -106,7 +106,9 @@ class SrtCounters(C.Structure):
 class SrtSceneInfo(C.Structure):
     _fields_ = [("n_prims", C.c_int32), ("n_entries", C.c_int32), ("n_bvhs", C.c_int32), ("n_lights", C.c_int32),
                 ("bvh_nodes", C.c_int64), ("bvh_node_bytes", C.c_int64), ("device_bytes", C.c_int64),
-                ("sah_cost", C.c_float), ("build_ms", C.c_float)]
+                ("sah_cost", C.c_float), ("build_ms", C.c_float), ("features", C.c_uint32),
+                ("render_variant", C.c_int32), ("render_registers", C.c_int32), ("render_blocks_per_sm", C.c_int32),
+                ("hot_table_bytes", C.c_int64)]
 
     def as_dict(self):
         return {n: getattr(self, n) for n, _ in self._fields_}
@@ -348,6 +350,7 @@ _SIGNATURES = {
     "srt_counters_get": (C.c_int, [C.c_void_p, C.POINTER(SrtCounters)]),
     "srt_sobol_points_u32": (C.c_int, [C.c_uint32, C.c_void_p]),
     "srt_merl_lookup": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
+    "srt_selftest_division": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_uint64)]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

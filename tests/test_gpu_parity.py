@@ -142,8 +142,11 @@ def test_counters_are_consistent(golden_scene):
     assert c["rays"] >= c["paths"] and c["prim_tests"] > 0
     # the reference's own rays/path for this scene (golden img_rays) within a few percent
     ref_rpp = float(g["img_rays"]) / (int(g["img_nx"]) * int(g["img_ny"]) * int(g["img_ns"]))
-    # (the backend does not trace continuation rays whose throughput is exactly zero; it counts them)
-    assert abs((c["rays"] + c["culled_rays"]) / c["paths"] - ref_rpp) < 0.05 * ref_rpp
+    # The backend stops a path whose throughput is exactly zero (it cannot change the sample); the
+    # reference keeps bouncing it.  culled_rays counts the first skipped ray of each such path, so
+    # rays + culled is a lower bound of the reference's count and not far below it.
+    got = (c["rays"] + c["culled_rays"]) / c["paths"]
+    assert 0.85 * ref_rpp <= got <= 1.02 * ref_rpp
 
 
 # ---- live oracle (oracle/_ref/libsrt_ref.so travelled with the snapshot) ---------------------------
