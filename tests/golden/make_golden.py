@@ -60,5 +60,5 @@ def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny):
 
 if __name__ == "__main__":
     kats()
-    scene_vectors("cornell", 64, 64, 2, 1024, 48, 48)
-    scene_vectors("spheres", 96, 64, 2, 1024, 48, 32)
+    scene_vectors("cornell", 64, 64, 2, 4096, 48, 48)
+    scene_vectors("spheres", 96, 64, 2, 16384, 48, 32)
