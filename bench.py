@@ -171,7 +171,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from simple_raytracing_render_b200 import ffi, render, scenes, scene as S
+    from simple_raytracing_render_b200 import ffi, multigpu, render, scenes, scene as S
 
     world_size = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -192,7 +192,7 @@ def main():
     info = sc.info()
 
     # sample-range shard of this rank: Sobol indices [s0, s1) of every pixel
-    s0, s1 = (ns * rank) // world_size, (ns * (rank + 1)) // world_size
+    s0, s1 = multigpu.sample_shard(ns, rank, world_size)
     params = render.render_params(nx, ny, ns, s0, s1, seed=SEED)
     accum = torch.zeros(n_pixels * 3, dtype=torch.float32, device=dev)
     rgb8 = torch.zeros(n_pixels * 3, dtype=torch.uint8, device=dev)
@@ -201,8 +201,7 @@ def main():
     def step():
         accum.zero_()
         sc.render(params, accum)
-        if world_size > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        multigpu.reduce_accum(accum, 0)
         if rank == 0:
             ctx.resolve(accum, n_pixels, ns, rgb8)
 
@@ -231,8 +230,7 @@ def main():
             kev[k][0].record(stream)
             sc.render(params, accum)
             kev[k][1].record(stream)
-            if world_size > 1:
-                dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+            multigpu.reduce_accum(accum, 0)
             if rank == 0:
                 ctx.resolve(accum, n_pixels, ns, rgb8)
             ev[k][1].record(stream)
@@ -262,8 +260,13 @@ def main():
     host_rgb = torch.empty(n_pixels * 3, dtype=torch.uint8).pin_memory()
     host_acc = torch.empty(n_pixels * 3, dtype=torch.float32).pin_memory() if world_size > 1 else None
 
+    e2e_parts = {"scene_create_ms": 0.0, "render_image_ms": 0.0}
+
     def e2e_step():
+        ta = time.perf_counter()
         sc2 = render.Scene(ctx, flat)  # host scene description -> device (h2d)
+        tb = time.perf_counter()
+        e2e_parts["scene_create_ms"] += (tb - ta) * 1e3
         if world_size > 1:
             sc2.render_image(full, rgb8=host_rgb.numpy(), accum=host_acc.numpy(), want_accum=True)
             a = host_acc.to(dev, non_blocking=True)
@@ -272,6 +275,7 @@ def main():
                 ctx.resolve(a, n_pixels, ns, host_rgb.numpy())
         else:
             sc2.render_image(full, rgb8=host_rgb.numpy())
+        e2e_parts["render_image_ms"] += (time.perf_counter() - tb) * 1e3
         sc2.close()
 
     with torch.cuda.stream(stream):
@@ -279,6 +283,7 @@ def main():
             e2e_step()
         sync_all()
         e2e_steps = max(3, min(args.steps, 10))
+        e2e_parts = {k: 0.0 for k in e2e_parts}
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
             e2e_step()
@@ -315,7 +320,8 @@ def main():
             "e2e": {"value": paths_per_step / e2e_s, "unit": "paths/s",
                     "h2d_bytes_per_step": int(info["device_bytes"]),
                     "d2h_bytes_per_step": int(n_pixels * 3 + (n_pixels * 12 if world_size > 1 else 0)),
-                    "ms_per_step": e2e_s * 1e3},
+                    "ms_per_step": e2e_s * 1e3,
+                    "parts_ms": {k: v / e2e_steps for k, v in e2e_parts.items()}},
             "gpu_launches": int(launches),
             "clocks": clk,
         }

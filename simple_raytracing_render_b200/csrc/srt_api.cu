@@ -49,6 +49,17 @@ struct SrtContext {
     size_t rgb8_cap = 0;
     uint8_t* h_rgb8 = nullptr;  // pinned
     size_t h_rgb8_cap = 0;
+    // work buffers shared by every scene of the context (a context renders one call at a time):
+    // kept across scenes so that re-creating a scene per frame costs no allocation
+    uint32_t* d_sobol = nullptr;  // Sobol numerators, [sobol_n][2]
+    uint32_t sobol_n = 0;
+    float* d_accum = nullptr;  // srt_render_image's internal accumulation buffer
+    size_t accum_cap = 0;
+    float* d_partial = nullptr;  // [n_chunks][n_pixels][3] per-item radiance sums of the last render
+    size_t partial_cap = 0;
+    int variant_blocks[SRT_N_VARIANTS] = {};  // occupancy query results, 0 = not queried yet
+    int variant_regs[SRT_N_VARIANTS] = {};
+    size_t variant_smem[SRT_N_VARIANTS] = {};  // dynamic shared memory the query was made with
 };
 
 struct SrtScene {
@@ -59,14 +70,6 @@ struct SrtScene {
     SrtSceneInfo info = {};
     std::vector<double*> d_merl;
     std::vector<const double*> merl_ptrs_host;
-    uint32_t* d_sobol = nullptr;
-    uint32_t sobol_n = 0;
-    float* d_accum = nullptr;  // srt_render_image's internal accumulation buffer
-    size_t accum_cap = 0;
-    float* h_accum = nullptr;  // pinned staging
-    size_t h_accum_cap = 0;
-    float* d_partial = nullptr;  // [n_chunks][n_pixels][3] per-item radiance sums of the last render
-    size_t partial_cap = 0;
     int variant = -1;        // render-kernel variant this scene runs on
     int variant_blocks = 0;  // its resident blocks per SM
     int variant_regs = 0;
@@ -320,6 +323,9 @@ int srt_context_destroy(SrtContext* ctx) {
     cudaStreamSynchronize(ctx->stream);
     cudaFree(ctx->d_counters);
     cudaFree(ctx->d_rgb8);
+    cudaFree(ctx->d_sobol);
+    cudaFree(ctx->d_accum);
+    cudaFree(ctx->d_partial);
     if (ctx->h_rgb8) cudaFreeHost(ctx->h_rgb8);
     delete ctx;
     return 0;
@@ -338,10 +344,6 @@ int srt_scene_destroy(SrtScene* s) {
     cudaStreamSynchronize(s->ctx->stream);
     cudaFree(s->d_blob);
     for (double* p : s->d_merl) cudaFree(p);
-    cudaFree(s->d_sobol);
-    cudaFree(s->d_accum);
-    cudaFree(s->d_partial);
-    if (s->h_accum) cudaFreeHost(s->h_accum);
     delete s;
     return 0;
 }
@@ -848,13 +850,13 @@ int srt_sobol_points_u32(uint32_t N, uint32_t* out) {
 
 namespace {
 
-int ensure_sobol(SrtScene* s, uint32_t n) {
+int ensure_sobol(SrtContext* s, uint32_t n) {
     if (s->sobol_n >= n) return 0;
-    uint32_t cap = std::max<uint32_t>(n, 64);
+    uint32_t cap = std::max<uint32_t>(n, 1024);
     std::vector<uint32_t> pts(2 * (size_t)cap);
     srt_sobol_points_u32(cap, pts.data());
     if (s->d_sobol) {
-        CUDA_TRY(cudaStreamSynchronize(s->ctx->stream));
+        CUDA_TRY(cudaStreamSynchronize(s->stream));
         CUDA_TRY(cudaFree(s->d_sobol));
         s->d_sobol = nullptr;
         s->sobol_n = 0;
@@ -908,7 +910,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     SrtContext* c = s->ctx;
     int count = p->s_end - p->s_begin;
     if (count == 0) return 0;
-    int rc = ensure_sobol(s, (uint32_t)p->s_end);
+    int rc = ensure_sobol(c, (uint32_t)p->s_end);
     if (rc) return rc;
     int v = pick_variant(s, counting);
     if (v < 0) return fail(SRT_E_UNSUPPORTED, "no render-kernel variant covers feature mask 0x%x", s->dev.features);
@@ -916,26 +918,29 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
 
     RenderLaunch L;
     L.scene = &s->dev;
-    L.sobol = s->d_sobol;
+    L.sobol = c->d_sobol;
     L.counters = c->d_counters;
     L.smem_bytes = smem;
     L.stream = c->stream;
     L.grid = 0;
     RenderVariantInfo info = {};
-    if (!counting && s->variant == v) {
-        info.blocks_per_sm = s->variant_blocks;
-        info.registers = s->variant_regs;
+    if (c->variant_blocks[v] > 0 && smem <= c->variant_smem[v]) {
+        info.blocks_per_sm = c->variant_blocks[v];
+        info.registers = c->variant_regs[v];
     } else {
         L.args = nullptr;
         L.out = nullptr;
         cudaError_t e = kVariants[v](L, &info);
         if (e != cudaSuccess) return fail(SRT_E_CUDA, "render variant %d: %s", v, cudaGetErrorString(e));
-        if (!counting) {
-            s->variant = v;
-            s->variant_blocks = info.blocks_per_sm;
-            s->variant_regs = info.registers;
-            s->variant_smem = smem;
-        }
+        c->variant_blocks[v] = info.blocks_per_sm;
+        c->variant_regs[v] = info.registers;
+        c->variant_smem[v] = smem;
+    }
+    if (!counting) {
+        s->variant = v;
+        s->variant_blocks = info.blocks_per_sm;
+        s->variant_regs = info.registers;
+        s->variant_smem = smem;
     }
     int blocks_per_sm = std::max(1, info.blocks_per_sm);
 
@@ -964,19 +969,20 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     A.n_items = (unsigned)(n_pixels * n_chunks);
     A.regen_threshold = std::max(1, std::min(32, env_int("SRT_REGEN", 8)));
     A.grab = std::max(32, env_int("SRT_GRAB", 128));
+    A.cta_sync = std::max(0, std::min(2, env_int("SRT_CTA_SYNC", 0)));
 
     float* out = accum;
     if (n_chunks > 1) {
         size_t need = sizeof(float) * 3 * (size_t)n_pixels * n_chunks;
-        if (s->partial_cap < need) {
+        if (c->partial_cap < need) {
             CUDA_TRY(cudaStreamSynchronize(c->stream));
-            cudaFree(s->d_partial);
-            s->d_partial = nullptr;
-            s->partial_cap = 0;
-            CUDA_TRY(cudaMalloc(&s->d_partial, need));
-            s->partial_cap = need;
+            cudaFree(c->d_partial);
+            c->d_partial = nullptr;
+            c->partial_cap = 0;
+            CUDA_TRY(cudaMalloc(&c->d_partial, need));
+            c->partial_cap = need;
         }
-        out = s->d_partial;
+        out = c->d_partial;
     }
     // counters[7] is the work counter
     CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
@@ -990,7 +996,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     if (e != cudaSuccess) return fail(SRT_E_CUDA, "k_render (variant %d): %s", v, cudaGetErrorString(e));
     if (n_chunks > 1) {
         long long nv = 3 * n_pixels;
-        srt::k_sum_partials<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(s->d_partial, n_chunks, nv, accum);
+        srt::k_sum_partials<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(c->d_partial, n_chunks, nv, accum);
         c->launches++;
         CUDA_TRY(cudaGetLastError());
     }
@@ -1076,19 +1082,19 @@ int srt_render_image(SrtScene* s, const SrtRenderParams* p, uint8_t* rgb8_host, 
     SrtContext* c = s->ctx;
     CUDA_TRY(cudaSetDevice(c->device));
     size_t nv = 3 * (size_t)p->nx * p->ny;
-    if (s->accum_cap < nv) {
+    if (c->accum_cap < nv) {
         CUDA_TRY(cudaStreamSynchronize(c->stream));
-        cudaFree(s->d_accum);
-        s->d_accum = nullptr;
-        s->accum_cap = 0;
-        CUDA_TRY(cudaMalloc(&s->d_accum, sizeof(float) * nv));
-        s->accum_cap = nv;
+        cudaFree(c->d_accum);
+        c->d_accum = nullptr;
+        c->accum_cap = 0;
+        CUDA_TRY(cudaMalloc(&c->d_accum, sizeof(float) * nv));
+        c->accum_cap = nv;
     }
-    CUDA_TRY(cudaMemsetAsync(s->d_accum, 0, sizeof(float) * nv, c->stream));
-    rc = launch_render(s, p, s->d_accum, false);
+    CUDA_TRY(cudaMemsetAsync(c->d_accum, 0, sizeof(float) * nv, c->stream));
+    rc = launch_render(s, p, c->d_accum, false);
     if (rc) return rc;
-    if (accum_host) CUDA_TRY(cudaMemcpyAsync(accum_host, s->d_accum, sizeof(float) * nv, cudaMemcpyDeviceToHost, c->stream));
-    return srt_resolve(c, s->d_accum, (int64_t)p->nx * p->ny, p->s_end - p->s_begin, rgb8_host);
+    if (accum_host) CUDA_TRY(cudaMemcpyAsync(accum_host, c->d_accum, sizeof(float) * nv, cudaMemcpyDeviceToHost, c->stream));
+    return srt_resolve(c, c->d_accum, (int64_t)p->nx * p->ny, p->s_end - p->s_begin, rgb8_host);
 }
 
 }  // extern "C"

@@ -17,6 +17,7 @@ struct RenderArgs {
     unsigned n_items;     // n_pixels * n_chunks
     int regen_threshold;  // idle lanes in a warp that trigger a regeneration phase
     int grab;             // work items a warp takes from the global counter at a time
+    int cta_sync;         // 1: the warps of a CTA start every bounce together; 2: and every shade together
 };
 
 constexpr int kRenderThreads = 256;
@@ -85,9 +86,16 @@ __global__ void __launch_bounds__(kRenderThreads, 2)
     unsigned w_cur = 0, w_end = 0;
     bool exhausted = false;
 
+    // cta_sync: the kernel is several times the instruction cache, and warps at unrelated program
+    // counters each stream it through on their own (profiles/r01_notes.md, capture A: 61 % of the
+    // stall samples were `no_instruction`).  Starting every bounce (and every shade) of a CTA's warps
+    // together makes one instruction-cache miss serve all of them.
+    bool warp_done = false;
     for (;;) {
+        if (A.cta_sync && !__syncthreads_or(!warp_done)) break;
+        bool run = !warp_done;
         unsigned dead = __ballot_sync(FULL, !alive);
-        if (dead == FULL || __popc(dead) >= A.regen_threshold) {
+        if (run && (dead == FULL || __popc(dead) >= A.regen_threshold)) {
             // ---- regeneration phase ---------------------------------------------------------------
             bool item_done = !alive && has_item && s_next >= s_stop;
             if (item_done) {
@@ -149,14 +157,21 @@ __global__ void __launch_bounds__(kRenderThreads, 2)
             }
             if (!__any_sync(FULL, alive)) {
                 bool pending = __any_sync(FULL, has_item);
-                if (!pending && exhausted && w_cur == w_end) break;
-                continue;
+                if (!pending && exhausted && w_cur == w_end) {
+                    if (!A.cta_sync) break;
+                    warp_done = true;
+                }
+                run = false;
             }
         }
         // ---- one ray + one bounce for every live path ---------------------------------------------
-        if (alive) {
+        Hit h;
+        if (run && alive) {
             if (COUNT) cnt.rays++;
-            Hit h = world_hit<F>(W, P.r, 0.001f, kFltMax, rng, tl);
+            h = world_hit<F>(W, P.r, 0.001f, kFltMax, rng, tl);
+        }
+        if (A.cta_sync >= 2) __syncthreads();
+        if (run && alive) {
             if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
                 V3 c = de_nan(P.L);  // col += de_nan(color(...)), Raytracing_n.cpp:841
                 sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);

@@ -161,3 +161,43 @@ def test_primary_hits_match_live_reference_full_size(oracle, gpu_ctx, name, nx, 
     worst = _check_hits(gid, gt, rid, rt)
     print(f"{name} {nx}x{ny}: {len(rid)} rays, ids exact, max rel t err {worst:.2e}")
     sc.close()
+
+
+def _read_p3(path):
+    tok = open(path).read().split()
+    assert tok[0] == "P3"
+    nx, ny, mx = int(tok[1]), int(tok[2]), int(tok[3])
+    return nx, ny, mx, np.array(tok[4:], np.int64).reshape(-1, 3)
+
+
+def test_python_crender_writes_the_reference_p3(gpu_ctx, tmp_path):
+    """render.CRender (mirror of Render.h:16-51): the P3 file of Raytracing_n.cpp:886, :873-876 holds
+    exactly what srt_render_image returns for the same parameters."""
+    world, hlist, cam = scenes.by_name("cornell")
+    path = str(tmp_path / "out.ppm")
+    r = render.CRender(50, 64, 64, 8, 8, path)
+    r.set_scene(world, hlist, cam)
+    img = r.Run()
+    nx, ny, mx, px = _read_p3(path)
+    assert (nx, ny, mx) == (64, 64, 255) and r.isfinished and r.finishedPixel == 64 * 64
+    assert np.array_equal(px, img.reshape(-1, 3).astype(np.int64))
+    sc = render.Scene.from_objects(gpu_ctx, world, hlist, cam)
+    again = sc.render_image(render.render_params(64, 64, 8))
+    sc.close()
+    assert np.array_equal(again, img)
+
+
+def test_cpp_crender_run_through_reference_headers(oracle, gpu_ctx, tmp_path):
+    """host/crender.hpp compiled against the UNMODIFIED reference headers (inside the oracle harness TU):
+    CRender(...).Run() on real reference objects -> C++ flattener -> libsrt_b200.so -> P3 file, equal
+    to the image the Python host renders from the mirrored scene (same flat scene, same seed)."""
+    world, hlist, cam = scenes.by_name("cornell")
+    rs = oracle.RefBuilder().realize(world, hlist, cam)
+    path = str(tmp_path / "cpp.ppm")
+    rs.crender_run(50, 64, 64, 8, ffi.BACKEND_PATH, path)
+    nx, ny, mx, px = _read_p3(path)
+    assert (nx, ny, mx) == (64, 64, 255)
+    sc = render.Scene.from_objects(gpu_ctx, world, hlist, cam)
+    img = sc.render_image(render.render_params(64, 64, 8))
+    sc.close()
+    assert np.array_equal(px, img.reshape(-1, 3).astype(np.int64))
