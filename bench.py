@@ -42,7 +42,8 @@ def config_of(name):
     from simple_raytracing_render_b200 import scenes
     nx, ny, ns = scenes.CONFIG_SIZES[name]
     label = {"cornell": "C1 Cornell box 512x512 @ 16 spp",
-             "spheres": "C2 random spheres (bvh_node) 1200x800 @ 64 spp"}[name]
+             "spheres": "C2 random spheres (bvh_node) 1200x800 @ 64 spp",
+             "teapot": "C3 Utah teapot 640k triangles (bvh_node), Beckmann, sky sphere 1024x1024 @ 256 spp"}[name]
     return nx, ny, ns, label
 
 
@@ -161,7 +162,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--config", default="spheres", choices=["spheres", "cornell"])
+    ap.add_argument("--config", default="spheres", choices=["spheres", "cornell", "teapot"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -252,7 +253,7 @@ def main():
         scratch = torch.zeros_like(accum)
         cnt = sc.render_counted(params, scratch)
     rpp = cnt["rays"] / max(cnt["paths"], 1)
-    prim_bytes = 16 if args.config == "spheres" else 20
+    prim_bytes = {"spheres": 16, "cornell": 20, "teapot": 48}[args.config]
     abytes, aflops = algorithmic_work(cnt, n_pixels, prim_bytes)
 
     # ---- e2e: HOST buffers through the C ABI, copies inside the timed region ----------------------

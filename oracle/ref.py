@@ -57,6 +57,7 @@ def lib():
         "ref_set_seed": (None, [C.c_uint64]),
         "ref_get_seed": (C.c_uint64, []),
         "ref_reset_pcg": (None, []),
+        "ref_probe_beckmann_stash": (C.c_float, [C.c_int]),
         "ref_kat_drand48": (None, [C.c_uint64, C.c_int, C.c_void_p]),
         "ref_kat_pcg32": (None, [C.c_int, C.c_void_p, C.c_void_p]),
         "ref_kat_sobol": (C.c_int, [C.c_uint, C.c_void_p]),
@@ -331,10 +332,18 @@ class RefBuilder:
         elif isinstance(o, S.hitable_list):
             hs = (C.c_int32 * max(1, len(o.list)))(*[self._hit(x) for x in o.list])
             h = L.ref_hitable_list(hs, len(o.list), o.list_size)
-        elif isinstance(o, S.teapot_bvh):
+        elif isinstance(o, S.teapot_bvh) and o.divs == 100:  # teapot.h:77 hard-codes divs = 100
             n = C.c_int32(0)
             L.ref_set_seed(int(o.seed_at_build))
             h = L.ref_teapot_bvh(float(o.scale), self._mat(o.mat), C.byref(n))
+        elif isinstance(o, S.triangle_soup):
+            # `new bvh_node(triangles, n, 0, 1)` over real triangle objects (Raytracing_n.cpp:286, :349)
+            m = self._mat(o.mat)
+            ids = np.empty(len(o.pos), np.int32)
+            for k in range(len(o.pos)):
+                ids[k] = L.ref_triangle(o.pos[k].ctypes.data, o.uv[k].ctypes.data, o.nrm[k].ctypes.data, m)
+            L.ref_set_seed(int(o.seed_at_build))
+            h = L.ref_bvh_node(ids.ctypes.data_as(C.POINTER(C.c_int32)), len(ids), 0.0, 1.0)
         elif isinstance(o, S.bvh_node):
             hs = (C.c_int32 * max(1, len(o.items)))(*[self._hit(x) for x in o.items])
             # the reference's constructor draws its split axes from the global drand48 stream

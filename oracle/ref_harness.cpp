@@ -202,6 +202,24 @@ void ref_sobol_fallback(unsigned N, double* out) {
     free_sobol(p, N);
 }
 
+// What beckmann_pdf::value returns before any generate() in THIS process: *pdf_value is a malloc(4)
+// block only generate() writes (pdf.h:121-135), so when the mixture picks the light branch first the
+// reference reads what the allocator left there — glibc's safe-linking residue of the block the
+// previous beckmann_pdf freed, (chunk address >> 12) ^ next.  Its value as a float depends on where
+// the heap lives: a low brk heap (non-PIE host such as this Python) gives a denormal (~0: the sample
+// counts in full), a PIE binary's 0x55.. heap gives ~1e13 (the sample counts for nothing).  The
+// tests read this probe so that the stand-in the backend uses (0) is checked against
+// what the oracle process really observes.
+float ref_probe_beckmann_stash(int) {
+    BeckmannDistribution d(0.1f, 0.1f, true);
+    float v = 0;
+    for (int i = 0; i < 3; i++) {
+        beckmann_pdf* p = new beckmann_pdf(&d, vec3(0, 1, 0));
+        v = p->value(vec3(0, -1, 0), vec3(0, 1, 0));
+        delete p;
+    }
+    return v;
+}
 float ref_kat_erf(float x) { return Erf(x); }
 float ref_kat_erfinv(float x) { return ErfInv(x); }
 float ref_kat_schlick(float c, float ri) { return schlick(c, ri); }

@@ -42,8 +42,13 @@ SRT_DEV View global_view(const DScene& S) { return View{S, S.entries, S.ops, S.d
 // The hot tables of the scene (entries, instance ops, primitive records, lights) are staged into
 // shared memory when the variant has F_SMEM_TABLES: every lane of a warp reads the same record at
 // the same time, which is a broadcast from shared memory.
+// resident CTAs per SM the register allocation is bounded for (srt_variants.h picks it per variant)
+#ifndef SRT_MINBLOCKS
+#define SRT_MINBLOCKS 2
+#endif
+
 template <uint32_t F, bool COUNT>
-__global__ void __launch_bounds__(kRenderThreads, 2)
+__global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
     k_render(DScene S, RenderArgs A, const uint32_t* __restrict__ sobol, float* __restrict__ out,
              unsigned long long* __restrict__ counters) {
     extern __shared__ float4 smem_hot[];

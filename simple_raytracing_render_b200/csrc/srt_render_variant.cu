@@ -1,11 +1,14 @@
 // srt_render_variant.cu — one instantiation of k_render; compiled SRT_N_VARIANTS times with
 // -DSRT_VARIANT=<n> (see srt_variants.h and __graft_entry__.build_backend).
-#include "srt_kernels.cuh"
-#include "srt_variants.h"
-
 #ifndef SRT_VARIANT
 #error "compile with -DSRT_VARIANT=<n>"
 #endif
+
+#include "srt_variants.h"
+#ifndef SRT_MINBLOCKS
+#define SRT_MINBLOCKS SRT_VARIANT_MINBLOCKS(SRT_VARIANT)
+#endif
+#include "srt_kernels.cuh"
 
 #define SRT_CAT2(a, b) a##b
 #define SRT_CAT(a, b) SRT_CAT2(a, b)

@@ -53,6 +53,11 @@ typedef cudaError_t (*RenderVariantFn)(const RenderLaunch& L, RenderVariantInfo*
      : (n) == 5 ? (SRT_VM_FULL)                              \
                 : (SRT_VM_FULL))
 #define SRT_VARIANT_COUNTING(n) ((n) == 6)
+// Resident CTAs per SM the register allocator is bounded for (__launch_bounds__).  Measured on B200
+// (profiles/r01_notes.md, capture C): the list and mesh kernels gain 30-40 % from 4 CTAs (64
+// registers, < 200 bytes of spills) because their stalls are fixed-latency waits and instruction
+// fetch that more warps hide; the sphere-BVH kernel spills ~1 KB at 64 registers and is best at 2.
+#define SRT_VARIANT_MINBLOCKS(n) ((n) == 1 ? 2 : 4)
 
 cudaError_t srt_render_variant_0(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_1(const RenderLaunch&, RenderVariantInfo*);

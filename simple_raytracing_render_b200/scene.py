@@ -391,14 +391,14 @@ class translate(hitable):  # hitable.h:35-61
 class rotate_y(hitable):  # hitable.h:65-107
     def __init__(self, p: hitable, angle):
         self.ptr, self.angle = p, f32(angle)
-        radians = (math.pi / 180.0) * float(self.angle)
+        radians = float(f32((math.pi / 180.0) * float(self.angle)))  # `float radians = (M_PI / 180.) * angle;`
         self.sin_theta, self.cos_theta = f32(math.sin(radians)), f32(math.cos(radians))
 
 
 class rotate_x(hitable):  # hitable.h:135-178
     def __init__(self, p: hitable, angle):
         self.ptr, self.angle = p, f32(angle)
-        radians = (math.pi / 180.0) * float(self.angle)
+        radians = float(f32((math.pi / 180.0) * float(self.angle)))  # `float radians = (M_PI / 180.) * angle;`
         self.sin_theta, self.cos_theta = f32(math.sin(radians)), f32(math.cos(radians))
 
 
@@ -547,7 +547,7 @@ class teapot_bvh(triangle_soup):
     """`new bvh_node(teapot(scale, mat).createPloyTeapot(), 640000, 0, 1)` (Raytracing_n.cpp:348-350)."""
 
     def __init__(self, scale, mat, divs: int = 100):
-        self.scale = f32(scale)
+        self.scale, self.divs = f32(scale), int(divs)
         super().__init__(teapot_triangles(scale, divs), mat)
 
 

@@ -17,9 +17,9 @@ import math
 import numpy as np
 
 from . import scene as S
-from .scene import (box, bvh_node, camera, checker_texture, constant_medium, constant_texture, dielectric,
-                    diffuse_light, flip_normals, hitable_list, image_texture, lambertian, metal, rotate_y,
-                    sphere, translate, vec3, xy_rect, xz_rect, yz_rect)
+from .scene import (beckmann, box, brdfmaterial, bvh_node, camera, checker_texture, constant_medium, constant_texture, dielectric,
+                    diffuse_light, flip_normals, hitable_list, image_texture, lambertian, metal, rotate_x, rotate_y,
+                    sphere, teapot_bvh, translate, triangle_soup, vec3, xy_rect, xz_rect, yz_rect)
 
 CONFIG_SIZES = {
     "cornell": (512, 512, 16),
@@ -85,8 +85,181 @@ def random_spheres(aspect: float = 1.5, seed: int = 1, grid: int = 11):
     return world, hlist, cam
 
 
+def synthetic_sky(nx: int = 1024, ny: int = 512) -> np.ndarray:
+    """Stand-in for contents/environment_map/sky_2.png (2000x1000 RGB8; the asset cannot travel to the
+    GPU box): a deterministic RGB8 sky — vertical gradient, a soft sun lobe and low-frequency bands — so
+    that image_texture::value (texture.h:58-70) has real texel variation to fetch."""
+    v = (np.arange(ny, dtype=np.float64) + 0.5) / ny  # row 0 = top of the image = v -> 1
+    u = (np.arange(nx, dtype=np.float64) + 0.5) / nx
+    up = 1.0 - v[:, None]
+    base = np.stack([0.35 + 0.45 * (1 - up) + 0 * u[None, :], 0.55 + 0.30 * (1 - up) + 0 * u[None, :],
+                     0.95 - 0.15 * (1 - up) + 0 * u[None, :]], -1)
+    sun = np.exp(-(((u[None, :] - 0.3) * 2.0) ** 2 + ((v[:, None] - 0.25) * 4.0) ** 2) * 18.0)
+    bands = 0.06 * np.sin(u[None, :] * 2 * np.pi * 5.0) * np.sin(v[:, None] * np.pi * 3.0)
+    img = base + sun[..., None] * np.array([0.6, 0.5, 0.3]) + bands[..., None]
+    ground = v[:, None] > 0.55
+    img = np.where(ground[..., None], img * np.array([0.45, 0.42, 0.38]), img)
+    return np.clip(img * 255.0 + 0.5, 0, 255).astype(np.uint8)
+
+
+def teapot_beckmann(aspect: float = 1.0, divs: int = 100, seed: int = 1):
+    """C3: teapot_scene (Raytracing_n.cpp:306-377) reduced to what BASELINE.json names —
+    the procedural Utah teapot (teapot.h, 32 x divs x divs x 2 triangles; 640 000 at divs = 100) with the
+    reference's gold Beckmann material in a bvh_node under rotate_x / translate, the lambertian floor, the
+    sampled flipped xz_rect light and the image-textured sky sphere around the camera."""
+    S.set_seed(seed)
+    lookfrom = vec3(100, 800, -400)
+    gold = beckmann(constant_texture(vec3(0.945, 0.75, 0.336)), 0.01, 0.05)
+    brown = lambertian(constant_texture(vec3(0.426, 0.3, 0.254)))
+    light = diffuse_light(constant_texture(vec3(40, 40, 40)))
+    sky = diffuse_light(image_texture(synthetic_sky()))
+    lst = [
+        flip_normals(xz_rect(3, 153, 217, 343, 800, light)),
+        xz_rect(0, 555, 0, 555, 0, brown),
+        flip_normals(sphere(lookfrom, 10000, sky)),
+        translate(rotate_x(teapot_bvh(40, gold, divs), 90), vec3(200, 0, 250)),
+    ]
+    world = hitable_list(lst, len(lst))
+    hlist = hitable_list([flip_normals(xz_rect(3, 153, 217, 343, 800, None))], 1)
+    cam = camera(lookfrom, vec3(300, 278, 200), vec3(0, 1, 0), 40.0, aspect, 0.0, 10.0, 0.0, 1.0)
+    return world, hlist, cam
+
+
+def synthetic_merl_table() -> np.ndarray:
+    """Stand-in for contents/brdfs/aluminium.binary (absent from the reference tree,
+    .MISSING_LARGE_BLOBS): a smooth metallic lobe in the MERL layout of brdf.h:171-184 —
+    [channel 3][theta_half 90][theta_diff 90][phi_diff 180] doubles, pre-scale (brdf.h:12-14)."""
+    th = (np.arange(90, dtype=np.float64) + 0.5) ** 2 / 90.0 / 90.0 * (np.pi / 2)  # theta_half_index is sqrt-spaced
+    td = (np.arange(90, dtype=np.float64) + 0.5) / 90.0 * (np.pi / 2)
+    pd = (np.arange(180, dtype=np.float64) + 0.5) / 180.0 * np.pi
+    lobe = np.exp(-(th[:, None, None] / 0.12) ** 2) * 40.0 + 0.35
+    fres = 1.0 + 2.5 * (1.0 - np.cos(td))[None, :, None] ** 5
+    aniso = 1.0 + 0.05 * np.cos(2 * pd)[None, None, :]
+    base = lobe * fres * aniso
+    tab = np.stack([base * 1500.0 / 1.0 * 0.91, base * 1500.0 / 1.15 * 0.92, base * 1500.0 / 1.66 * 0.93])
+    return np.ascontiguousarray(tab.reshape(-1), np.float64)
+
+
+def _ellipsoid(center, radii, nu, nv, uv_lo, uv_hi):
+    """UV-sphere tessellation: positions [n][9], smooth normals [n][9], uvs [n][6]."""
+    cx, cy, cz = center
+    rx, ry, rz = radii
+    u = np.linspace(0.0, 2 * np.pi, nu + 1)
+    v = np.linspace(0.0, np.pi, nv + 1)
+    uu, vv = np.meshgrid(u, v, indexing="ij")
+    n = np.stack([np.cos(uu) * np.sin(vv), np.cos(vv), np.sin(uu) * np.sin(vv)], -1)
+    p = n * np.array([rx, ry, rz]) + np.array([cx, cy, cz])
+    nn = n / np.array([rx, ry, rz])
+    nn = nn / np.maximum(np.linalg.norm(nn, axis=-1, keepdims=True), 1e-20)
+    tu = uv_lo[0] + (uv_hi[0] - uv_lo[0]) * (uu / (2 * np.pi))
+    tv = uv_lo[1] + (uv_hi[1] - uv_lo[1]) * (vv / np.pi)
+    t = np.stack([tu, tv], -1)
+    i, j = np.meshgrid(np.arange(nu), np.arange(nv), indexing="ij")
+    i, j = i.reshape(-1), j.reshape(-1)
+    quads = [(i, j), (i + 1, j), (i + 1, j + 1), (i, j + 1)]
+    tris = [(0, 1, 2), (0, 2, 3)]
+    pos, nrm, uv = [], [], []
+    for a, b, c in tris:
+        pos.append(np.concatenate([p[quads[k]] for k in (a, b, c)], -1))
+        nrm.append(np.concatenate([nn[quads[k]] for k in (a, b, c)], -1))
+        uv.append(np.concatenate([t[quads[k]] for k in (a, b, c)], -1))
+    pos, nrm, uv = np.concatenate(pos), np.concatenate(nrm), np.concatenate(uv)
+    # drop the degenerate pole triangles (zero area: the reference's det test rejects them anyway)
+    e1, e2 = pos[:, 3:6] - pos[:, 0:3], pos[:, 6:9] - pos[:, 0:3]
+    keep = np.linalg.norm(np.cross(e1, e2), axis=1) > 1e-9
+    return pos[keep].astype(np.float32), nrm[keep].astype(np.float32), uv[keep].astype(np.float32)
+
+
+def figure_mesh(detail: int = 12):
+    """Stand-in for mesh[0] of contents/models/Soilder.FBX (~3.3 k triangles; assimp is a Windows binary,
+    SURVEY.md §8c): a standing figure of tessellated ellipsoids with smooth normals and atlas uvs."""
+    parts = [  # centre, radii, uv window
+        ((0, 62, 0), (5.0, 6.0, 5.0), (0.0, 0.0), (0.5, 0.25)),      # head
+        ((0, 42, 0), (9.0, 14.0, 6.0), (0.0, 0.25), (1.0, 0.75)),    # torso
+        ((-12, 44, 0), (3.0, 13.0, 3.0), (0.5, 0.0), (0.75, 0.25)),  # arms
+        ((12, 44, 0), (3.0, 13.0, 3.0), (0.75, 0.0), (1.0, 0.25)),
+        ((-5, 14, 0), (4.0, 15.0, 4.0), (0.0, 0.75), (0.5, 1.0)),    # legs
+        ((5, 14, 0), (4.0, 15.0, 4.0), (0.5, 0.75), (1.0, 1.0)),
+    ]
+    out = [_ellipsoid(c, r, 2 * detail, detail, lo, hi) for c, r, lo, hi in parts]
+    return tuple(np.concatenate([o[k] for o in out]) for k in range(3))
+
+
+def synthetic_albedo(n: int = 512) -> np.ndarray:
+    """Stand-in for contents/textures/NPC_YuanChengBing_A.png (1024x1024 RGB8)."""
+    y, x = np.mgrid[0:n, 0:n].astype(np.float64) / n
+    r = 0.45 + 0.35 * np.sin(x * 17.0) * np.cos(y * 11.0)
+    g = 0.40 + 0.30 * np.cos(x * 7.0 + y * 13.0)
+    b = 0.35 + 0.25 * np.sin((x + y) * 23.0)
+    return np.clip(np.stack([r, g, b], -1) * 255.0 + 0.5, 0, 255).astype(np.uint8)
+
+
+def soldier_like(aspect: float = 16.0 / 9.0, detail: int = 12, seed: int = 1):
+    """C4: soldier_scene (Raytracing_n.cpp:585-657) — textured Beckmann mesh in a
+    bvh_node under rotate_y / translate, sky-sphere environment map, glass slab, sampled xz_rect light —
+    with the floor given the MERL measured-BRDF material (brdfmaterial) as BASELINE.json:configs[3]
+    asks.  Assets that cannot travel are deterministic stand-ins of the same kind and layout."""
+    S.set_seed(seed)
+    lookfrom = vec3(300, 500, -800)
+    light_1 = diffuse_light(constant_texture(vec3(35, 35, 35)))
+    floor = brdfmaterial(synthetic_merl_table(), vec3(0.7, 0.7, 0.72))
+    glass = dielectric(1.4)
+    sky = diffuse_light(image_texture(synthetic_sky(2048, 1024)))
+    skin = beckmann(image_texture(synthetic_albedo()), 0.9, 0.85)
+    pos, nrm, uv = figure_mesh(detail)
+    pos = (pos * np.float32(8.0)).astype(np.float32)  # model(..., vec3(8, 8, 8))
+    lst = [
+        flip_normals(xz_rect(203, 353, 17, 167, 800, light_1)),
+        box(vec3(0, -0.1, 0), vec3(600, 0.1, 600), floor),
+        box(vec3(0, -1, 0), vec3(600, 1, 600), glass),
+        flip_normals(sphere(lookfrom, 10000, sky)),
+        translate(rotate_y(triangle_soup(pos, skin, uv=uv, nrm=nrm), 180), vec3(250, 0, 300)),
+    ]
+    world = hitable_list(lst, len(lst))
+    hlist = hitable_list([flip_normals(xz_rect(203, 353, 17, 167, 800, None))], 1)
+    cam = camera(lookfrom, vec3(300, 278, 200), vec3(0, 1, 0), 40.0, aspect, 10.0, 1000.0, 0.0, 1.0)
+    return world, hlist, cam
+
+
+def terrain_triangles(n_side: int) -> np.ndarray:
+    """2 * n_side^2 triangles of a tessellated height field over [0, 555]^2 (positions [n][9])."""
+    g = np.linspace(0.0, 555.0, n_side + 1)
+    x, z = np.meshgrid(g, g, indexing="ij")
+    y = (40.0 * np.sin(x * 0.021) * np.cos(z * 0.017) + 12.0 * np.sin(x * 0.13 + 1.0) * np.sin(z * 0.11)
+         + 3.0 * np.sin(x * 0.9) * np.cos(z * 0.7) + 60.0)
+    p = np.stack([x, y, z], -1).astype(np.float32)
+    a, b, c, d = p[:-1, :-1], p[1:, :-1], p[1:, 1:], p[:-1, 1:]
+    t0 = np.concatenate([a, c, b], -1).reshape(-1, 9)  # counter-clockwise seen from +y
+    t1 = np.concatenate([a, d, c], -1).reshape(-1, 9)
+    return np.concatenate([t0, t1]).astype(np.float32)
+
+
+def tessellated_medium(aspect: float = 16.0 / 9.0, n_side: int = 512, seed: int = 1):
+    """C5 (SURVEY.md §8d): a tessellated triangle scene (2 * n_side^2 triangles in one bvh_node;
+    n_side = 2237 gives the 10 M of BASELINE.json:configs[4]) plus a constant_medium volume, lit by a
+    sampled xz_rect light and a constant sky."""
+    S.set_seed(seed)
+    ground = lambertian(constant_texture(vec3(0.48, 0.63, 0.36)))
+    light = diffuse_light(constant_texture(vec3(25, 25, 25)))
+    sky = diffuse_light(constant_texture(vec3(0.35, 0.45, 0.7)))
+    lookfrom = vec3(278, 420, -600)
+    fog_boundary = sphere(vec3(300, 150, 280), 110, dielectric(1.5))
+    lst = [
+        flip_normals(xz_rect(123, 423, 147, 412, 700, light)),
+        flip_normals(sphere(lookfrom, 10000, sky)),
+        triangle_soup(terrain_triangles(n_side), ground),
+        fog_boundary,
+        constant_medium(fog_boundary, 0.01, constant_texture(vec3(0.9, 0.9, 0.95))),
+    ]
+    world = hitable_list(lst, len(lst))
+    hlist = hitable_list([flip_normals(xz_rect(123, 423, 147, 412, 700, None))], 1)
+    cam = camera(lookfrom, vec3(278, 120, 278), vec3(0, 1, 0), 40.0, aspect, 0.0, 10.0, 0.0, 1.0)
+    return world, hlist, cam
+
+
 def by_name(name: str, **kw):
-    fn = {"cornell": cornell_box_classic, "spheres": random_spheres}.get(name)
+    fn = {"cornell": cornell_box_classic, "spheres": random_spheres, "teapot": teapot_beckmann,
+          "soldier": soldier_like, "tessellated": tessellated_medium}.get(name)
     if fn is None:
         raise KeyError(name)
     nx, ny, _ = CONFIG_SIZES[name]

@@ -37,3 +37,21 @@ def gpu_ctx(backend_lib):
     ctx = render.Context(0)
     yield ctx
     ctx.close()
+
+
+_SCENES, _REF_SCENES = {}, {}
+
+
+def get_scene(name):
+    """(world, hlist, cam) of a named config, built once per session (the teapot takes seconds)."""
+    if name not in _SCENES:
+        from simple_raytracing_render_b200 import scenes
+        _SCENES[name] = scenes.by_name(name)
+    return _SCENES[name]
+
+
+def get_ref_scene(ref, name):
+    """The same scene as REAL reference objects (oracle), realised once per session."""
+    if name not in _REF_SCENES:
+        _REF_SCENES[name] = ref.RefBuilder().realize(*get_scene(name))
+    return _REF_SCENES[name]

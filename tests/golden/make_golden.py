@@ -59,6 +59,13 @@ def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny):
 
 
 if __name__ == "__main__":
+    only = sys.argv[1:]
+    if only:
+        cfg = {"cornell": (64, 64, 2, 4096, 48, 48), "spheres": (96, 64, 2, 16384, 48, 32), "teapot": (96, 96, 1, 4096, 40, 40)}
+        for name in only:
+            scene_vectors(name, *cfg[name])
+        sys.exit(0)
     kats()
     scene_vectors("cornell", 64, 64, 2, 4096, 48, 48)
     scene_vectors("spheres", 96, 64, 2, 16384, 48, 32)
+    scene_vectors("teapot", 96, 96, 1, 4096, 40, 40)

@@ -6,9 +6,10 @@ import pytest
 from simple_raytracing_render_b200 import ffi, scene as S, scenes
 
 
-@pytest.mark.parametrize("name", ["cornell", "spheres"])
-def test_python_and_cpp_flatteners_agree(oracle, name):
-    world, hlist, cam = scenes.by_name(name)
+@pytest.mark.parametrize("name,kw", [("cornell", {}), ("spheres", {}), ("teapot", {"divs": 12}),
+                                     ("soldier", {"detail": 4}), ("tessellated", {"n_side": 16})])
+def test_python_and_cpp_flatteners_agree(oracle, name, kw):
+    world, hlist, cam = scenes.by_name(name, **kw)
     mine = S.flatten(world, hlist, cam)
     theirs = oracle.RefBuilder().realize(world, hlist, cam).flat()
     assert mine.equal(theirs) == []

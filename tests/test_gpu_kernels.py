@@ -6,6 +6,7 @@ import os
 import numpy as np
 import pytest
 
+from conftest import get_ref_scene, get_scene
 from simple_raytracing_render_b200 import ffi, render, scenes, scene as S
 
 pytestmark = pytest.mark.gpu
@@ -45,16 +46,19 @@ def test_hoisted_reciprocal_division_is_ieee_exact(gpu_ctx):
     assert total_bad == 0
 
 
-@pytest.mark.parametrize("name", ["cornell", "spheres"])
+@pytest.mark.parametrize("name", ["cornell", "spheres", "teapot"])
 def test_random_rays_match_live_reference(oracle, gpu_ctx, name):
     """1M rays from random points inside the scene in random (un-normalised) directions."""
-    world, hlist, cam = scenes.by_name(name)
-    rs = oracle.RefBuilder().realize(world, hlist, cam)
+    world, hlist, cam = get_scene(name)
+    rs = get_ref_scene(oracle, name)
     sc = render.Scene.from_objects(gpu_ctx, world, hlist, cam)
     rng = np.random.default_rng(5)
     n = 1_000_000
     if name == "cornell":
         o = rng.uniform(1, 554, size=(n, 3))
+    elif name == "teapot":  # around and inside the 640 000-triangle teapot (reference: ~0.3 Mrays/s)
+        n = 300_000
+        o = rng.uniform([60, 1, 100], [340, 260, 400], size=(n, 3))
     else:
         o = rng.uniform([-12, 0.05, -12], [12, 4, 12], size=(n, 3))
     d = rng.standard_normal((n, 3)) * rng.uniform(0.1, 50, size=(n, 1))

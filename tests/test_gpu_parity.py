@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import GOLDEN
+from conftest import GOLDEN, get_ref_scene, get_scene
 from simple_raytracing_render_b200 import ffi, render, scenes, scene as S
 
 pytestmark = pytest.mark.gpu
@@ -27,11 +27,11 @@ def rel_mse(x, r):
     return float(np.mean((x - r) ** 2 / (r ** 2 + 1e-2)))
 
 
-@pytest.fixture(scope="module", params=["cornell", "spheres"])
+@pytest.fixture(scope="module", params=["cornell", "spheres", "teapot"])
 def golden_scene(request, gpu_ctx):
     name = request.param
     g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
-    sc = render.Scene.from_objects(gpu_ctx, *scenes.by_name(name))
+    sc = render.Scene.from_objects(gpu_ctx, *get_scene(name))
     yield name, g, sc
     sc.close()
 
@@ -150,10 +150,9 @@ def test_counters_are_consistent(golden_scene):
 
 
 # ---- live oracle (oracle/_ref/libsrt_ref.so travelled with the snapshot) ---------------------------
-@pytest.mark.parametrize("name,nx,ny", [("cornell", 512, 512), ("spheres", 600, 400)])
+@pytest.mark.parametrize("name,nx,ny", [("cornell", 512, 512), ("spheres", 600, 400), ("teapot", 512, 512)])
 def test_primary_hits_match_live_reference_full_size(oracle, gpu_ctx, name, nx, ny):
-    world, hlist, cam = scenes.by_name(name)
-    rs = oracle.RefBuilder().realize(world, hlist, cam)
+    rs = get_ref_scene(oracle, name)
     sc = render.Scene.from_desc_address(gpu_ctx, rs.desc_address())  # the C++ flattener's output
     rays = rs.primary_rays(nx, ny, 1, seed=7, mod_ny=nx == ny)
     rid, rt, _ = rs.trace(rays, want_rec=False)

@@ -82,12 +82,22 @@ def test_closed_form_helpers_pinned(oracle, kats):
 def test_golden_scene_vectors_match_live_reference(oracle):
     """The committed closest-hit vectors are what the reference computes today."""
     from simple_raytracing_render_b200 import scenes
-    for name in ("cornell", "spheres"):
+    from conftest import get_ref_scene
+    for name in ("cornell", "spheres", "teapot"):
         g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
-        rs = oracle.RefBuilder().realize(*scenes.by_name(name))
+        rs = get_ref_scene(oracle, name)
         n = 2000
         ids, t, rec = rs.trace(g["rays"][:n])
         assert np.array_equal(ids, g["ids"][:n])
         assert np.array_equal(t, g["t"][:n])
         lp = rs.light_pdf(g["light_od"][:n])
         assert np.array_equal(lp, g["light_pdf"][:n])
+
+
+def test_uninitialised_beckmann_pdf_reads_about_zero_in_this_process(oracle):
+    """pdf.h:133-135 before any generate(): undefined behaviour in the reference.  The backend's
+    stand-in is 0 (srt_microfacet.cuh: kBeckmannStashInit); the golden teapot image was rendered by an
+    oracle process that observed a denormal.  If the allocator of this process behaves differently the
+    Beckmann image comparison is meaningless: fail here, loudly, instead."""
+    v = float(oracle.lib().ref_probe_beckmann_stash(0))
+    assert abs(v) < 1e-30, f"oracle process reads {v!r} from an unwritten beckmann_pdf::pdf_value"

@@ -2,7 +2,7 @@
 # A/B harness for kernel experiments on the GPU box: tools/ab_bench.sh <tag> [ENV=VAL ...]
 # prints one line per config with the kernel time bench.py measured.
 tag=$1; shift
-for cfg in spheres cornell; do
+for cfg in ${SRT_AB_CONFIGS:-spheres cornell}; do
   env "$@" python bench.py --config $cfg --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/ab_${tag}_${cfg}.json 2> gpurun_out/ab_${tag}_${cfg}.err
   python - "$tag" "$cfg" <<'PY'
 import json,sys
