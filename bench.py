@@ -43,7 +43,9 @@ def config_of(name):
     nx, ny, ns = scenes.CONFIG_SIZES[name]
     label = {"cornell": "C1 Cornell box 512x512 @ 16 spp",
              "spheres": "C2 random spheres (bvh_node) 1200x800 @ 64 spp",
-             "teapot": "C3 Utah teapot 640k triangles (bvh_node), Beckmann, sky sphere 1024x1024 @ 256 spp"}[name]
+             "teapot": "C3 Utah teapot 640k triangles (bvh_node), Beckmann, sky sphere 1024x1024 @ 256 spp",
+             "soldier": "C4-like textured Beckmann mesh + env map + MERL-material floor + glass 1920x1080 @ 1024 spp",
+             "tessellated": "C5-like tessellated terrain (2 x 512^2 triangles) + constant_medium 3840x2160 @ 256 spp"}[name]
     return nx, ny, ns, label
 
 
@@ -162,7 +164,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--config", default="spheres", choices=["spheres", "cornell", "teapot"])
+    ap.add_argument("--config", default="spheres", choices=["spheres", "cornell", "teapot", "soldier", "tessellated"])
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
@@ -253,7 +255,7 @@ def main():
         scratch = torch.zeros_like(accum)
         cnt = sc.render_counted(params, scratch)
     rpp = cnt["rays"] / max(cnt["paths"], 1)
-    prim_bytes = {"spheres": 16, "cornell": 20, "teapot": 48}[args.config]
+    prim_bytes = {"spheres": 16, "cornell": 20, "teapot": 48, "soldier": 48, "tessellated": 48}[args.config]
     abytes, aflops = algorithmic_work(cnt, n_pixels, prim_bytes)
 
     # ---- e2e: HOST buffers through the C ABI, copies inside the timed region ----------------------

@@ -58,6 +58,7 @@ def lib():
         "ref_get_seed": (C.c_uint64, []),
         "ref_reset_pcg": (None, []),
         "ref_probe_beckmann_stash": (C.c_float, [C.c_int]),
+        "ref_merl_lookup": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
         "ref_kat_drand48": (None, [C.c_uint64, C.c_int, C.c_void_p]),
         "ref_kat_pcg32": (None, [C.c_int, C.c_void_p, C.c_void_p]),
         "ref_kat_sobol": (C.c_int, [C.c_uint, C.c_void_p]),
@@ -215,6 +216,17 @@ class RefScene:
         if rc != 0:
             raise RuntimeError(f"CRender::Run failed ({rc}): {_err()}")
         return rc
+
+
+def merl_lookup(mat, angles: np.ndarray) -> np.ndarray:
+    """The reference's brdf::lookup_brdf_val on the table of a mirror `brdfmaterial` (scene.py)."""
+    b = RefBuilder()
+    h = b._mat(mat)
+    angles = np.ascontiguousarray(angles, np.float64).reshape(-1, 4)
+    out = np.zeros((len(angles), 3), np.float64)
+    if lib().ref_merl_lookup(h, angles.ctypes.data, len(angles), out.ctypes.data) != 0:
+        raise RuntimeError("not a brdfmaterial")
+    return out
 
 
 def named_scene(name: str, aspect: float) -> RefScene:

@@ -244,10 +244,38 @@ int ref_mat_metal(float r, float g, float b, float fuzz) { return put(K_MAT, new
 int ref_mat_dielectric(float ri) { return put(K_MAT, new dielectric(ri)); }
 int ref_mat_diffuse_light(int tex) { return put(K_MAT, new diffuse_light(get<texture>(tex, K_TEX))); }
 int ref_mat_isotropic(int tex) { return put(K_MAT, new isotropic(get<texture>(tex, K_TEX))); }
+// brdfmaterial::scatter (material.h:214-236) returns a non-specular record WITHOUT setting
+// srec.pdf_ptr (the assignment at :234 is commented out): color() then calls generate / value through
+// an uninitialised pointer and deletes it — the reference crashes (or reuses a freed cosine_pdf) on
+// the first hit.  To have a defined oracle the harness completes the record with the cosine_pdf every
+// other diffuse material supplies (material.h:109); everything else, including the discarded MERL
+// lookup, is the reference's own scatter().  The backend documents the same stand-in.
+class brdfmaterial_defined : public brdfmaterial {
+   public:
+    brdfmaterial_defined(const char* file, const vec3& a) : brdfmaterial(file, a) {}
+    virtual bool scatter(const ray& r_in, const hit_record& hrec, scatter_record& srec) const {
+        bool ok = brdfmaterial::scatter(r_in, hrec, srec);
+        srec.pdf_ptr = new cosine_pdf(hrec.normal);
+        return ok;
+    }
+};
+
 int ref_mat_brdf(const char* file, float r, float g, float b) {
     CoutSilencer quiet;
-    brdfmaterial* m = new brdfmaterial(file, vec3(r, g, b));
+    brdfmaterial* m = new brdfmaterial_defined(file, vec3(r, g, b));
     return put(K_MAT, m);
+}
+
+// brdf::lookup_brdf_val (brdf.h:190-214) on the table a brdfmaterial loaded: angles [n][4] =
+// theta_in, fi_in, theta_out, fi_out; rgb [n][3].
+int ref_merl_lookup(int mat, const double* angles, int64_t n, double* rgb) {
+    brdfmaterial* m = dynamic_cast<brdfmaterial*>(get<material>(mat, K_MAT));
+    if (!m) return -1;
+    CoutSilencer quiet;  // "Below horizon." (brdf.h:211-212)
+    for (int64_t i = 0; i < n; i++)
+        m->brdf_reader->lookup_brdf_val(m->brdf_data, angles[4 * i], angles[4 * i + 1], angles[4 * i + 2],
+                                        angles[4 * i + 3], rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]);
+    return 0;
 }
 
 int ref_sphere(float x, float y, float z, float r, int mat) {

@@ -234,7 +234,7 @@ def terrain_triangles(n_side: int) -> np.ndarray:
     return np.concatenate([t0, t1]).astype(np.float32)
 
 
-def tessellated_medium(aspect: float = 16.0 / 9.0, n_side: int = 512, seed: int = 1):
+def tessellated_medium(aspect: float = 16.0 / 9.0, n_side: int = 512, seed: int = 1, fog: bool = True):
     """C5 (SURVEY.md §8d): a tessellated triangle scene (2 * n_side^2 triangles in one bvh_node;
     n_side = 2237 gives the 10 M of BASELINE.json:configs[4]) plus a constant_medium volume, lit by a
     sampled xz_rect light and a constant sky."""
@@ -249,8 +249,9 @@ def tessellated_medium(aspect: float = 16.0 / 9.0, n_side: int = 512, seed: int 
         flip_normals(sphere(lookfrom, 10000, sky)),
         triangle_soup(terrain_triangles(n_side), ground),
         fog_boundary,
-        constant_medium(fog_boundary, 0.01, constant_texture(vec3(0.9, 0.9, 0.95))),
     ]
+    if fog:  # constant_medium::hit draws its free-flight distance at random: closest-hit parity is checked without it
+        lst.append(constant_medium(fog_boundary, 0.01, constant_texture(vec3(0.9, 0.9, 0.95))))
     world = hitable_list(lst, len(lst))
     hlist = hitable_list([flip_normals(xz_rect(123, 423, 147, 412, 700, None))], 1)
     cam = camera(lookfrom, vec3(278, 120, 278), vec3(0, 1, 0), 40.0, aspect, 0.0, 10.0, 0.0, 1.0)

@@ -41,13 +41,24 @@ def gpu_ctx(backend_lib):
 
 _SCENES, _REF_SCENES = {}, {}
 
+# the sizes the golden vectors were made at (tests/golden/make_golden.py); "<name>:trace" is the variant
+# closest-hit vectors use when the scene holds a constant_medium (its hits are random)
+SCENE_KW = {
+    "tessellated": {"n_side": 128},
+    "tessellated:trace": {"n_side": 128, "fog": False},
+}
+
 
 def get_scene(name):
     """(world, hlist, cam) of a named config, built once per session (the teapot takes seconds)."""
     if name not in _SCENES:
         from simple_raytracing_render_b200 import scenes
-        _SCENES[name] = scenes.by_name(name)
+        _SCENES[name] = scenes.by_name(name.split(":")[0], **SCENE_KW.get(name, {}))
     return _SCENES[name]
+
+
+def trace_name(name):
+    return name + ":trace" if name + ":trace" in SCENE_KW else name
 
 
 def get_ref_scene(ref, name):

@@ -15,6 +15,8 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 ROOT = os.path.dirname(os.path.dirname(HERE))
 sys.path.insert(0, ROOT)
 
+sys.path.insert(0, os.path.dirname(HERE))
+from conftest import get_scene, trace_name  # noqa: E402
 from oracle import ref  # noqa: E402
 from simple_raytracing_render_b200 import scenes  # noqa: E402
 
@@ -34,9 +36,26 @@ def kats():
              r2a=np.array([L.ref_kat_roughness_to_alpha(r) for r in (0.0005, 0.01, 0.05, 0.3, 1.0)], np.float32))
 
 
+def merl_angles(n=4096, seed=11):
+    rng = np.random.default_rng(seed)
+    a = np.stack([rng.uniform(0, np.pi / 2, n), rng.uniform(0, 2 * np.pi, n),
+                  rng.uniform(0, np.pi / 2, n), rng.uniform(0, 2 * np.pi, n)], 1)
+    a[: n // 8, 2:] = a[: n // 8, :2]  # brdfmaterial::scatter looks up (theta_in, phi_in) twice (material.h:231)
+    return a
+
+
+def merl_kat():
+    """brdf::lookup_brdf_val (brdf.h:190-214) of the reference on the synthetic MERL-layout table."""
+    from simple_raytracing_render_b200 import scene as S
+    m = S.brdfmaterial(scenes.synthetic_merl_table(), S.vec3(0.7, 0.7, 0.7))
+    a = merl_angles()
+    np.savez_compressed(os.path.join(HERE, "merl.npz"), angles=a, rgb=ref.merl_lookup(m, a))
+
+
 def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny):
-    world, hlist, cam = scenes.by_name(name)
-    rs = ref.RefBuilder().realize(world, hlist, cam)
+    world, hlist, cam = get_scene(name)
+    rs_img = ref.RefBuilder().realize(world, hlist, cam)
+    rs = rs_img if trace_name(name) == name else ref.RefBuilder().realize(*get_scene(trace_name(name)))
     mod_ny = nx == ny
     rays = rs.primary_rays(nx, ny, ns_rays, seed=1, mod_ny=mod_ny)
     ids, t, rec = rs.trace(rays)
@@ -49,7 +68,7 @@ def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny):
     ids2, t2, rec2 = rs.trace(rays2)
     od = np.concatenate([o, d], 1).astype(np.float32)
     lp = rs.light_pdf(od)
-    img, nrays = rs.render_float(img_nx, img_ny, ns_img, mod_ny=img_nx == img_ny)
+    img, nrays = rs_img.render_float(img_nx, img_ny, ns_img, mod_ny=img_nx == img_ny)
     np.savez_compressed(os.path.join(HERE, f"{name}.npz"), nx=nx, ny=ny, ns_rays=ns_rays,
                         rays=rays, ids=ids, t=t, rec=rec, rays2=rays2, ids2=ids2, t2=t2, rec2=rec2,
                         light_od=od, light_pdf=lp, img=img / ns_img, img_nx=img_nx, img_ny=img_ny, img_ns=ns_img,
@@ -60,12 +79,19 @@ def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny):
 
 if __name__ == "__main__":
     only = sys.argv[1:]
+    if only == ["merl"]:
+        merl_kat()
+        sys.exit(0)
     if only:
-        cfg = {"cornell": (64, 64, 2, 4096, 48, 48), "spheres": (96, 64, 2, 16384, 48, 32), "teapot": (96, 96, 1, 4096, 40, 40)}
+        cfg = {"cornell": (64, 64, 2, 4096, 48, 48), "spheres": (96, 64, 2, 16384, 48, 32), "teapot": (96, 96, 1, 4096, 40, 40),
+               "soldier": (96, 54, 2, 4096, 48, 27), "tessellated": (96, 54, 2, 4096, 48, 27)}
         for name in only:
             scene_vectors(name, *cfg[name])
         sys.exit(0)
     kats()
+    merl_kat()
     scene_vectors("cornell", 64, 64, 2, 4096, 48, 48)
     scene_vectors("spheres", 96, 64, 2, 16384, 48, 32)
     scene_vectors("teapot", 96, 96, 1, 4096, 40, 40)
+    scene_vectors("soldier", 96, 54, 2, 4096, 48, 27)
+    scene_vectors("tessellated", 96, 54, 2, 4096, 48, 27)

@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import GOLDEN, get_ref_scene, get_scene
+from conftest import GOLDEN, get_ref_scene, get_scene, trace_name
 from simple_raytracing_render_b200 import ffi, render, scenes, scene as S
 
 pytestmark = pytest.mark.gpu
@@ -27,13 +27,26 @@ def rel_mse(x, r):
     return float(np.mean((x - r) ** 2 / (r ** 2 + 1e-2)))
 
 
-@pytest.fixture(scope="module", params=["cornell", "spheres", "teapot"])
+@pytest.fixture(scope="module", params=["cornell", "spheres", "teapot", "soldier", "tessellated"])
 def golden_scene(request, gpu_ctx):
     name = request.param
     g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
     sc = render.Scene.from_objects(gpu_ctx, *get_scene(name))
     yield name, g, sc
     sc.close()
+
+
+@pytest.fixture(scope="module")
+def trace_scene(golden_scene, gpu_ctx):
+    """The scene the closest-hit vectors were made on: the same one, or — when it holds a
+    constant_medium, whose hits are random (constant_medium.h:19-50) — its twin without the medium."""
+    name, g, sc = golden_scene
+    if trace_name(name) == name:
+        yield name, g, sc
+        return
+    sc2 = render.Scene.from_objects(gpu_ctx, *get_scene(trace_name(name)))
+    yield name, g, sc2
+    sc2.close()
 
 
 def _check_hits(gid, gt, rid, rt):
@@ -44,8 +57,8 @@ def _check_hits(gid, gt, rid, rt):
     return float(rel.max()) if rel.size else 0.0
 
 
-def test_primary_hits_match_golden(golden_scene):
-    name, g, sc = golden_scene
+def test_primary_hits_match_golden(trace_scene):
+    name, g, sc = trace_scene
     gid, gt, grec = sc.trace_closest(g["rays"])
     _check_hits(gid, gt, g["ids"], g["t"])
     # the whole hit_record (u, v, p, normal) of hitable.h:17-25
@@ -53,24 +66,24 @@ def test_primary_hits_match_golden(golden_scene):
     assert np.allclose(grec[hit], g["rec"][hit], rtol=1e-5, atol=1e-4)
 
 
-def test_secondary_hits_match_golden(golden_scene):
+def test_secondary_hits_match_golden(trace_scene):
     """Un-normalised directions from surface points (what hitable_pdf samples produce)."""
-    name, g, sc = golden_scene
+    name, g, sc = trace_scene
     gid, gt, _ = sc.trace_closest(g["rays2"])
     _check_hits(gid, gt, g["ids2"], g["t2"])
 
 
-def test_light_pdf_matches_golden(golden_scene):
-    name, g, sc = golden_scene
+def test_light_pdf_matches_golden(trace_scene):
+    name, g, sc = trace_scene
     got = sc.light_pdf(g["light_od"])
     want = g["light_pdf"]
     assert np.array_equal(got == 0, want == 0)
     assert np.allclose(got, want, rtol=1e-5, atol=0)
 
 
-def test_device_pointers_are_accepted(golden_scene):
+def test_device_pointers_are_accepted(trace_scene):
     import torch
-    name, g, sc = golden_scene
+    name, g, sc = trace_scene
     rays = torch.from_numpy(g["rays"][:4096].copy()).cuda()
     ids = torch.empty(len(rays), dtype=torch.int32, device="cuda")
     t = torch.empty(len(rays), dtype=torch.float32, device="cuda")
@@ -200,3 +213,17 @@ def test_cpp_crender_run_through_reference_headers(oracle, gpu_ctx, tmp_path):
     img = sc.render_image(render.render_params(64, 64, 8))
     sc.close()
     assert np.array_equal(px, img.reshape(-1, 3).astype(np.int64))
+
+
+def test_merl_lookup_matches_golden(gpu_ctx):
+    """srt_merl_lookup (fp64 half/diff-angle index arithmetic of brdf.h:17-61, :106-153, :190-214 on the
+    device) against the reference's lookup_brdf_val.  The table fetch is an exact copy, so values are
+    bit-equal whenever the three bin indices agree; device libm may round an angle across a bin edge."""
+    g = np.load(os.path.join(GOLDEN, "merl.npz"))
+    sc = render.Scene.from_objects(gpu_ctx, *get_scene("soldier"))
+    got = sc.merl_lookup(0, g["angles"])
+    sc.close()
+    same = (got == g["rgb"]).all(axis=1)
+    print(f"merl: {int(same.sum())} of {len(same)} lookups bit-equal")
+    assert same.mean() >= 0.999
+    assert np.allclose(got, g["rgb"], rtol=0.2)  # a neighbouring bin of the smooth table at worst

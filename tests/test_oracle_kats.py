@@ -82,10 +82,10 @@ def test_closed_form_helpers_pinned(oracle, kats):
 def test_golden_scene_vectors_match_live_reference(oracle):
     """The committed closest-hit vectors are what the reference computes today."""
     from simple_raytracing_render_b200 import scenes
-    from conftest import get_ref_scene
-    for name in ("cornell", "spheres", "teapot"):
+    from conftest import get_ref_scene, trace_name
+    for name in ("cornell", "spheres", "teapot", "soldier", "tessellated"):
         g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
-        rs = get_ref_scene(oracle, name)
+        rs = get_ref_scene(oracle, trace_name(name))
         n = 2000
         ids, t, rec = rs.trace(g["rays"][:n])
         assert np.array_equal(ids, g["ids"][:n])
@@ -101,3 +101,13 @@ def test_uninitialised_beckmann_pdf_reads_about_zero_in_this_process(oracle):
     Beckmann image comparison is meaningless: fail here, loudly, instead."""
     v = float(oracle.lib().ref_probe_beckmann_stash(0))
     assert abs(v) < 1e-30, f"oracle process reads {v!r} from an unwritten beckmann_pdf::pdf_value"
+
+
+def test_merl_lookup_golden_matches_live_reference(oracle):
+    """brdf::lookup_brdf_val (brdf.h:190-214) on the synthetic MERL-layout table (scenes.py)."""
+    from simple_raytracing_render_b200 import scenes, scene as S
+    g = np.load(os.path.join(GOLDEN, "merl.npz"))
+    m = S.brdfmaterial(scenes.synthetic_merl_table(), S.vec3(0.7, 0.7, 0.7))
+    got = oracle.merl_lookup(m, g["angles"])
+    assert np.array_equal(got, g["rgb"])
+    assert (got > 0).all() and len(np.unique(got[:, 0])) > 1000  # the angles really spread over the table
