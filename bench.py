@@ -299,6 +299,7 @@ def main():
 
     if rank == 0:
         hbm_peak, which, sm_max = peaks()
+        fp32_meas = ctx.measure_fp32_peak()
         k_s = kernel_ms * 1e-3
         achieved = abytes / k_s / 1e9
         line = {
@@ -317,7 +318,9 @@ def main():
                                  "see fp32 below and DESIGN.md §8"},
             "fp32": {"achieved_tflops": aflops / k_s / 1e12,
                      "nominal_peak_tflops": FP32_LANES * sm_max * 1e6 / 1e12,
-                     "frac": (aflops / k_s) / (FP32_LANES * sm_max * 1e6),
+                     "measured_peak_tflops": fp32_meas,
+                     "frac": (aflops / k_s / 1e12) / fp32_meas if fp32_meas > 0 else None,
+                     "frac_of": "measured FMA-chain peak (srt_measure_fp32_peak)",
                      "algorithmic_flops_per_launch": int(aflops)},
             "counters": {k: cnt[k] for k in ("paths", "rays", "culled_rays", "probe_rays", "node_visits", "prim_tests", "reject_iters")},
             "e2e": {"value": paths_per_step / e2e_s, "unit": "paths/s",

@@ -345,6 +345,11 @@ int srt_context_synchronize(SrtContext* ctx);
  * (must be 0).  a, b: device or host pointers to n floats. */
 int srt_selftest_division(SrtContext* ctx, const float* a, const float* b, int64_t n, uint64_t* mismatches);
 
+/* Measurement aid (bench.py): FP32 throughput of this GPU in TFLOP/s from a dependent-FMA-chain kernel
+ * (16 chains per thread, 8 CTAs x 256 threads per SM, best of 6 launches) — the measured denominator of
+ * the FP32 roofline fraction, since MEASURED_PEAKS.json carries HBM and tensor peaks only. */
+int srt_measure_fp32_peak(SrtContext* ctx, double* tflops);
+
 /* Host-side helpers (no device work): the reference's Sobol table (Raytracing_n.cpp:721-812,
  * D = 2; direction numbers of contents/sobol/new-joe-kuo-6.21201 line 2) as u32 numerators of
  * x / 2^32.  out: [n][2]. */

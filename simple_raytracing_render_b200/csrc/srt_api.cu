@@ -814,6 +814,35 @@ int srt_selftest_division(SrtContext* c, const float* a, const float* b, int64_t
     return 0;
 }
 
+int srt_measure_fp32_peak(SrtContext* c, double* tflops) {
+    if (!c || !tflops) return fail(SRT_E_INVALID, "null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    float* d = nullptr;
+    const int blocks = c->sm_count * 8, iters = 4096;
+    CUDA_TRY(cudaMalloc(&d, sizeof(float) * 256 * (size_t)blocks));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 6; rep++) {  // first repetitions warm the clocks up
+        CUDA_TRY(cudaEventRecord(e0, c->stream));
+        srt::k_fp32_peak<<<blocks, 256, 0, c->stream>>>(d, iters, 1.0f + rep);
+        CUDA_TRY(cudaEventRecord(e1, c->stream));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        c->launches++;
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        double fl = 2.0 * 16.0 * (double)iters * 256.0 * (double)blocks;
+        if (ms > 0.f) best = std::max(best, fl / (ms * 1e-3) / 1e12);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(d);
+    CUDA_TRY(cudaGetLastError());
+    *tflops = best;
+    return 0;
+}
+
 int srt_sobol_points_u32(uint32_t N, uint32_t* out) {
     // Raytracing_n.cpp:721-812 with D = 2: gray-code order, dimension 1 all m = 1, dimension 2 from
     // line 2 of new-joe-kuo-6.21201 ("2 1 0 1": s = 1, a = 0, m1 = 1).
@@ -970,6 +999,8 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     A.regen_threshold = std::max(1, std::min(32, env_int("SRT_REGEN", 8)));
     A.grab = std::max(32, env_int("SRT_GRAB", 128));
     A.cta_sync = std::max(0, std::min(2, env_int("SRT_CTA_SYNC", 0)));
+    A.dbg_pixel = counting ? env_int("SRT_DEBUG_PIXEL", -1) : -1;
+    A.dbg_sample = counting ? env_int("SRT_DEBUG_SAMPLE", -1) : -1;
 
     float* out = accum;
     if (n_chunks > 1) {

@@ -97,5 +97,22 @@ __global__ void k_check_xdiv(const float* __restrict__ a, const float* __restric
     if (__float_as_uint(q1) != __float_as_uint(q2) && !(q1 != q1 && q2 != q2)) atomicAdd(mismatches, 1ull);
 }
 
+// Measured FP32 roofline denominator (bench.py): 16 independent FMA chains per thread, enough
+// resident warps to saturate both FP32 datapaths of every SM sub-partition.  2 flops per FMA.
+__global__ void __launch_bounds__(256) k_fp32_peak(float* __restrict__ out, int iters, float seed) {
+    float a[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) a[k] = seed + (float)(threadIdx.x + k);
+    const float m = 1.0000001f, c = 1e-7f;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) a[k] = fmaf(a[k], m, c);
+    }
+    float s = 0.f;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s += a[k];
+    if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;  // never true: keeps the chains alive
+}
+
 }  // namespace srt
 #endif

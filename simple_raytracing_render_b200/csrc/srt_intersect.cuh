@@ -18,6 +18,7 @@ namespace srt {
 
 struct Counters {  // per-thread tallies of an instrumented launch (SrtCounters)
     unsigned long long rays, probe_rays, node_visits, prim_tests, reject_iters, culled_rays;
+    int dbg;  // counting build only: this lane traces the path selected by SRT_DEBUG_PIXEL / _SAMPLE
 };
 
 template <bool COUNT>

@@ -17,6 +17,7 @@ struct RenderArgs {
     unsigned n_items;     // n_pixels * n_chunks
     int regen_threshold;  // idle lanes in a warp that trigger a regeneration phase
     int grab;             // work items a warp takes from the global counter at a time
+    int dbg_pixel, dbg_sample;  // counting build: print the bounces of this one path (-1: off)
     int cta_sync;         // 1: the warps of a CTA start every bounce together; 2: and every shade together
 };
 
@@ -76,7 +77,7 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
     const int n_pixels = A.nx * A.ny;
     unsigned long long* work_counter = counters + 7;
 
-    Counters cnt = {0, 0, 0, 0, 0, 0};
+    Counters cnt = {0, 0, 0, 0, 0, 0, 0};
     Tally<COUNT> tl{&cnt};
     unsigned long long paths = 0;
 
@@ -158,7 +159,13 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
                 P.L = v3(0.f, 0.f, 0.f);
                 P.depth = 0;
                 alive = true;
-                if (COUNT) paths++;
+                if (COUNT) {
+                    paths++;
+                    cnt.dbg = (pixel == A.dbg_pixel && s == A.dbg_sample) ? 1 : 0;
+                    if (cnt.dbg)
+                        printf("[dbg] pixel %d sample %d: o=(%g %g %g) d=(%g %g %g)\n", pixel, s, P.r.o.x, P.r.o.y, P.r.o.z,
+                               P.r.d.x, P.r.d.y, P.r.d.z);
+                }
             }
             if (!__any_sync(FULL, alive)) {
                 bool pending = __any_sync(FULL, has_item);
@@ -177,6 +184,9 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
         }
         if (A.cta_sync >= 2) __syncthreads();
         if (run && alive) {
+            if (COUNT && cnt.dbg)
+                printf("[dbg] depth %d hit prim %d entry %d t %g thr=(%g %g %g) L=(%g %g %g)\n", P.depth, h.prim, h.entry, h.t,
+                       P.thr.x, P.thr.y, P.thr.z, P.L.x, P.L.y, P.L.z);
             if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
                 V3 c = de_nan(P.L);  // col += de_nan(color(...)), Raytracing_n.cpp:841
                 sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);

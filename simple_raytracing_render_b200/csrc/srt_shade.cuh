@@ -438,6 +438,10 @@ SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, P
     }
     // emitted is 0 for every scattering material (material.h:89-92)
     float wgt = spdf / pdf_val;
+    if (COUNT && tl.c->dbg)
+        printf("[dbg]   mat %d n=(%g %g %g) p=(%g %g %g) sdir=(%g %g %g) spdf %g pdf_val %g stash %g wgt %g\n", m.type,
+               rec.normal.x, rec.normal.y, rec.normal.z, rec.p.x, rec.p.y, rec.p.z, sdir.x, sdir.y, sdir.z, spdf, pdf_val,
+               B.stash, wgt);
     P.thr = fm::mul(P.thr, fm::scale(attenuation, wgt));
     P.r = Ray{rec.p, sdir, r.time};
     P.depth++;

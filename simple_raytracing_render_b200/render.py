@@ -56,6 +56,12 @@ class Context:
         ffi.check(self.lib, self.lib.srt_counters_get(self.h, C.byref(c)))
         return c.as_dict()
 
+    def measure_fp32_peak(self) -> float:
+        """TFLOP/s of an FMA-chain kernel on this GPU (srt_measure_fp32_peak)."""
+        v = C.c_double(0.0)
+        ffi.check(self.lib, self.lib.srt_measure_fp32_peak(self.h, C.byref(v)))
+        return float(v.value)
+
     def resolve(self, accum_dev, n_pixels: int, n_samples: int, rgb8_out):
         ffi.check(self.lib, self.lib.srt_resolve(self.h, _ptr(accum_dev), int(n_pixels), int(n_samples), _ptr(rgb8_out)))
 
