@@ -15,6 +15,7 @@
 #include "srt_aux_kernels.cuh"
 #include "srt_types.h"
 #include "srt_variants.h"
+#include "srt_wavefront.cuh"
 
 namespace {
 
@@ -60,6 +61,15 @@ struct SrtContext {
     int variant_blocks[SRT_N_VARIANTS] = {};  // occupancy query results, 0 = not queried yet
     int variant_regs[SRT_N_VARIANTS] = {};
     size_t variant_smem[SRT_N_VARIANTS] = {};  // dynamic shared memory the query was made with
+    // wavefront path (srt_wavefront.cuh): slot pool, per-pass live counts, host poll words
+    uint8_t* d_wf = nullptr;
+    size_t wf_cap = 0;
+    int* d_live = nullptr;
+    int* h_poll = nullptr;  // pinned, 2 words
+    cudaEvent_t wf_ev[2] = {nullptr, nullptr};
+    WfVariantInfo wf_info[SRT_N_WF_VARIANTS] = {};
+    size_t wf_info_smem[SRT_N_WF_VARIANTS] = {};
+    unsigned long long wf_passes = 0;  // passes enqueued by the last wavefront render
 };
 
 struct SrtScene {
@@ -326,6 +336,11 @@ int srt_context_destroy(SrtContext* ctx) {
     cudaFree(ctx->d_sobol);
     cudaFree(ctx->d_accum);
     cudaFree(ctx->d_partial);
+    cudaFree(ctx->d_wf);
+    cudaFree(ctx->d_live);
+    if (ctx->h_poll) cudaFreeHost(ctx->h_poll);
+    for (int i = 0; i < 2; i++)
+        if (ctx->wf_ev[i]) cudaEventDestroy(ctx->wf_ev[i]);
     if (ctx->h_rgb8) cudaFreeHost(ctx->h_rgb8);
     delete ctx;
     return 0;
@@ -743,8 +758,17 @@ int srt_trace_closest(SrtScene* s, const float* rays, int64_t n, int32_t* prim_i
     if ((rc = o_t.init(t, sizeof(float) * (size_t)n))) return rc;
     if ((rc = o_rec.init(rec, sizeof(float) * 8 * (size_t)n))) return rc;
     unsigned blocks = (unsigned)((n + 127) / 128);
-    srt::k_trace_closest<<<blocks, 128, 0, c->stream>>>(s->dev, (const float*)in.ptr, (long long)n, (int32_t*)o_id.ptr,
-                                                       (float*)o_t.ptr, (float*)o_rec.ptr, 0x5EEDu);
+    // the smallest of the feature classes of srt_variants.h that covers the scene
+    const uint32_t need = s->dev.features & F_ALL_SCENE;
+    auto kernel = srt::k_trace_closest<F_ALL_SCENE>;
+    if ((need & ~(uint32_t)SRT_VM_LIST) == 0)
+        kernel = srt::k_trace_closest<SRT_VM_LIST>;
+    else if ((need & ~(uint32_t)SRT_VM_SPHERES) == 0)
+        kernel = srt::k_trace_closest<SRT_VM_SPHERES>;
+    else if ((need & ~(uint32_t)SRT_VM_MESH) == 0)
+        kernel = srt::k_trace_closest<SRT_VM_MESH>;
+    kernel<<<blocks, 128, 0, c->stream>>>(s->dev, (const float*)in.ptr, (long long)n, (int32_t*)o_id.ptr, (float*)o_t.ptr,
+                                          (float*)o_rec.ptr, 0x5EEDu);
     c->launches++;
     CUDA_TRY(cudaGetLastError());
     if ((rc = o_id.finish(c->stream))) return rc;
@@ -935,12 +959,136 @@ int pick_variant(const SrtScene* s, bool counting) {
     return -1;
 }
 
+const WfVariantFn kWfVariants[SRT_N_WF_VARIANTS] = {srt_wavefront_variant_0, srt_wavefront_variant_1, srt_wavefront_variant_2,
+                                                     srt_wavefront_variant_3};
+constexpr uint32_t kWfMask[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_MASK(0), SRT_WF_VARIANT_MASK(1), SRT_WF_VARIANT_MASK(2),
+                                                 SRT_WF_VARIANT_MASK(3)};
+constexpr int kWfMaxPasses = 1 << 20;
+constexpr int kWfBatch = 8;  // passes enqueued between two polls of the live count
+
+int pick_wf_variant(const SrtScene* s) {
+    uint32_t need = s->dev.features & F_ALL_SCENE;
+    bool smem_ok = s->dev.hot_bytes <= kMaxHotSmem && !env_int("SRT_NO_SMEM", 0);
+    int forced = env_int("SRT_WF_VARIANT", -1);
+    for (int v = 0; v < SRT_N_WF_VARIANTS; v++) {
+        if (forced >= 0 && v != forced) continue;
+        if ((kWfMask[v] & F_SMEM_TABLES) && !smem_ok) continue;
+        if ((kWfMask[v] & need) != need) continue;
+        return v;
+    }
+    return -1;
+}
+
+// The wavefront form of one render (srt_wavefront.cuh): pass 0 fills the slot pool, then
+// trace + shade passes until a shade pass leaves no slot alive.  Passes are enqueued kWfBatch at a
+// time; after each batch the live count of its last pass is copied to pinned memory, and the host
+// waits for the copy of the PREVIOUS batch only, so the stream never drains while work remains.
+int run_wavefront(SrtScene* s, const srt::RenderArgs& A, float* out, int v) {
+    SrtContext* c = s->ctx;
+    const size_t smem = (kWfMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
+    WfLaunch L = {};
+    L.scene = &s->dev;
+    L.args = &A;
+    L.sobol = c->d_sobol;
+    L.out = out;
+    L.counters = c->d_counters;
+    L.smem_bytes = smem;
+    L.stream = c->stream;
+    if (c->wf_info[v].trace_blocks_per_sm == 0 || smem > c->wf_info_smem[v]) {
+        cudaError_t e = kWfVariants[v](L, &c->wf_info[v]);
+        if (e != cudaSuccess) return fail(SRT_E_CUDA, "wavefront variant %d: %s", v, cudaGetErrorString(e));
+        c->wf_info_smem[v] = smem;
+    }
+    const WfVariantInfo& info = c->wf_info[v];
+    const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 2048)) & ~31;
+    const int n_slots = c->sm_count * slots_per_sm;
+    const size_t need = (size_t)n_slots * 144;
+    if (c->wf_cap < need) {
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        cudaFree(c->d_wf);
+        c->d_wf = nullptr;
+        c->wf_cap = 0;
+        CUDA_TRY(cudaMalloc(&c->d_wf, need));
+        c->wf_cap = need;
+    }
+    if (!c->d_live) {
+        CUDA_TRY(cudaMalloc(&c->d_live, sizeof(int) * kWfMaxPasses));
+        CUDA_TRY(cudaHostAlloc(&c->h_poll, sizeof(int) * 2, cudaHostAllocDefault));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->wf_ev[0], cudaEventDisableTiming));
+        CUDA_TRY(cudaEventCreateWithFlags(&c->wf_ev[1], cudaEventDisableTiming));
+    }
+    srt::WfState st;
+    uint8_t* b = c->d_wf;
+    const size_t col = (size_t)n_slots * 16;
+    st.ray_o = (float4*)(b + 0 * col);
+    st.ray_d = (float4*)(b + 1 * col);
+    st.hit = (float4*)(b + 2 * col);
+    st.thr = (float4*)(b + 3 * col);
+    st.rad = (float4*)(b + 4 * col);
+    st.sum = (float4*)(b + 5 * col);
+    st.item = (int4*)(b + 6 * col);
+    st.rng = (uint4*)(b + 7 * col);
+    st.n_slots = n_slots;
+    L.state = &st;
+    L.live = c->d_live;
+
+    // every pass this render can need: each pass retires at least one ray per live slot
+    CUDA_TRY(cudaMemsetAsync(c->d_live, 0, sizeof(int) * kWfMaxPasses, c->stream));
+    const int blocks_needed = (n_slots + srt::kWfThreads - 1) / srt::kWfThreads;
+    const int grid_trace = std::min(blocks_needed, c->sm_count * std::max(1, info.trace_blocks_per_sm));
+    const int grid_shade = std::min(blocks_needed, c->sm_count * std::max(1, info.shade_blocks_per_sm));
+    auto launch = [&](int stage, int pass) -> cudaError_t {
+        L.stage = stage;
+        L.pass = pass;
+        L.grid = stage == 0 ? grid_trace : grid_shade;
+        c->launches++;
+        return kWfVariants[v](L, nullptr);
+    };
+    cudaError_t e = launch(1, 0);
+    if (e != cudaSuccess) return fail(SRT_E_CUDA, "k_wf_shade (variant %d): %s", v, cudaGetErrorString(e));
+    int pass = 1, batch = 0;
+    bool done = false;
+    while (!done) {
+        if (pass + kWfBatch >= kWfMaxPasses) return fail(SRT_E_UNSUPPORTED, "wavefront render exceeds %d passes", kWfMaxPasses);
+        for (int k = 0; k < kWfBatch; k++, pass++) {
+            e = launch(0, pass);
+            if (e == cudaSuccess) e = launch(1, pass);
+            if (e != cudaSuccess) return fail(SRT_E_CUDA, "wavefront pass %d (variant %d): %s", pass, v, cudaGetErrorString(e));
+        }
+        CUDA_TRY(cudaMemcpyAsync(c->h_poll + (batch & 1), c->d_live + (pass - 1), sizeof(int), cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaEventRecord(c->wf_ev[batch & 1], c->stream));
+        if (batch >= 1) {
+            CUDA_TRY(cudaEventSynchronize(c->wf_ev[(batch - 1) & 1]));
+            done = c->h_poll[(batch - 1) & 1] == 0;
+        }
+        batch++;
+    }
+    c->wf_passes = (unsigned long long)pass;
+    return 0;
+}
+
+// Wavefront by default when the scene has an acceleration structure (hundreds of primitives or more)
+// and the frame is long enough to amortise the passes' launches.
+bool auto_wavefront(const SrtScene* s, const SrtRenderParams* p) {
+    long long paths = (long long)p->nx * p->ny * (p->s_end - p->s_begin);
+    return s->dev.n_bvhs > 0 && paths >= (1LL << 24);
+}
+
 int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool counting) {
     SrtContext* c = s->ctx;
     int count = p->s_end - p->s_begin;
     if (count == 0) return 0;
     int rc = ensure_sobol(c, (uint32_t)p->s_end);
     if (rc) return rc;
+    // scheduler: the fused persistent-warp kernel (srt_kernels.cuh) or the two-stage wavefront
+    // (srt_wavefront.cuh).  SRT_RENDER_WAVEFRONT asks for the latter; without the flag the backend picks
+    // (DESIGN.md 5.1): scenes made of a handful of primitives stay on the fused kernel, whose whole
+    // frame is shorter than the wavefront's ramp-up and tail.
+    int wf_env = env_int("SRT_WAVEFRONT", -1);
+    bool wavefront = !counting && (wf_env >= 0 ? wf_env != 0
+                                               : ((p->flags & SRT_RENDER_WAVEFRONT) != 0 || auto_wavefront(s, p)));
+    int wv = wavefront ? pick_wf_variant(s) : -1;
+    if (wv < 0) wavefront = false;
     int v = pick_variant(s, counting);
     if (v < 0) return fail(SRT_E_UNSUPPORTED, "no render-kernel variant covers feature mask 0x%x", s->dev.features);
     size_t smem = (kVariantMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
@@ -953,7 +1101,9 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     L.stream = c->stream;
     L.grid = 0;
     RenderVariantInfo info = {};
-    if (c->variant_blocks[v] > 0 && smem <= c->variant_smem[v]) {
+    if (wavefront) {
+        info.blocks_per_sm = 1;
+    } else if (c->variant_blocks[v] > 0 && smem <= c->variant_smem[v]) {
         info.blocks_per_sm = c->variant_blocks[v];
         info.registers = c->variant_regs[v];
     } else {
@@ -965,17 +1115,19 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
         c->variant_regs[v] = info.registers;
         c->variant_smem[v] = smem;
     }
-    if (!counting) {
+    if (!counting && !wavefront) {
         s->variant = v;
         s->variant_blocks = info.blocks_per_sm;
         s->variant_regs = info.registers;
         s->variant_smem = smem;
     }
+    if (wavefront) s->variant = 100 + wv;
     int blocks_per_sm = std::max(1, info.blocks_per_sm);
 
     // work decomposition (srt_kernels.cuh): enough items for ~16 per resident lane
     long long n_pixels = (long long)p->nx * p->ny;
-    long long resident = (long long)c->sm_count * blocks_per_sm * srt::kRenderThreads;
+    long long resident = wavefront ? (long long)c->sm_count * (std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 2048)) & ~31)
+                                   : (long long)c->sm_count * blocks_per_sm * srt::kRenderThreads;
     long long want_items = 16 * resident;
     int n_chunks = 1;
     while (n_chunks < count && n_pixels * n_chunks < want_items) n_chunks <<= 1;
@@ -1017,6 +1169,17 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     }
     // counters[7] is the work counter
     CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
+    if (wavefront) {
+        int rc2 = run_wavefront(s, A, out, wv);
+        if (rc2) return rc2;
+        if (n_chunks > 1) {
+            long long nv = 3 * n_pixels;
+            srt::k_sum_partials<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(c->d_partial, n_chunks, nv, accum);
+            c->launches++;
+            CUDA_TRY(cudaGetLastError());
+        }
+        return 0;
+    }
     long long warps_needed = ((long long)A.n_items + 31) / 32;
     long long blocks_needed = (warps_needed + (srt::kRenderThreads / 32) - 1) / (srt::kRenderThreads / 32);
     L.args = &A;

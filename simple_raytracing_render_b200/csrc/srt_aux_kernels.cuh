@@ -9,6 +9,7 @@
 namespace srt {
 
 // Closest hit for a batch of rays: world->hit(r, 0.001, FLT_MAX, rec) (Raytracing_n.cpp:58).
+template <uint32_t FM>
 __global__ void __launch_bounds__(128) k_trace_closest(DScene S, const float* __restrict__ rays, long long n,
                                                        int32_t* __restrict__ prim, float* __restrict__ t,
                                                        float* __restrict__ rec, uint32_t seed) {
@@ -20,7 +21,7 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene S, const float* __
     Philox rng;
     philox_init(rng, seed, (uint32_t)i, (uint32_t)(i >> 32));
     Tally<false> tl{nullptr};
-    Hit h = world_hit<F_ALL_SCENE>(W, r, 0.001f, kFltMax, rng, tl);
+    Hit h = world_hit<FM>(W, r, 0.001f, kFltMax, rng, tl);
     if (h.prim < 0) {
         prim[i] = -1;
         t[i] = 0.f;
@@ -31,7 +32,7 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene S, const float* __
     prim[i] = h.prim;
     t[i] = h.t;
     if (rec) {
-        HitRecord hr = make_record<F_ALL_SCENE, true>(W, r, h);
+        HitRecord hr = make_record<FM, true>(W, r, h);
         float* o = rec + 8 * i;
         o[0] = hr.u;
         o[1] = hr.v;

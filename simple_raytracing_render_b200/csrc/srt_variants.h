@@ -59,6 +59,44 @@ typedef cudaError_t (*RenderVariantFn)(const RenderLaunch& L, RenderVariantInfo*
 // fetch that more warps hide; the sphere-BVH kernel spills ~1 KB at 64 registers and is best at 2.
 #define SRT_VARIANT_MINBLOCKS(n) ((n) == 1 ? 2 : 4)
 
+// ---- wavefront kernel pairs (srt_wavefront.cuh), one translation unit per mask -----------------------
+struct WfLaunch {
+    const DScene* scene;
+    const srt::RenderArgs* args;
+    const void* state;  // srt::WfState
+    const uint32_t* sobol;
+    float* out;
+    unsigned long long* counters;
+    int* live;    // live[pass] = slots left alive by shade pass `pass`
+    int pass;
+    int stage;    // 0: trace, 1: shade
+    int grid;
+    size_t smem_bytes;
+    cudaStream_t stream;
+};
+
+struct WfVariantInfo {
+    uint32_t features;
+    int trace_blocks_per_sm, shade_blocks_per_sm;
+    int trace_registers, shade_registers;
+};
+
+typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
+
+#define SRT_N_WF_VARIANTS 4
+#define SRT_WF_VARIANT_MASK(n)                                 \
+    ((n) == 0   ? (SRT_VM_LIST | F_SMEM_TABLES)                \
+     : (n) == 1 ? (SRT_VM_SPHERES | F_SMEM_TABLES)             \
+     : (n) == 2 ? (SRT_VM_MESH)                                \
+                : (SRT_VM_FULL))
+#define SRT_WF_VARIANT_TRACE_MINBLOCKS(n) 3
+#define SRT_WF_VARIANT_SHADE_MINBLOCKS(n) 3
+
+cudaError_t srt_wavefront_variant_0(const WfLaunch&, WfVariantInfo*);
+cudaError_t srt_wavefront_variant_1(const WfLaunch&, WfVariantInfo*);
+cudaError_t srt_wavefront_variant_2(const WfLaunch&, WfVariantInfo*);
+cudaError_t srt_wavefront_variant_3(const WfLaunch&, WfVariantInfo*);
+
 cudaError_t srt_render_variant_0(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_1(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_2(const RenderLaunch&, RenderVariantInfo*);

@@ -1,0 +1,224 @@
+// srt_wavefront.cuh — the render loop as a two-stage wavefront over a fixed pool of path slots.
+//
+// Why (profiles/r01_notes.md, captures A-D): the fused kernel of srt_kernels.cuh is bound by
+// instruction fetch — its hot code (37 KB for the sphere-BVH scene, 95 KB for the Beckmann mesh) is
+// larger than the SM's instruction cache, 60 % of its stall samples are `no_instruction`, while the
+// closest-hit code run on its own (k_trace_closest) sustains 10-27 Grays/s, five times the fused rate.
+// Splitting the bounce into a TRACE kernel (world->hit only) and a SHADE kernel (color()'s material /
+// pdf / light-sampling step, path regeneration and ray generation) gives each stage a hot set that
+// fits the instruction cache, and gives the trace stage full warps: a slot whose path ended is
+// refilled in the same shade pass, so every lane of every warp traces a live ray.
+//
+// State lives in global memory as 16-byte SoA records, 144 B per slot; the pool is sized to the
+// resident threads of the GPU (a few 100 k slots, tens of MB), so it stays in the 126 MB L2 between
+// the passes and HBM sees none of it.  One iteration = one k_wf_trace + one k_wf_shade launch; the
+// host enqueues iterations in batches and polls the live-slot count of an earlier pass, never
+// draining the stream (srt_api.cu: launch_wavefront).
+//
+// Results are the ones of the fused kernel: same work items, same Philox counters (the buffered
+// outputs of a path's generator are part of the slot), same per-item partial sums.
+#ifndef SRT_WAVEFRONT_CUH
+#define SRT_WAVEFRONT_CUH
+
+#include "srt_kernels.cuh"
+
+// resident CTAs per SM the two kernels are register-bounded for (srt_variants.h picks per variant)
+#ifndef SRT_WF_TRACE_MINBLOCKS
+#define SRT_WF_TRACE_MINBLOCKS 3
+#endif
+#ifndef SRT_WF_SHADE_MINBLOCKS
+#define SRT_WF_SHADE_MINBLOCKS 3
+#endif
+
+namespace srt {
+
+struct WfState {
+    float4* ray_o;  // o.xyz, time
+    float4* ray_d;  // d.xyz, -
+    float4* hit;    // t, prim (int bits), entry (int bits), -
+    float4* thr;    // throughput.xyz, depth (int bits)
+    float4* rad;    // radiance gathered so far .xyz, -
+    float4* sum;    // radiance sum of the current work item .xyz, flags (int bits: 1 alive, 2 has_item)
+    int4* item;     // pixel, chunk_id, s_next, s_stop
+    uint4* rng;     // (c2 << 3) | have, out[0], out[1], out[2]
+    int n_slots;    // multiple of 32
+};
+
+constexpr int kWfThreads = 256;
+constexpr int kWfAlive = 1, kWfHasItem = 2;
+
+SRT_DEV void wf_load_rng(const WfState& st, int slot, uint32_t seed, uint32_t pixel, uint32_t sample, Philox& p) {
+    uint4 v = st.rng[slot];
+    philox_init(p, seed, pixel, sample);
+    p.c2 = v.x >> 3;
+    p.have = (int)(v.x & 7u);
+    p.out[0] = v.y;
+    p.out[1] = v.z;
+    p.out[2] = v.w;
+    p.out[3] = 0;
+}
+SRT_DEV void wf_store_rng(const WfState& st, int slot, const Philox& p) {
+    st.rng[slot] = make_uint4((p.c2 << 3) | (uint32_t)p.have, p.out[0], p.out[1], p.out[2]);
+}
+
+// Stage the hot tables of the scene into shared memory (F_SMEM_TABLES) and return the view.
+template <uint32_t F>
+SRT_DEV View wf_view(const DScene& S, float4* smem_hot) {
+    if (F & F_SMEM_TABLES) {
+        const float4* src = reinterpret_cast<const float4*>(S.entries);
+        const unsigned n16 = S.hot_bytes >> 4;
+        for (unsigned i = threadIdx.x; i < n16; i += blockDim.x) smem_hot[i] = __ldg(src + i);
+        __syncthreads();
+        const char* base = reinterpret_cast<const char*>(smem_hot);
+        const char* g0 = reinterpret_cast<const char*>(S.entries);
+        return View{S, reinterpret_cast<const DEntry*>(base),
+                    reinterpret_cast<const SrtXformOp*>(base + (reinterpret_cast<const char*>(S.ops) - g0)),
+                    reinterpret_cast<const DPrim*>(base + (reinterpret_cast<const char*>(S.dprims) - g0)),
+                    reinterpret_cast<const DPrim*>(base + (reinterpret_cast<const char*>(S.lights) - g0))};
+    }
+    return global_view(S);
+}
+
+// ---- TRACE: world->hit(r, 0.001, FLT_MAX, rec) (Raytracing_n.cpp:58) for every live slot -----------
+// `live[pass]` is the number of live slots the shade pass `pass` left behind; a trace / shade pass
+// whose predecessor left none (and is not the first) has nothing to do and returns at once: the host
+// may enqueue a few passes more than needed (it polls with a lag), they cost a launch each.
+template <uint32_t F>
+__global__ void __launch_bounds__(kWfThreads, SRT_WF_TRACE_MINBLOCKS)
+    k_wf_trace(DScene S, RenderArgs A, WfState st, const int* __restrict__ live, int pass) {
+    extern __shared__ float4 smem_hot[];
+    if (pass > 0 && live[pass - 1] == 0) return;
+    View W = wf_view<F>(S, smem_hot);
+    Tally<false> tl{nullptr};
+    const int stride = gridDim.x * blockDim.x;
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride) {
+        const int flags = __float_as_int(st.sum[slot].w);
+        if (!(flags & kWfAlive)) continue;
+        float4 o = st.ray_o[slot], d = st.ray_d[slot];
+        Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+        Philox rng;
+        rng.have = 0;
+        if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
+            int4 it = st.item[slot];
+            wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)(it.z - 1), rng);
+        }
+        Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
+        st.hit[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f);
+        if (F & F_MEDIA) wf_store_rng(st, slot, rng);
+    }
+}
+
+// ---- SHADE: one level of color() for every live slot, then refill ----------------------------------
+// For a live slot: shade_bounce on the hit the trace pass stored (emitted / scatter / mixture sampling,
+// Raytracing_n.cpp:61-99); a path that ends adds de_nan(radiance) to its work item's sum (:841).
+// For a slot without a live path: close the finished work item (write its sum to the item's own
+// partial slot, as the fused kernel does), take the next item from the global counter (one atomic per
+// warp), and start the next path: Sobol jitter + camera::get_ray (:827-836).
+// counters[7] is the work-item counter; live[pass] receives the number of slots left alive.
+template <uint32_t F>
+__global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
+    k_wf_shade(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, float* __restrict__ out,
+               unsigned long long* __restrict__ counters, int* __restrict__ live, int pass) {
+    extern __shared__ float4 smem_hot[];
+    if (pass > 0 && live[pass - 1] == 0) return;
+    View W = wf_view<F>(S, smem_hot);
+    Tally<false> tl{nullptr};
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n_pixels = A.nx * A.ny;
+    unsigned long long* work_counter = counters + 7;
+    const int stride = gridDim.x * blockDim.x;
+    int n_alive = 0;
+    // n_slots is a multiple of 32 and blockDim of 32: the warps of this loop are always full
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride) {
+        float4 sm = st.sum[slot];
+        int flags = pass == 0 ? 0 : __float_as_int(sm.w);
+        V3 sum = pass == 0 ? v3(0.f, 0.f, 0.f) : v3(sm.x, sm.y, sm.z);
+        int4 it = pass == 0 ? make_int4(0, 0, 0, 0) : st.item[slot];
+        int pixel = it.x, chunk_id = it.y, s_next = it.z, s_stop = it.w;
+        bool alive = (flags & kWfAlive) != 0, has_item = (flags & kWfHasItem) != 0;
+        Philox rng;
+        rng.have = 0;
+        Path P;
+        if (alive) {
+            float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
+            P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+            P.thr = v3(tv.x, tv.y, tv.z);
+            P.depth = __float_as_int(tv.w);
+            P.L = v3(lv.x, lv.y, lv.z);
+            Hit h;
+            h.t = hv.x;
+            h.prim = __float_as_int(hv.y);
+            h.entry = __float_as_int(hv.z);
+            wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)(s_next - 1), rng);
+            if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
+                V3 c = de_nan(P.L);
+                sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
+                alive = false;
+            }
+        }
+        // ---- refill (the regeneration phase of srt_kernels.cuh, per lane and without a threshold) ----
+        if (!alive && has_item && s_next >= s_stop) {
+            float* o = out + 3 * ((size_t)chunk_id * n_pixels + pixel);
+            if (A.n_chunks == 1) {
+                o[0] += sum.x;
+                o[1] += sum.y;
+                o[2] += sum.z;
+            } else {
+                o[0] = sum.x;
+                o[1] = sum.y;
+                o[2] = sum.z;
+            }
+            has_item = false;
+        }
+        const bool need_item = !alive && !has_item;
+        const unsigned m = __ballot_sync(FULL, need_item);
+        if (m) {
+            unsigned long long base = 0;
+            if (lane == 0) base = atomicAdd(work_counter, (unsigned long long)__popc(m));
+            base = __shfl_sync(FULL, base, 0);
+            const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
+            if (need_item && item < (unsigned long long)A.n_items) {
+                pixel = (int)((unsigned)item / (unsigned)A.n_chunks);
+                chunk_id = (int)((unsigned)item - (unsigned)pixel * (unsigned)A.n_chunks);
+                s_next = A.s_begin + chunk_id * A.chunk;
+                s_stop = min(s_next + A.chunk, A.s_end);
+                sum = v3(0.f, 0.f, 0.f);
+                has_item = true;
+            }
+        }
+        if (!alive && has_item && s_next < s_stop) {
+            int i = pixel % (A.mod_ny ? A.ny : A.nx);
+            int j = A.ny - 1 - (pixel / A.nx);
+            int s = s_next++;
+            double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
+            double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
+            float u = xdiv((float)(sx + (double)i), (float)A.nx);
+            float v = xdiv((float)(sy + (double)j), (float)A.ny);
+            philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
+            P.r = camera_get_ray(S.camera, u, v, rng);
+            P.thr = v3(1.f, 1.f, 1.f);
+            P.L = v3(0.f, 0.f, 0.f);
+            P.depth = 0;
+            alive = true;
+        }
+        // ---- store ------------------------------------------------------------------------------------
+        flags = (alive ? kWfAlive : 0) | (has_item ? kWfHasItem : 0);
+        st.sum[slot] = make_float4(sum.x, sum.y, sum.z, __int_as_float(flags));
+        st.item[slot] = make_int4(pixel, chunk_id, s_next, s_stop);
+        if (alive) {
+            st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
+            st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
+            st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
+            st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
+            wf_store_rng(st, slot, rng);
+            n_alive++;
+        }
+    }
+    const unsigned total = __reduce_add_sync(FULL, (unsigned)n_alive);
+    if (lane == 0 && total) atomicAdd(live + pass, (int)total);
+}
+
+}  // namespace srt
+#endif

@@ -1,0 +1,55 @@
+// srt_wavefront_variant.cu — one instantiation of the wavefront kernel pair (srt_wavefront.cuh);
+// compiled SRT_N_WF_VARIANTS times with -DSRT_WF_VARIANT=<n> (srt_variants.h).
+#ifndef SRT_WF_VARIANT
+#error "compile with -DSRT_WF_VARIANT=<n>"
+#endif
+
+#include "srt_variants.h"
+#ifndef SRT_WF_TRACE_MINBLOCKS
+#define SRT_WF_TRACE_MINBLOCKS SRT_WF_VARIANT_TRACE_MINBLOCKS(SRT_WF_VARIANT)
+#endif
+#ifndef SRT_WF_SHADE_MINBLOCKS
+#define SRT_WF_SHADE_MINBLOCKS SRT_WF_VARIANT_SHADE_MINBLOCKS(SRT_WF_VARIANT)
+#endif
+#include "srt_wavefront.cuh"
+
+#define SRT_CAT2(a, b) a##b
+#define SRT_CAT(a, b) SRT_CAT2(a, b)
+
+namespace {
+constexpr uint32_t kMask = SRT_WF_VARIANT_MASK(SRT_WF_VARIANT);
+}
+
+cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, WfVariantInfo* info) {
+    auto trace = srt::k_wf_trace<kMask>;
+    auto shade = srt::k_wf_shade<kMask>;
+    cudaError_t e;
+    if (L.smem_bytes > 48 * 1024) {
+        e = cudaFuncSetAttribute(trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(shade, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+        if (e != cudaSuccess) return e;
+    }
+    if (info) {
+        info->features = kMask;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->trace_blocks_per_sm, trace, srt::kWfThreads, L.smem_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->shade_blocks_per_sm, shade, srt::kWfThreads, L.smem_bytes);
+        if (e != cudaSuccess) return e;
+        cudaFuncAttributes fa;
+        e = cudaFuncGetAttributes(&fa, trace);
+        if (e != cudaSuccess) return e;
+        info->trace_registers = fa.numRegs;
+        e = cudaFuncGetAttributes(&fa, shade);
+        if (e != cudaSuccess) return e;
+        info->shade_registers = fa.numRegs;
+        return cudaSuccess;
+    }
+    const srt::WfState& st = *static_cast<const srt::WfState*>(L.state);
+    if (L.stage == 0)
+        trace<<<L.grid, srt::kWfThreads, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.live, L.pass);
+    else
+        shade<<<L.grid, srt::kWfThreads, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters, L.live,
+                                                                   L.pass);
+    return cudaGetLastError();
+}
