@@ -983,7 +983,7 @@ int pick_wf_variant(const SrtScene* s) {
 // trace + shade passes until a shade pass leaves no slot alive.  Passes are enqueued kWfBatch at a
 // time; after each batch the live count of its last pass is copied to pinned memory, and the host
 // waits for the copy of the PREVIOUS batch only, so the stream never drains while work remains.
-int run_wavefront(SrtScene* s, const srt::RenderArgs& A, float* out, int v) {
+int run_wavefront(SrtScene* s, const srt::RenderArgs& A, float* out, int v, bool persistent) {
     SrtContext* c = s->ctx;
     const size_t smem = (kWfMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
     WfLaunch L = {};
@@ -1001,7 +1001,11 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, float* out, int v) {
     }
     const WfVariantInfo& info = c->wf_info[v];
     const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 2048)) & ~31;
-    const int n_slots = c->sm_count * slots_per_sm;
+    // persistent form: every CTA owns per_thread x threads slots
+    const int p_blocks = std::max(1, info.persist_blocks_per_sm), p_threads = std::max(32, info.persist_threads);
+    const int per_thread = std::max(1, slots_per_sm / (p_blocks * p_threads));
+    const int p_grid = c->sm_count * p_blocks;
+    const int n_slots = persistent ? p_grid * per_thread * p_threads : c->sm_count * slots_per_sm;
     const size_t need = (size_t)n_slots * 144;
     if (c->wf_cap < need) {
         CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -1031,6 +1035,16 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, float* out, int v) {
     st.n_slots = n_slots;
     L.state = &st;
     L.live = c->d_live;
+    if (persistent) {  // one launch: shade / trace phases alternate inside the kernel (k_wf_persist)
+        L.stage = 2;
+        L.per_thread = per_thread;
+        L.grid = p_grid;
+        c->launches++;
+        cudaError_t pe = kWfVariants[v](L, nullptr);
+        if (pe != cudaSuccess) return fail(SRT_E_CUDA, "k_wf_persist (variant %d): %s", v, cudaGetErrorString(pe));
+        c->wf_passes = 0;
+        return 0;
+    }
 
     // every pass this render can need: each pass retires at least one ray per live slot
     CUDA_TRY(cudaMemsetAsync(c->d_live, 0, sizeof(int) * kWfMaxPasses, c->stream));
@@ -1121,7 +1135,8 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
         s->variant_regs = info.registers;
         s->variant_smem = smem;
     }
-    if (wavefront) s->variant = 100 + wv;
+    const bool wf_persistent = wavefront && (wf_env == 2 || (wf_env < 0 && env_int("SRT_WF_PERSIST", 1)));
+    if (wavefront) s->variant = (wf_persistent ? 200 : 100) + wv;
     int blocks_per_sm = std::max(1, info.blocks_per_sm);
 
     // work decomposition (srt_kernels.cuh): enough items for ~16 per resident lane
@@ -1170,7 +1185,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     // counters[7] is the work counter
     CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
     if (wavefront) {
-        int rc2 = run_wavefront(s, A, out, wv);
+        int rc2 = run_wavefront(s, A, out, wv, wf_persistent);
         if (rc2) return rc2;
         if (n_chunks > 1) {
             long long nv = 3 * n_pixels;

@@ -202,7 +202,7 @@ struct Collapser {
             hix[i] = hiy[i] = hiz[i] = -FLT_MAX;
         }
         (&w.child.x)[i] = child;
-        (&w.count.x)[i] = count;
+        (&w.ref.x)[i] = child >= 0 ? child : (count == 0 ? (int32_t)0x80000000 : ~(((~child) << 3) | count));
     }
 
     // emit a wide node for binary node `b` (must be inner, or the single-leaf root)

@@ -312,12 +312,29 @@ SRT_DEV bool ref_reachable(const RefNode* root, int rank, const Ray& r, RayInv i
 // out unreachable it becomes the new bound and the search repeats.  One pass in all but ~1e-6 of rays.
 constexpr int kStackSize = 48;
 
+// Wide-node step helpers.  Children that pass the slab test are ordered near-to-far with a 5-comparator
+// network on 32-bit keys held in registers: key = bits of max(lower bound, 0) with the two low
+// mantissa bits replaced by the child slot (non-negative floats order like unsigned integers), all
+// ones for a child that is not visited.  No dynamically indexed local arrays, no data-dependent loop.
+constexpr uint32_t kKeyNone = 0xffffffffu;
+constexpr int32_t kRefEmpty = (int32_t)0x80000000;  // WideNode4::ref of an unused child slot
+constexpr int32_t kRefDone = (int32_t)0x80000001;   // traversal cursor: nothing left
+SRT_DEV void key_sort2(uint32_t& a, uint32_t& b) {
+    uint32_t lo = min(a, b), hi = max(a, b);
+    a = lo;
+    b = hi;
+}
+SRT_DEV int32_t ref_select(int4 r, uint32_t key) {
+    uint32_t i = key & 3u;
+    int32_t lo = (i & 1u) ? r.y : r.x, hi = (i & 1u) ? r.w : r.z;
+    return (i & 2u) ? hi : lo;
+}
+
 template <uint32_t F, bool COUNT>
 SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, float t_max, bool is_medium,
                      float& t_out, int32_t& prim_out, Tally<COUNT> tl) {
     const DScene& S = W.S;
     const Ray& r = q.r;
-    RayInv inv{xdiv(1.0f, q.kx), xdiv(1.0f, q.ky), xdiv(1.0f, q.kz)};
     // pruning scale: triangle t is a distance, box slabs are parametric
     float len = xsqrt(q.a);
     const int kind = (F & F_BVH_GENERIC) || ((F & F_BVH_SPHERE) && (F & F_BVH_TRI))
@@ -326,10 +343,19 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
     float tscale = kind == BVH_KIND_SPHERE ? 1.0f : (kind == BVH_KIND_TRIANGLE ? len : fminf(1.0f, len));
     if (!(tscale == tscale)) return false;  // NaN direction: nothing sensible to report
     const WideNode4* nodes = S.wide_nodes + B.node_base;
-    const RefNode* ref = S.ref_nodes + B.ref_base;
     const int32_t* ranks = S.leaf_rank + B.leaf_base;
     V3 tdir = v3(0.f, 0.f, 0.f);
     if ((F & (F_BVH_TRI | F_BVH_GENERIC)) && kind != BVH_KIND_SPHERE) tdir = tri_dir(r);
+
+    // Slab planes of OUR tree in the form fma(plane, 1/d, -o/d): it only orders and prunes, so it needs
+    // to be conservative, not exact.  1/d is clamped to +-1e30 (axis-parallel and denormal directions:
+    // inside the slab the interval is huge, outside it is empty, on the face the margin decides for
+    // "hit"); `em` covers the rounding of o/d, which the subtract-first form does not have.
+    const float cix = fminf(fmaxf(q.kx.r, -1e30f), 1e30f), ciy = fminf(fmaxf(q.ky.r, -1e30f), 1e30f),
+                ciz = fminf(fmaxf(q.kz.r, -1e30f), 1e30f);
+    const float nox = -r.o.x * cix, noy = -r.o.y * ciy, noz = -r.o.z * ciz;
+    const float em = 1e-6f * fmaxf(fmaxf(fabsf(nox), fabsf(noy)), fabsf(noz));
+    const float f_floor = fminf(t_min, 0.0f);
 
     float ex_t = -CUDART_INF_F;
     int ex_rank = 0x7fffffff;
@@ -337,68 +363,62 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
         float best_t = CUDART_INF_F;
         int best_rank = -1;
         int32_t best_prim = -1;
-        int32_t stack[kStackSize];
+        uint2 stack[kStackSize];  // (key, ref)
         int sp = 0;
-        int32_t cur = 0;  // >= 0 inner node; < 0 leaf reference packed as ~(first << 3 | count)
+        int32_t cur = 0;  // >= 0 inner node; < 0 leaf reference ~(first << 3 | count); kRefDone
         for (;;) {
-            if (cur >= 0) {
+            // ---- inner nodes: descend until this lane holds a leaf (or has nothing left) -------------
+            while (cur >= 0) {
                 const float4* nq = reinterpret_cast<const float4*>(nodes + cur);
                 float4 lox = __ldg(nq), loy = __ldg(nq + 1), loz = __ldg(nq + 2);
                 float4 hix = __ldg(nq + 3), hiy = __ldg(nq + 4), hiz = __ldg(nq + 5);
-                int4 child = __ldg(reinterpret_cast<const int4*>(nq + 6));
-                int4 count = __ldg(reinterpret_cast<const int4*>(nq + 7));
+                int4 refs = __ldg(reinterpret_cast<const int4*>(nq + 7));
                 tl.node();
-                float tn[4];
-                int32_t ref4[4];
                 const float LX[4] = {lox.x, lox.y, lox.z, lox.w}, LY[4] = {loy.x, loy.y, loy.z, loy.w};
                 const float LZ[4] = {loz.x, loz.y, loz.z, loz.w}, HX[4] = {hix.x, hix.y, hix.z, hix.w};
                 const float HY[4] = {hiy.x, hiy.y, hiy.z, hiy.w}, HZ[4] = {hiz.x, hiz.y, hiz.z, hiz.w};
-                const int CH[4] = {child.x, child.y, child.z, child.w}, CN[4] = {count.x, count.y, count.z, count.w};
-                int nhit = 0;
+                const int RF[4] = {refs.x, refs.y, refs.z, refs.w};
+                uint32_t key[4];
 #pragma unroll
                 for (int i = 0; i < 4; i++) {
-                    float ax = (LX[i] - r.o.x) * inv.ix, bx = (HX[i] - r.o.x) * inv.ix;
-                    float ay = (LY[i] - r.o.y) * inv.iy, by = (HY[i] - r.o.y) * inv.iy;
-                    float az = (LZ[i] - r.o.z) * inv.iz, bz = (HZ[i] - r.o.z) * inv.iz;
+                    float ax = fmaf(LX[i], cix, nox), bx = fmaf(HX[i], cix, nox);
+                    float ay = fmaf(LY[i], ciy, noy), by = fmaf(HY[i], ciy, noy);
+                    float az = fmaf(LZ[i], ciz, noz), bz = fmaf(HZ[i], ciz, noz);
                     float n = fmaxf(fmaxf(fminf(ax, bx), fminf(ay, by)), fminf(az, bz));
                     float f = fminf(fminf(fmaxf(ax, bx), fmaxf(ay, by)), fmaxf(az, bz));
-                    // conservative: widen the interval by a few ulps before deciding
-                    n = n - fabsf(n) * 4e-6f;
-                    f = f + fabsf(f) * 4e-6f;
-                    bool empty = CH[i] < 0 && CN[i] == 0;
+                    // conservative: widen the interval before deciding
+                    n = fmaf(fabsf(n), -4e-6f, n) - em;
+                    f = fmaf(fabsf(f), 4e-6f, f) + em;
                     // lower bound of any leaf t inside this box, in the leaves' own units
                     float lb = n > 0.0f ? n * tscale : (kind == BVH_KIND_TRIANGLE ? 0.0f : n);
-                    bool h = !empty && n <= f && f >= fminf(t_min, 0.0f) && lb <= best_t;
-                    if (h) {
-                        tn[nhit] = n;
-                        ref4[nhit] = CH[i] >= 0 ? CH[i] : ~(((~CH[i]) << 3) | CN[i]);
-                        nhit++;
+                    bool h = RF[i] != kRefEmpty && n <= f && f >= f_floor && lb <= best_t;
+                    key[i] = h ? ((__float_as_uint(fmaxf(lb, 0.0f)) & ~3u) | (uint32_t)i) : kKeyNone;
+                }
+                key_sort2(key[0], key[1]);
+                key_sort2(key[2], key[3]);
+                key_sort2(key[0], key[2]);
+                key_sort2(key[1], key[3]);
+                key_sort2(key[1], key[2]);
+                // push far-to-near, continue with the nearest
+                if (key[3] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[3], (uint32_t)ref_select(refs, key[3]));
+                if (key[2] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[2], (uint32_t)ref_select(refs, key[2]));
+                if (key[1] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[1], (uint32_t)ref_select(refs, key[1]));
+                if (key[0] != kKeyNone) {
+                    cur = ref_select(refs, key[0]);
+                } else {
+                    cur = kRefDone;
+                    while (sp > 0) {  // pop, skipping entries the current best has overtaken
+                        uint2 e = stack[--sp];
+                        float lb = __uint_as_float(e.x & ~3u);
+                        if (lb == 0.0f || lb <= best_t) {
+                            cur = (int32_t)e.y;
+                            break;
+                        }
                     }
                 }
-                if (nhit == 0) {
-                    if (sp == 0) break;
-                    cur = stack[--sp];
-                    continue;
-                }
-                // insertion sort by entry distance (nearest first), push the rest far-to-near
-                for (int i = 1; i < nhit; i++) {
-                    float kt = tn[i];
-                    int32_t kr = ref4[i];
-                    int j = i - 1;
-                    while (j >= 0 && tn[j] > kt) {
-                        tn[j + 1] = tn[j];
-                        ref4[j + 1] = ref4[j];
-                        j--;
-                    }
-                    tn[j + 1] = kt;
-                    ref4[j + 1] = kr;
-                }
-                for (int i = nhit - 1; i >= 1; i--)
-                    if (sp < kStackSize) stack[sp++] = ref4[i];
-                cur = ref4[0];
-                continue;
             }
-            // leaf
+            if (cur == kRefDone) break;
+            // ---- leaf ---------------------------------------------------------------------------------
             {
                 int packed = ~cur;
                 int first = packed >> 3, cnt = packed & 7;
@@ -432,11 +452,20 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
                     }
                 }
             }
-            if (sp == 0) break;
-            cur = stack[--sp];
+            cur = kRefDone;
+            while (sp > 0) {
+                uint2 e = stack[--sp];
+                float lb = __uint_as_float(e.x & ~3u);
+                if (lb == 0.0f || lb <= best_t) {
+                    cur = (int32_t)e.y;
+                    break;
+                }
+            }
+            if (cur == kRefDone) break;
         }
         if (best_rank < 0) return false;
-        if (ref_reachable(ref, best_rank, r, inv, t_min, t_max, tl)) {
+        RayInv inv{xdiv(1.0f, q.kx), xdiv(1.0f, q.ky), xdiv(1.0f, q.kz)};
+        if (ref_reachable(S.ref_nodes + B.ref_base, best_rank, r, inv, t_min, t_max, tl)) {
             if (best_prim == -2) best_prim = S.groups[S.bvh_items[B.first_item + best_rank]].first_prim;
             t_out = best_t;
             prim_out = best_prim;

@@ -100,14 +100,16 @@ struct alignas(16) DMaterial {
 };
 
 // ---- wide BVH (4-ary, full-precision child boxes, SoA per node; 128 B = 8 x 16 B loads) --------
-// child[i] >= 0            : index of an inner node
-// child[i] <  0, count > 0 : leaf; first = ~child[i] is the first slot of the bvh's leaf arrays
-// count[i] == 0 and child[i] < 0 : empty slot (its box is inverted, never hit)
+// child[i] >= 0 : index of an inner node; child[i] < 0 : leaf whose first slot in the bvh's leaf
+// arrays is ~child[i] (builder bookkeeping; the kernels read `ref` only)
+// ref[i]        : what traversal follows, ready to use: the inner node index (>= 0), or
+//                 ~((first << 3) | count) for a leaf of `count` (1..7) slots, or 0x80000000 for an
+//                 unused slot (its box is inverted as well, never hit)
 struct alignas(16) WideNode4 {
     float4 lox, loy, loz;
     float4 hix, hiy, hiz;
     int4 child;
-    int4 count;
+    int4 ref;
 };
 
 // ---- the reference's own bvh_node tree (bvh.h:96-119), kept only as boxes ---------------------

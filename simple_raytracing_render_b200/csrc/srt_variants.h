@@ -69,7 +69,8 @@ struct WfLaunch {
     unsigned long long* counters;
     int* live;    // live[pass] = slots left alive by shade pass `pass`
     int pass;
-    int stage;    // 0: trace, 1: shade
+    int stage;    // 0: trace, 1: shade, 2: the persistent kernel (both stages as phases)
+    int per_thread;  // stage 2: slots per thread
     int grid;
     size_t smem_bytes;
     cudaStream_t stream;
@@ -79,6 +80,7 @@ struct WfVariantInfo {
     uint32_t features;
     int trace_blocks_per_sm, shade_blocks_per_sm;
     int trace_registers, shade_registers;
+    int persist_blocks_per_sm, persist_registers, persist_threads;
 };
 
 typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);

@@ -84,28 +84,32 @@ SRT_DEV View wf_view(const DScene& S, float4* smem_hot) {
 // whose predecessor left none (and is not the first) has nothing to do and returns at once: the host
 // may enqueue a few passes more than needed (it polls with a lag), they cost a launch each.
 template <uint32_t F>
+SRT_DEV void wf_trace_slot(const View& W, const RenderArgs& A, const WfState& st, int slot) {
+    Tally<false> tl{nullptr};
+    const int flags = __float_as_int(st.sum[slot].w);
+    if (!(flags & kWfAlive)) return;
+    float4 o = st.ray_o[slot], d = st.ray_d[slot];
+    Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+    Philox rng;
+    rng.have = 0;
+    if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
+        int4 it = st.item[slot];
+        wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)(it.z - 1), rng);
+    }
+    Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
+    st.hit[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f);
+    if (F & F_MEDIA) wf_store_rng(st, slot, rng);
+}
+
+template <uint32_t F>
 __global__ void __launch_bounds__(kWfThreads, SRT_WF_TRACE_MINBLOCKS)
     k_wf_trace(DScene S, RenderArgs A, WfState st, const int* __restrict__ live, int pass) {
     extern __shared__ float4 smem_hot[];
     if (pass > 0 && live[pass - 1] == 0) return;
     View W = wf_view<F>(S, smem_hot);
-    Tally<false> tl{nullptr};
     const int stride = gridDim.x * blockDim.x;
-    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride) {
-        const int flags = __float_as_int(st.sum[slot].w);
-        if (!(flags & kWfAlive)) continue;
-        float4 o = st.ray_o[slot], d = st.ray_d[slot];
-        Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-        Philox rng;
-        rng.have = 0;
-        if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
-            int4 it = st.item[slot];
-            wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)(it.z - 1), rng);
-        }
-        Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
-        st.hit[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f);
-        if (F & F_MEDIA) wf_store_rng(st, slot, rng);
-    }
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride)
+        wf_trace_slot<F>(W, A, st, slot);
 }
 
 // ---- SHADE: one level of color() for every live slot, then refill ----------------------------------
@@ -115,6 +119,110 @@ __global__ void __launch_bounds__(kWfThreads, SRT_WF_TRACE_MINBLOCKS)
 // partial slot, as the fused kernel does), take the next item from the global counter (one atomic per
 // warp), and start the next path: Sobol jitter + camera::get_ray (:827-836).
 // counters[7] is the work-item counter; live[pass] receives the number of slots left alive.
+// One slot of the shade pass; warp-collective (the refill takes work items with one ballot and one
+// atomic per warp): every lane of the warp must call it, each with its own slot.  Returns whether
+// the slot holds a live path afterwards.
+template <uint32_t F>
+SRT_DEV bool wf_shade_slot(const DScene& S, const View& W, const RenderArgs& A, const WfState& st,
+                           const uint32_t* __restrict__ sobol, float* __restrict__ out,
+                           unsigned long long* __restrict__ work_counter, int slot, bool first,
+                           volatile int* exhausted = nullptr) {
+    Tally<false> tl{nullptr};
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n_pixels = A.nx * A.ny;
+    float4 sm = st.sum[slot];
+    int flags = first ? 0 : __float_as_int(sm.w);
+    V3 sum = first ? v3(0.f, 0.f, 0.f) : v3(sm.x, sm.y, sm.z);
+    int4 it = first ? make_int4(0, 0, 0, 0) : st.item[slot];
+    int pixel = it.x, chunk_id = it.y, s_next = it.z, s_stop = it.w;
+    bool alive = (flags & kWfAlive) != 0, has_item = (flags & kWfHasItem) != 0;
+    Philox rng;
+    rng.have = 0;
+    Path P;
+    if (alive) {
+        float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
+        P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+        P.thr = v3(tv.x, tv.y, tv.z);
+        P.depth = __float_as_int(tv.w);
+        P.L = v3(lv.x, lv.y, lv.z);
+        Hit h;
+        h.t = hv.x;
+        h.prim = __float_as_int(hv.y);
+        h.entry = __float_as_int(hv.z);
+        wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)(s_next - 1), rng);
+        if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
+            V3 c = de_nan(P.L);
+            sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
+            alive = false;
+        }
+    }
+    // ---- refill (the regeneration phase of srt_kernels.cuh, per lane and without a threshold) ----
+    if (!alive && has_item && s_next >= s_stop) {
+        float* o = out + 3 * ((size_t)chunk_id * n_pixels + pixel);
+        if (A.n_chunks == 1) {
+            o[0] += sum.x;
+            o[1] += sum.y;
+            o[2] += sum.z;
+        } else {
+            o[0] = sum.x;
+            o[1] = sum.y;
+            o[2] = sum.z;
+        }
+        has_item = false;
+    }
+    const bool need_item = !alive && !has_item;
+    const unsigned m = __ballot_sync(FULL, need_item);
+    // `exhausted` (shared memory, persistent kernel): once the counter has run past the last item
+    // the draining warps stop hammering it
+    if (m && !(exhausted && *exhausted)) {
+        unsigned long long base = 0;
+        if (lane == 0) {
+            base = atomicAdd(work_counter, (unsigned long long)__popc(m));
+            if (exhausted && base >= (unsigned long long)A.n_items) *exhausted = 1;
+        }
+        base = __shfl_sync(FULL, base, 0);
+        const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
+        if (need_item && item < (unsigned long long)A.n_items) {
+            pixel = (int)((unsigned)item / (unsigned)A.n_chunks);
+            chunk_id = (int)((unsigned)item - (unsigned)pixel * (unsigned)A.n_chunks);
+            s_next = A.s_begin + chunk_id * A.chunk;
+            s_stop = min(s_next + A.chunk, A.s_end);
+            sum = v3(0.f, 0.f, 0.f);
+            has_item = true;
+        }
+    }
+    if (!alive && has_item && s_next < s_stop) {
+        int i = pixel % (A.mod_ny ? A.ny : A.nx);
+        int j = A.ny - 1 - (pixel / A.nx);
+        int s = s_next++;
+        double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
+        double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
+        float u = xdiv((float)(sx + (double)i), (float)A.nx);
+        float v = xdiv((float)(sy + (double)j), (float)A.ny);
+        philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
+        P.r = camera_get_ray(S.camera, u, v, rng);
+        P.thr = v3(1.f, 1.f, 1.f);
+        P.L = v3(0.f, 0.f, 0.f);
+        P.depth = 0;
+        alive = true;
+    }
+    // ---- store ------------------------------------------------------------------------------------
+    flags = (alive ? kWfAlive : 0) | (has_item ? kWfHasItem : 0);
+    st.sum[slot] = make_float4(sum.x, sum.y, sum.z, __int_as_float(flags));
+    st.item[slot] = make_int4(pixel, chunk_id, s_next, s_stop);
+    if (alive) {
+        st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
+        st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
+        st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
+        st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
+        wf_store_rng(st, slot, rng);
+        return true;
+    }
+    return false;
+}
+
 template <uint32_t F>
 __global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
     k_wf_shade(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, float* __restrict__ out,
@@ -122,102 +230,55 @@ __global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
     extern __shared__ float4 smem_hot[];
     if (pass > 0 && live[pass - 1] == 0) return;
     View W = wf_view<F>(S, smem_hot);
-    Tally<false> tl{nullptr};
-    const unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const int n_pixels = A.nx * A.ny;
-    unsigned long long* work_counter = counters + 7;
     const int stride = gridDim.x * blockDim.x;
     int n_alive = 0;
     // n_slots is a multiple of 32 and blockDim of 32: the warps of this loop are always full
-    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride) {
-        float4 sm = st.sum[slot];
-        int flags = pass == 0 ? 0 : __float_as_int(sm.w);
-        V3 sum = pass == 0 ? v3(0.f, 0.f, 0.f) : v3(sm.x, sm.y, sm.z);
-        int4 it = pass == 0 ? make_int4(0, 0, 0, 0) : st.item[slot];
-        int pixel = it.x, chunk_id = it.y, s_next = it.z, s_stop = it.w;
-        bool alive = (flags & kWfAlive) != 0, has_item = (flags & kWfHasItem) != 0;
-        Philox rng;
-        rng.have = 0;
-        Path P;
-        if (alive) {
-            float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
-            P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-            P.thr = v3(tv.x, tv.y, tv.z);
-            P.depth = __float_as_int(tv.w);
-            P.L = v3(lv.x, lv.y, lv.z);
-            Hit h;
-            h.t = hv.x;
-            h.prim = __float_as_int(hv.y);
-            h.entry = __float_as_int(hv.z);
-            wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)(s_next - 1), rng);
-            if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
-                V3 c = de_nan(P.L);
-                sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
-                alive = false;
-            }
-        }
-        // ---- refill (the regeneration phase of srt_kernels.cuh, per lane and without a threshold) ----
-        if (!alive && has_item && s_next >= s_stop) {
-            float* o = out + 3 * ((size_t)chunk_id * n_pixels + pixel);
-            if (A.n_chunks == 1) {
-                o[0] += sum.x;
-                o[1] += sum.y;
-                o[2] += sum.z;
-            } else {
-                o[0] = sum.x;
-                o[1] = sum.y;
-                o[2] = sum.z;
-            }
-            has_item = false;
-        }
-        const bool need_item = !alive && !has_item;
-        const unsigned m = __ballot_sync(FULL, need_item);
-        if (m) {
-            unsigned long long base = 0;
-            if (lane == 0) base = atomicAdd(work_counter, (unsigned long long)__popc(m));
-            base = __shfl_sync(FULL, base, 0);
-            const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
-            if (need_item && item < (unsigned long long)A.n_items) {
-                pixel = (int)((unsigned)item / (unsigned)A.n_chunks);
-                chunk_id = (int)((unsigned)item - (unsigned)pixel * (unsigned)A.n_chunks);
-                s_next = A.s_begin + chunk_id * A.chunk;
-                s_stop = min(s_next + A.chunk, A.s_end);
-                sum = v3(0.f, 0.f, 0.f);
-                has_item = true;
-            }
-        }
-        if (!alive && has_item && s_next < s_stop) {
-            int i = pixel % (A.mod_ny ? A.ny : A.nx);
-            int j = A.ny - 1 - (pixel / A.nx);
-            int s = s_next++;
-            double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
-            double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
-            float u = xdiv((float)(sx + (double)i), (float)A.nx);
-            float v = xdiv((float)(sy + (double)j), (float)A.ny);
-            philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-            P.r = camera_get_ray(S.camera, u, v, rng);
-            P.thr = v3(1.f, 1.f, 1.f);
-            P.L = v3(0.f, 0.f, 0.f);
-            P.depth = 0;
-            alive = true;
-        }
-        // ---- store ------------------------------------------------------------------------------------
-        flags = (alive ? kWfAlive : 0) | (has_item ? kWfHasItem : 0);
-        st.sum[slot] = make_float4(sum.x, sum.y, sum.z, __int_as_float(flags));
-        st.item[slot] = make_int4(pixel, chunk_id, s_next, s_stop);
-        if (alive) {
-            st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
-            st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
-            st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
-            st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
-            wf_store_rng(st, slot, rng);
-            n_alive++;
-        }
+    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride)
+        n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, slot, pass == 0) ? 1 : 0;
+    const unsigned total = __reduce_add_sync(0xffffffffu, (unsigned)n_alive);
+    if ((threadIdx.x & 31) == 0 && total) atomicAdd(live + pass, (int)total);
+}
+
+
+// ---- PERSISTENT form: the same two stages as phases of ONE kernel ------------------------------------
+// Every CTA owns a private, contiguous range of the slot pool (slot = base + k * blockDim + thread,
+// k < per_thread: a slot is only ever touched by one thread, coalesced across the warp) and
+// alternates   shade phase -> __syncthreads -> trace phase -> __syncthreads   until a shade phase
+// leaves none of its slots alive.  The barriers are not needed for correctness; they keep every warp
+// of the CTA in the same phase, so the SM's instruction cache holds one stage's code at a time
+// (what the two-kernel form buys), without a launch, a table re-staging and a ramp-up/tail per
+// stage and bounce: profiles/r02_notes.md measured ~14 us of those per launch, 1500 launches per
+// C2 frame.  CTAs take work items from the same global counter, so load balance is dynamic and a
+// CTA's tail is bounded by chunk x depth iterations over its own slots only.
+#ifndef SRT_WFP_THREADS
+#define SRT_WFP_THREADS 768
+#endif
+#ifndef SRT_WFP_MINBLOCKS
+#define SRT_WFP_MINBLOCKS 1
+#endif
+
+template <uint32_t F>
+__global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
+    k_wf_persist(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, float* __restrict__ out,
+                 unsigned long long* __restrict__ counters, int per_thread) {
+    extern __shared__ float4 smem_hot[];
+    __shared__ int s_exhausted;
+    if (threadIdx.x == 0) s_exhausted = 0;
+    View W = wf_view<F>(S, smem_hot);
+    __syncthreads();
+    const int base = blockIdx.x * per_thread * blockDim.x + threadIdx.x;
+    for (int iter = 0;; iter++) {
+        int n_alive = 0;
+        for (int k = 0; k < per_thread; k++)
+            n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, base + k * blockDim.x, iter == 0,
+                                        &s_exhausted)
+                           ? 1
+                           : 0;
+        if (!__syncthreads_or(n_alive)) break;
+        if (n_alive)
+            for (int k = 0; k < per_thread; k++) wf_trace_slot<F>(W, A, st, base + k * blockDim.x);
+        __syncthreads();
     }
-    const unsigned total = __reduce_add_sync(FULL, (unsigned)n_alive);
-    if (lane == 0 && total) atomicAdd(live + pass, (int)total);
 }
 
 }  // namespace srt

@@ -23,11 +23,14 @@ constexpr uint32_t kMask = SRT_WF_VARIANT_MASK(SRT_WF_VARIANT);
 cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, WfVariantInfo* info) {
     auto trace = srt::k_wf_trace<kMask>;
     auto shade = srt::k_wf_shade<kMask>;
+    auto persist = srt::k_wf_persist<kMask>;
     cudaError_t e;
     if (L.smem_bytes > 48 * 1024) {
         e = cudaFuncSetAttribute(trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
         if (e != cudaSuccess) return e;
         e = cudaFuncSetAttribute(shade, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncSetAttribute(persist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
         if (e != cudaSuccess) return e;
     }
     if (info) {
@@ -43,10 +46,20 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         e = cudaFuncGetAttributes(&fa, shade);
         if (e != cudaSuccess) return e;
         info->shade_registers = fa.numRegs;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->persist_blocks_per_sm, persist, SRT_WFP_THREADS,
+                                                          L.smem_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncGetAttributes(&fa, persist);
+        if (e != cudaSuccess) return e;
+        info->persist_registers = fa.numRegs;
+        info->persist_threads = SRT_WFP_THREADS;
         return cudaSuccess;
     }
     const srt::WfState& st = *static_cast<const srt::WfState*>(L.state);
-    if (L.stage == 0)
+    if (L.stage == 2)
+        persist<<<L.grid, SRT_WFP_THREADS, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters,
+                                                                     L.per_thread);
+    else if (L.stage == 0)
         trace<<<L.grid, srt::kWfThreads, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.live, L.pass);
     else
         shade<<<L.grid, srt::kWfThreads, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters, L.live,
