@@ -56,8 +56,9 @@ struct SrtContext {
     uint32_t sobol_n = 0;
     float* d_accum = nullptr;  // srt_render_image's internal accumulation buffer
     size_t accum_cap = 0;
-    float* d_partial = nullptr;  // [n_chunks][n_pixels][3] per-item radiance sums of the last render
-    size_t partial_cap = 0;
+    long long* d_fixed = nullptr;  // [n_pixels][3] fixed-point radiance sums of the render in flight (zero between renders)
+    size_t fixed_cap = 0;
+    bool fixed_dirty = false;
     int variant_blocks[SRT_N_VARIANTS] = {};  // occupancy query results, 0 = not queried yet
     int variant_regs[SRT_N_VARIANTS] = {};
     size_t variant_smem[SRT_N_VARIANTS] = {};  // dynamic shared memory the query was made with
@@ -335,7 +336,7 @@ int srt_context_destroy(SrtContext* ctx) {
     cudaFree(ctx->d_rgb8);
     cudaFree(ctx->d_sobol);
     cudaFree(ctx->d_accum);
-    cudaFree(ctx->d_partial);
+    cudaFree(ctx->d_fixed);
     cudaFree(ctx->d_wf);
     cudaFree(ctx->d_live);
     if (ctx->h_poll) cudaFreeHost(ctx->h_poll);
@@ -983,7 +984,7 @@ int pick_wf_variant(const SrtScene* s) {
 // trace + shade passes until a shade pass leaves no slot alive.  Passes are enqueued kWfBatch at a
 // time; after each batch the live count of its last pass is copied to pinned memory, and the host
 // waits for the copy of the PREVIOUS batch only, so the stream never drains while work remains.
-int run_wavefront(SrtScene* s, const srt::RenderArgs& A, float* out, int v, bool persistent) {
+int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, bool persistent) {
     SrtContext* c = s->ctx;
     const size_t smem = (kWfMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
     WfLaunch L = {};
@@ -1139,18 +1140,13 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     if (wavefront) s->variant = (wf_persistent ? 200 : 100) + wv;
     int blocks_per_sm = std::max(1, info.blocks_per_sm);
 
-    // work decomposition (srt_kernels.cuh): enough items for ~16 per resident lane
+    // work decomposition (srt_kernels.cuh): an item is `chunk` consecutive Sobol indices of one pixel,
+    // numbered pixel-major.  One path per item by default: the lanes of a warp that start paths
+    // together then start them in the same pixel, and the drain at the end of the frame is one path
+    // long (profiles/r01_notes.md, capture F).
     long long n_pixels = (long long)p->nx * p->ny;
-    long long resident = wavefront ? (long long)c->sm_count * (std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 2048)) & ~31)
-                                   : (long long)c->sm_count * blocks_per_sm * srt::kRenderThreads;
-    long long want_items = 16 * resident;
-    int n_chunks = 1;
-    while (n_chunks < count && n_pixels * n_chunks < want_items) n_chunks <<= 1;
-    n_chunks = std::min(n_chunks, count);
-    n_chunks = env_int("SRT_CHUNKS", n_chunks);
-    n_chunks = std::max(1, std::min(n_chunks, count));
-    int chunk = (count + n_chunks - 1) / n_chunks;
-    n_chunks = (count + chunk - 1) / chunk;
+    int chunk = std::max(1, std::min(count, env_int("SRT_CHUNK", 1)));
+    int n_chunks = (count + chunk - 1) / chunk;
 
     srt::RenderArgs A;
     A.nx = p->nx;
@@ -1162,38 +1158,45 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     A.mod_ny = (p->flags & SRT_COMPAT_PIXEL_MOD_NY) ? 1 : 0;
     A.chunk = chunk;
     A.n_chunks = n_chunks;
-    A.n_items = (unsigned)(n_pixels * n_chunks);
+    A.n_items = (unsigned long long)n_pixels * (unsigned long long)n_chunks;
+    A.fx_clamp = 4.0e9f / (float)count;
     A.regen_threshold = std::max(1, std::min(32, env_int("SRT_REGEN", 8)));
     A.grab = std::max(32, env_int("SRT_GRAB", 128));
     A.cta_sync = std::max(0, std::min(2, env_int("SRT_CTA_SYNC", 0)));
     A.dbg_pixel = counting ? env_int("SRT_DEBUG_PIXEL", -1) : -1;
     A.dbg_sample = counting ? env_int("SRT_DEBUG_SAMPLE", -1) : -1;
 
-    float* out = accum;
-    if (n_chunks > 1) {
-        size_t need = sizeof(float) * 3 * (size_t)n_pixels * n_chunks;
-        if (c->partial_cap < need) {
+    // the kernels accumulate into the context's fixed-point buffer; k_fixed_to_accum adds it to the
+    // caller's float buffer and leaves it zero for the next render
+    {
+        size_t need = sizeof(long long) * 3 * (size_t)n_pixels;
+        if (c->fixed_cap < need) {
             CUDA_TRY(cudaStreamSynchronize(c->stream));
-            cudaFree(c->d_partial);
-            c->d_partial = nullptr;
-            c->partial_cap = 0;
-            CUDA_TRY(cudaMalloc(&c->d_partial, need));
-            c->partial_cap = need;
+            cudaFree(c->d_fixed);
+            c->d_fixed = nullptr;
+            c->fixed_cap = 0;
+            CUDA_TRY(cudaMalloc(&c->d_fixed, need));
+            c->fixed_cap = need;
+            c->fixed_dirty = true;
         }
-        out = c->d_partial;
+        if (c->fixed_dirty) CUDA_TRY(cudaMemsetAsync(c->d_fixed, 0, c->fixed_cap, c->stream));
+        c->fixed_dirty = true;
     }
+    long long* out = c->d_fixed;
+    auto finish = [&]() -> int {
+        long long nv = 3 * n_pixels;
+        srt::k_fixed_to_accum<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(c->d_fixed, nv, accum);
+        c->launches++;
+        CUDA_TRY(cudaGetLastError());
+        c->fixed_dirty = false;
+        return 0;
+    };
     // counters[7] is the work counter
     CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
     if (wavefront) {
         int rc2 = run_wavefront(s, A, out, wv, wf_persistent);
         if (rc2) return rc2;
-        if (n_chunks > 1) {
-            long long nv = 3 * n_pixels;
-            srt::k_sum_partials<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(c->d_partial, n_chunks, nv, accum);
-            c->launches++;
-            CUDA_TRY(cudaGetLastError());
-        }
-        return 0;
+        return finish();
     }
     long long warps_needed = ((long long)A.n_items + 31) / 32;
     long long blocks_needed = (warps_needed + (srt::kRenderThreads / 32) - 1) / (srt::kRenderThreads / 32);
@@ -1203,13 +1206,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     cudaError_t e = kVariants[v](L, nullptr);
     c->launches++;
     if (e != cudaSuccess) return fail(SRT_E_CUDA, "k_render (variant %d): %s", v, cudaGetErrorString(e));
-    if (n_chunks > 1) {
-        long long nv = 3 * n_pixels;
-        srt::k_sum_partials<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(c->d_partial, n_chunks, nv, accum);
-        c->launches++;
-        CUDA_TRY(cudaGetLastError());
-    }
-    return 0;
+    return finish();
 }
 
 }  // namespace

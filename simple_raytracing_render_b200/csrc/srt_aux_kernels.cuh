@@ -56,14 +56,14 @@ __global__ void __launch_bounds__(128) k_light_pdf(DScene S, const float* __rest
     out[i] = S.n_lights > 0 ? light_pdf_value<F_ALL_SCENE>(W, v3(q[0], q[1], q[2]), v3(q[3], q[4], q[5]), tl) : 0.f;
 }
 
-// accum[i] += partial[0][i] + partial[1][i] + ... in fixed order (n_values = 3 * n_pixels).
-__global__ void __launch_bounds__(256) k_sum_partials(const float* __restrict__ partial, int n_chunks, long long n_values,
-                                                      float* __restrict__ accum) {
+// accum[i] += fixed[i] * 2^-31 (the render kernels' fixed-point sums, srt_kernels.cuh: item_commit), and
+// fixed[i] is cleared for the next render (n_values = 3 * n_pixels).
+__global__ void __launch_bounds__(256) k_fixed_to_accum(long long* __restrict__ fixed, long long n_values,
+                                                        float* __restrict__ accum) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n_values) return;
-    float s = partial[i];
-    for (int c = 1; c < n_chunks; c++) s += partial[(size_t)c * n_values + i];
-    accum[i] += s;
+    accum[i] += (float)((double)fixed[i] * 4.656612873077392578125e-10);
+    fixed[i] = 0;
 }
 
 // mean -> sqrt -> int(255.99 c) -> clamp (Raytracing_n.cpp:848-862)

@@ -14,7 +14,8 @@ struct RenderArgs {
     int mod_ny;           // SRT_COMPAT_PIXEL_MOD_NY
     int chunk;            // Sobol indices per work item
     int n_chunks;         // work items per pixel
-    unsigned n_items;     // n_pixels * n_chunks
+    unsigned long long n_items;  // n_pixels * n_chunks
+    float fx_clamp;       // largest |item sum| the fixed-point accumulator takes (4e9 / samples per pixel)
     int regen_threshold;  // idle lanes in a warp that trigger a regeneration phase
     int grab;             // work items a warp takes from the global counter at a time
     int dbg_pixel, dbg_sample;  // counting build: print the bounces of this one path (-1: off)
@@ -22,6 +23,29 @@ struct RenderArgs {
 };
 
 constexpr int kRenderThreads = 256;
+
+// item number -> (pixel, chunk, first and one-past-last Sobol index): pixel-major, so that the lanes
+// which start paths together (they take consecutive items) start them in the same pixel
+SRT_DEV void decode_item(const RenderArgs& A, unsigned long long item, int& pixel, int& chunk_id, int& s_next, int& s_stop) {
+    pixel = (int)(item / (unsigned)A.n_chunks);
+    chunk_id = (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
+    s_next = A.s_begin + chunk_id * A.chunk;
+    s_stop = min(s_next + A.chunk, A.s_end);
+}
+
+// The image accumulates in 64-bit fixed point (31 fractional bits) with integer atomics: integer
+// addition is associative, so the sum of a pixel does not depend on the order in which its items
+// finish — the frame is bit-reproducible for ANY schedule, with 24 bytes per pixel instead of one
+// float3 slot per work item, which is what lets a work item be a single path.  x * 2^31 is exact in
+// float and its conversion is exact; contributions are clamped so that the sum cannot overflow.
+SRT_DEV void item_commit(long long* __restrict__ fx, int pixel, V3 sum, float clampv) {
+    unsigned long long* o = reinterpret_cast<unsigned long long*>(fx + 3 * (size_t)pixel);
+    float x = fminf(fmaxf(sum.x, -clampv), clampv), y = fminf(fmaxf(sum.y, -clampv), clampv),
+          z = fminf(fmaxf(sum.z, -clampv), clampv);
+    atomicAdd(o + 0, (unsigned long long)__float2ll_rn(x * 2147483648.0f));
+    atomicAdd(o + 1, (unsigned long long)__float2ll_rn(y * 2147483648.0f));
+    atomicAdd(o + 2, (unsigned long long)__float2ll_rn(z * 2147483648.0f));
+}
 
 SRT_DEV View global_view(const DScene& S) { return View{S, S.entries, S.ops, S.dprims, S.lights}; }
 
@@ -50,7 +74,7 @@ SRT_DEV View global_view(const DScene& S) { return View{S, S.entries, S.ops, S.d
 
 template <uint32_t F, bool COUNT>
 __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
-    k_render(DScene S, RenderArgs A, const uint32_t* __restrict__ sobol, float* __restrict__ out,
+    k_render(DScene S, RenderArgs A, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
              unsigned long long* __restrict__ counters) {
     extern __shared__ float4 smem_hot[];
     const DEntry* entries = S.entries;
@@ -89,7 +113,7 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
     P.depth = 0;
     Philox rng;
     // warp-uniform range of items
-    unsigned w_cur = 0, w_end = 0;
+    unsigned long long w_cur = 0, w_end = 0;
     bool exhausted = false;
 
     // cta_sync: the kernel is several times the instruction cache, and warps at unrelated program
@@ -105,40 +129,27 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
             // ---- regeneration phase ---------------------------------------------------------------
             bool item_done = !alive && has_item && s_next >= s_stop;
             if (item_done) {
-                float* o = out + 3 * ((size_t)chunk_id * n_pixels + pixel);
-                if (A.n_chunks == 1) {
-                    o[0] += sum.x;
-                    o[1] += sum.y;
-                    o[2] += sum.z;
-                } else {
-                    o[0] = sum.x;
-                    o[1] = sum.y;
-                    o[2] = sum.z;
-                }
+                item_commit(out, pixel, sum, A.fx_clamp);
                 has_item = false;
             }
             bool need_item = !alive && !has_item;
             unsigned m = __ballot_sync(FULL, need_item);
             if (m) {
                 if (w_cur == w_end && !exhausted) {
-                    unsigned base = 0;
-                    if (lane == 0) base = (unsigned)atomicAdd(work_counter, (unsigned long long)A.grab);
+                    unsigned long long base = 0;
+                    if (lane == 0) base = atomicAdd(work_counter, (unsigned long long)A.grab);
                     base = __shfl_sync(FULL, base, 0);
                     if (base >= A.n_items) {
                         exhausted = true;
                     } else {
                         w_cur = base;
-                        w_end = min(base + (unsigned)A.grab, A.n_items);
+                        w_end = min(base + (unsigned long long)A.grab, A.n_items);
                     }
                 }
-                unsigned avail = w_end - w_cur;
+                unsigned avail = (unsigned)(w_end - w_cur);
                 unsigned rank = __popc(m & lt_mask);
                 if (need_item && rank < avail) {
-                    unsigned item = w_cur + rank;
-                    pixel = (int)(item / (unsigned)A.n_chunks);
-                    chunk_id = (int)(item - (unsigned)pixel * (unsigned)A.n_chunks);
-                    s_next = A.s_begin + chunk_id * A.chunk;
-                    s_stop = min(s_next + A.chunk, A.s_end);
+                    decode_item(A, w_cur + rank, pixel, chunk_id, s_next, s_stop);
                     sum = v3(0.f, 0.f, 0.f);
                     has_item = true;
                 }

@@ -314,23 +314,41 @@ struct Path {
     int depth;
 };
 
-// One level of color() (Raytracing_n.cpp:55-106) for a path whose ray has just been traced to `h`.
-// Returns true when the path continues (P.r is the next ray), false when it has ended (P.L is final).
+// One level of color() (Raytracing_n.cpp:55-106) for a path whose ray has just been traced to `h`,
+// in three parts so that a scheduler can run the `while (pdf_val == 0)` rejection loop (:79-84) one
+// iteration at a time across different paths (srt_wavefront.cuh); shade_bounce below chains them.
+enum ShadeStatus { SHADE_ENDED = 0, SHADE_CONTINUES = 1, SHADE_SAMPLE = 2 };
+
+// What the sampling loop of a non-specular vertex reads and writes.
+struct SampleCtx {
+    V3 p;            // rec.p
+    V3 wo;           // direction of the incoming ray (r.direction())
+    float time;      // r.time()
+    V3 attenuation;  // srec.attenuation
+    BsdfPdf B;       // the material's pdf object (normal, onb, parameters, Beckmann stash)
+    int mat_type;
+    V3 sdir;         // out: the accepted direction
+    float pdf_val;   // out: its mixture density
+    int iters;
+};
+
+// Part 1 (:58-74): miss / emission / depth cap / specular scatter, or the set-up of the sampling loop.
 template <uint32_t F, bool COUNT>
-SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, Philox& rng, Tally<COUNT> tl) {
+SRT_DEV ShadeStatus shade_hit(const View& W, Path& P, const Hit& h, int max_depth, Philox& rng, SampleCtx& C,
+                              Tally<COUNT> tl) {
     const DScene& S = W.S;
     if (h.prim < 0) {
         // miss: color() returns vec3(0) — kept as `thr * 0` so that an inf / NaN throughput poisons
         // the sample exactly as in the recursive form (de_nan then zeroes those channels)
         P.L = fm::madd(P.thr, 0.f, P.L);
-        return false;
+        return SHADE_ENDED;
     }
     int mat_index;
     if ((F & F_MEDIA) && h.prim >= S.n_prims)
         mat_index = S.media[h.prim - S.n_prims].phase_material;
     else
         mat_index = load_prim(W.dprims + h.prim).material;
-    if (mat_index < 0) return false;  // no material: the reference would dereference null
+    if (mat_index < 0) return SHADE_ENDED;  // no material: the reference would dereference null
     DMaterial m = load_material(S.materials + mat_index);
     HitRecord rec = material_needs_uv<F>(m) ? make_record<F, true>(W, P.r, h) : make_record<F, false>(W, P.r, h);
     const Ray r = P.r;
@@ -342,11 +360,11 @@ SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, P
         } else {
             P.L = fm::madd(P.thr, 0.f, P.L);
         }
-        return false;
+        return SHADE_ENDED;
     }
     if (!(P.depth < max_depth)) {  // Raytracing_n.cpp:63: returns emitted (0 for every non-light)
         P.L = fm::madd(P.thr, 0.f, P.L);
-        return false;
+        return SHADE_ENDED;
     }
     // specular materials: return attenuation * color(specular_ray) (emitted is dropped, :66-70)
     if ((F & F_METAL) && m.type == SRT_MAT_METAL) {  // material.h:248-256
@@ -355,7 +373,7 @@ SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, P
         P.thr = fm::mul(P.thr, v3(m.c[0], m.c[1], m.c[2]));
         P.r = Ray{rec.p, dir, 0.f};
         P.depth++;
-        return true;
+        return SHADE_CONTINUES;
     }
     if ((F & F_DIELECTRIC) && m.type == SRT_MAT_DIELECTRIC) {  // material.h:285-324
         float ref_idx = m.p[0];
@@ -380,18 +398,17 @@ SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, P
         V3 dir = (rand_f(rng) < reflect_prob) ? reflected : refracted;
         P.r = Ray{rec.p, dir, 0.f};
         P.depth++;
-        return true;
+        return SHADE_CONTINUES;
     }
     if ((F & F_MEDIA) && m.type == SRT_MAT_ISOTROPIC) {  // material.h:362-367
         V3 dir = random_in_unit_sphere(rng);
         P.thr = fm::mul(P.thr, material_color<F>(S, m, rec));
         P.r = Ray{rec.p, dir, 0.f};
         P.depth++;
-        return true;
+        return SHADE_CONTINUES;
     }
     // non-specular: lambertian, orennayar, beckmann, brdfmaterial
-    V3 attenuation;
-    BsdfPdf B;
+    BsdfPdf& B = C.B;
     B.n = rec.normal;
     B.stash = kBeckmannStashInit;
     B.a = m.p[0];
@@ -402,48 +419,64 @@ SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, P
         // (DESIGN.md §5): the cosine_pdf every other diffuse material gets.  The discarded lookup has
         // no side effect and is not evaluated here; its arithmetic is exported for parity through
         // srt_merl_lookup (srt_microfacet.cuh: merl_lookup).
-        attenuation = v3(m.c[0], m.c[1], m.c[2]);
+        C.attenuation = v3(m.c[0], m.c[1], m.c[2]);
         B.kind = SRT_MAT_LAMBERTIAN;
     } else {
-        attenuation = material_color<F>(S, m, rec);
+        C.attenuation = material_color<F>(S, m, rec);
         B.kind = (F & (F_ORENNAYAR | F_BECKMANN)) ? m.type : SRT_MAT_LAMBERTIAN;
     }
     B.uvw = onb_fast(rec.normal);
-    V3 sdir = v3(0.f, 0.f, 0.f);
-    float pdf_val = 0.f;
-    if (S.n_lights > 0) {  // Raytracing_n.cpp:75-84: mixture_pdf(hitable_pdf, bsdf pdf)
-        int iters = 0;
-        while (pdf_val == 0.f) {
-            if (++iters > kMaxRejectIters) break;
-            if (COUNT) tl.c->reject_iters++;
-            if (rand_f(rng) < 0.5f)  // pdf.h:183-189
-                sdir = light_random<F>(W, rec.p, rng);
-            else
-                sdir = bsdf_generate<F>(B, r.d, rng);
-            float pl = light_pdf_value<F>(W, rec.p, sdir, tl);
-            float pb = bsdf_value<F>(B, r.d, sdir);
-            pdf_val = 0.5f * pl + 0.5f * pb;  // pdf.h:177-182
-        }
-    } else {  // Raytracing_n.cpp:85-89
-        sdir = bsdf_generate<F>(B, r.d, rng);
-        pdf_val = bsdf_value<F>(B, r.d, sdir);
+    C.p = rec.p;
+    C.wo = r.d;
+    C.time = r.time;
+    C.mat_type = m.type;
+    C.sdir = v3(0.f, 0.f, 0.f);
+    C.pdf_val = 0.f;
+    C.iters = 0;
+    return SHADE_SAMPLE;
+}
+
+// Part 2: ONE iteration of the loop at Raytracing_n.cpp:79-84 (mixture_pdf(hitable_pdf, bsdf pdf),
+// pdf.h:173-193), or the single draw of the light-less branch (:85-89).  Returns true when the loop
+// is over (a direction with non-zero density, or the iteration bound).
+template <uint32_t F, bool COUNT>
+SRT_DEV bool shade_sample_iter(const View& W, SampleCtx& C, Philox& rng, Tally<COUNT> tl) {
+    if (W.S.n_lights > 0) {
+        if (++C.iters > kMaxRejectIters) return true;
+        if (COUNT) tl.c->reject_iters++;
+        if (rand_f(rng) < 0.5f)  // pdf.h:183-189
+            C.sdir = light_random<F>(W, C.p, rng);
+        else
+            C.sdir = bsdf_generate<F>(C.B, C.wo, rng);
+        float pl = light_pdf_value<F>(W, C.p, C.sdir, tl);
+        float pb = bsdf_value<F>(C.B, C.wo, C.sdir);
+        C.pdf_val = 0.5f * pl + 0.5f * pb;  // pdf.h:177-182
+        return C.pdf_val != 0.f;
     }
+    C.sdir = bsdf_generate<F>(C.B, C.wo, rng);
+    C.pdf_val = bsdf_value<F>(C.B, C.wo, C.sdir);
+    return true;
+}
+
+// Part 3 (:90-99): weight the throughput and set the continuation ray.
+template <uint32_t F, bool COUNT>
+SRT_DEV bool shade_finish(Path& P, const SampleCtx& C, Tally<COUNT> tl) {
     float spdf;
-    if ((F & F_BECKMANN) && m.type == SRT_MAT_BECKMANN) {
-        spdf = beckmann_scattering_pdf(rec.normal, m.p[0], m.p[1], r.d, sdir);
+    if ((F & F_BECKMANN) && C.mat_type == SRT_MAT_BECKMANN) {
+        spdf = beckmann_scattering_pdf(C.B.n, C.B.a, C.B.b, C.wo, C.sdir);
     } else {  // material.h:100-105, :133-137, :207-213
-        float c = fm::dot(rec.normal, sdir) * fm::rlength(sdir);
+        float c = fm::dot(C.B.n, C.sdir) * fm::rlength(C.sdir);
         if (c < 0.f) c = 0.f;
         spdf = c * fm::kInvPi;
     }
     // emitted is 0 for every scattering material (material.h:89-92)
-    float wgt = spdf / pdf_val;
+    float wgt = spdf / C.pdf_val;
     if (COUNT && tl.c->dbg)
-        printf("[dbg]   mat %d n=(%g %g %g) p=(%g %g %g) sdir=(%g %g %g) spdf %g pdf_val %g stash %g wgt %g\n", m.type,
-               rec.normal.x, rec.normal.y, rec.normal.z, rec.p.x, rec.p.y, rec.p.z, sdir.x, sdir.y, sdir.z, spdf, pdf_val,
-               B.stash, wgt);
-    P.thr = fm::mul(P.thr, fm::scale(attenuation, wgt));
-    P.r = Ray{rec.p, sdir, r.time};
+        printf("[dbg]   mat %d n=(%g %g %g) p=(%g %g %g) sdir=(%g %g %g) spdf %g pdf_val %g stash %g wgt %g\n", C.mat_type,
+               C.B.n.x, C.B.n.y, C.B.n.z, C.p.x, C.p.y, C.p.z, C.sdir.x, C.sdir.y, C.sdir.z, spdf, C.pdf_val, C.B.stash,
+               wgt);
+    P.thr = fm::mul(P.thr, fm::scale(C.attenuation, wgt));
+    P.r = Ray{C.p, C.sdir, C.time};
     P.depth++;
     // a zero throughput cannot contribute any more: finite * 0 == 0 in the recursive form too
     if (P.thr.x == 0.f && P.thr.y == 0.f && P.thr.z == 0.f) {
@@ -451,6 +484,17 @@ SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, P
         return false;
     }
     return true;
+}
+
+// Returns true when the path continues (P.r is the next ray), false when it has ended (P.L is final).
+template <uint32_t F, bool COUNT>
+SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, Philox& rng, Tally<COUNT> tl) {
+    SampleCtx C;
+    ShadeStatus st = shade_hit<F>(W, P, h, max_depth, rng, C, tl);
+    if (st != SHADE_SAMPLE) return st == SHADE_CONTINUES;
+    while (!shade_sample_iter<F>(W, C, rng, tl)) {
+    }
+    return shade_finish<F>(P, C, tl);
 }
 
 // camera::get_ray (camera.h:51-59).  Exact arithmetic: these rays are what srt_trace_closest is

@@ -18,7 +18,7 @@ struct RenderLaunch {
     const DScene* scene;
     const srt::RenderArgs* args;
     const uint32_t* sobol;
-    float* out;
+    long long* out;  // fixed-point accumulation buffer, 3 per pixel
     unsigned long long* counters;
     int grid;  // 0: only query (blocks_per_sm, registers)
     size_t smem_bytes;
@@ -65,7 +65,7 @@ struct WfLaunch {
     const srt::RenderArgs* args;
     const void* state;  // srt::WfState
     const uint32_t* sobol;
-    float* out;
+    long long* out;  // fixed-point accumulation buffer, 3 per pixel
     unsigned long long* counters;
     int* live;    // live[pass] = slots left alive by shade pass `pass`
     int pass;

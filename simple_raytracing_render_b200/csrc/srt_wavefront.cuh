@@ -124,7 +124,7 @@ __global__ void __launch_bounds__(kWfThreads, SRT_WF_TRACE_MINBLOCKS)
 // the slot holds a live path afterwards.
 template <uint32_t F>
 SRT_DEV bool wf_shade_slot(const DScene& S, const View& W, const RenderArgs& A, const WfState& st,
-                           const uint32_t* __restrict__ sobol, float* __restrict__ out,
+                           const uint32_t* __restrict__ sobol, long long* __restrict__ out,
                            unsigned long long* __restrict__ work_counter, int slot, bool first,
                            volatile int* exhausted = nullptr) {
     Tally<false> tl{nullptr};
@@ -160,16 +160,7 @@ SRT_DEV bool wf_shade_slot(const DScene& S, const View& W, const RenderArgs& A, 
     }
     // ---- refill (the regeneration phase of srt_kernels.cuh, per lane and without a threshold) ----
     if (!alive && has_item && s_next >= s_stop) {
-        float* o = out + 3 * ((size_t)chunk_id * n_pixels + pixel);
-        if (A.n_chunks == 1) {
-            o[0] += sum.x;
-            o[1] += sum.y;
-            o[2] += sum.z;
-        } else {
-            o[0] = sum.x;
-            o[1] = sum.y;
-            o[2] = sum.z;
-        }
+        item_commit(out, pixel, sum, A.fx_clamp);
         has_item = false;
     }
     const bool need_item = !alive && !has_item;
@@ -180,15 +171,12 @@ SRT_DEV bool wf_shade_slot(const DScene& S, const View& W, const RenderArgs& A, 
         unsigned long long base = 0;
         if (lane == 0) {
             base = atomicAdd(work_counter, (unsigned long long)__popc(m));
-            if (exhausted && base >= (unsigned long long)A.n_items) *exhausted = 1;
+            if (exhausted && base >= A.n_items) *exhausted = 1;
         }
         base = __shfl_sync(FULL, base, 0);
         const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
-        if (need_item && item < (unsigned long long)A.n_items) {
-            pixel = (int)((unsigned)item / (unsigned)A.n_chunks);
-            chunk_id = (int)((unsigned)item - (unsigned)pixel * (unsigned)A.n_chunks);
-            s_next = A.s_begin + chunk_id * A.chunk;
-            s_stop = min(s_next + A.chunk, A.s_end);
+        if (need_item && item < A.n_items) {
+            decode_item(A, item, pixel, chunk_id, s_next, s_stop);
             sum = v3(0.f, 0.f, 0.f);
             has_item = true;
         }
@@ -225,7 +213,7 @@ SRT_DEV bool wf_shade_slot(const DScene& S, const View& W, const RenderArgs& A, 
 
 template <uint32_t F>
 __global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
-    k_wf_shade(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, float* __restrict__ out,
+    k_wf_shade(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
                unsigned long long* __restrict__ counters, int* __restrict__ live, int pass) {
     extern __shared__ float4 smem_hot[];
     if (pass > 0 && live[pass - 1] == 0) return;
@@ -253,31 +241,205 @@ __global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
 #ifndef SRT_WFP_THREADS
 #define SRT_WFP_THREADS 768
 #endif
+#ifndef SRT_WFP_LANE_SCHED
+#define SRT_WFP_LANE_SCHED 0  // 1: wf_shade_phase (rejection loop scheduled per lane); measured slower, see notes
+#endif
+#ifndef SRT_WFP_DYNAMIC
+#define SRT_WFP_DYNAMIC 1  // warps take 32-slot groups from a shared-memory cursor instead of a fixed mapping
+#endif
 #ifndef SRT_WFP_MINBLOCKS
 #define SRT_WFP_MINBLOCKS 1
 #endif
 
+// The shade phase of the persistent kernel, for one warp: wf_shade_slot's work, but scheduled per
+// LANE.  A lane that reaches the `while (pdf_val == 0)` rejection loop of color() (:79-84) keeps its
+// slot and runs ONE iteration per trip of the loop below, while the lanes that are done store their
+// slot and fetch the next one from the CTA's cursor.  In the per-slot form the warp waits for its
+// unluckiest lane: the loop ran at 3 of 32 lanes and held a quarter of the kernel's instructions
+// (profiles/r01_notes.md, capture E).  Same paths, same Philox counters, same sums.
+template <uint32_t F>
+SRT_DEV int wf_shade_phase(const DScene& S, const View& W, const RenderArgs& A, const WfState& st,
+                           const uint32_t* __restrict__ sobol, long long* __restrict__ out,
+                           unsigned long long* __restrict__ work_counter, int cta_base, int n_cta_slots, int* cursor,
+                           volatile int* exhausted, bool first) {
+    Tally<false> tl{nullptr};
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int n_pixels = A.nx * A.ny;
+    int n_alive = 0;
+    bool sampling = false, more = true;
+    int slot = 0;
+    V3 sum = v3(0.f, 0.f, 0.f);
+    int pixel = 0, chunk_id = 0, s_next = 0, s_stop = 0;
+    bool has_item = false;
+    Philox rng;
+    rng.have = 0;
+    Path P;
+    SampleCtx C;
+    for (;;) {
+        // ---- 1. lanes without a pending vertex take the next slots of this CTA ------------------------
+        const unsigned free_m = __ballot_sync(FULL, !sampling);
+        bool got = false;
+        if (more && free_m) {
+            int base = 0;
+            if (lane == 0) base = atomicAdd(cursor, __popc(free_m));
+            base = __shfl_sync(FULL, base, 0);
+            const int idx = base + __popc(free_m & lt_mask);
+            got = !sampling && idx < n_cta_slots;
+            slot = got ? cta_base + idx : slot;
+            more = base + __popc(free_m) < n_cta_slots;
+        }
+        if (!__ballot_sync(FULL, got || sampling)) break;
+        bool finishing = false, alive = false;
+        if (got) {
+            float4 sm = st.sum[slot];
+            int flags = first ? 0 : __float_as_int(sm.w);
+            sum = first ? v3(0.f, 0.f, 0.f) : v3(sm.x, sm.y, sm.z);
+            int4 it = first ? make_int4(0, 0, 0, 0) : st.item[slot];
+            pixel = it.x, chunk_id = it.y, s_next = it.z, s_stop = it.w;
+            alive = (flags & kWfAlive) != 0;
+            has_item = (flags & kWfHasItem) != 0;
+            finishing = true;
+            if (alive) {
+                float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
+                P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+                P.thr = v3(tv.x, tv.y, tv.z);
+                P.depth = __float_as_int(tv.w);
+                P.L = v3(lv.x, lv.y, lv.z);
+                Hit h;
+                h.t = hv.x;
+                h.prim = __float_as_int(hv.y);
+                h.entry = __float_as_int(hv.z);
+                wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)(s_next - 1), rng);
+                ShadeStatus ss = shade_hit<F>(W, P, h, A.max_depth, rng, C, tl);
+                if (ss == SHADE_SAMPLE) {
+                    sampling = true;
+                    finishing = false;
+                } else if (ss == SHADE_ENDED) {
+                    V3 c = de_nan(P.L);
+                    sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
+                    alive = false;
+                }
+            }
+        }
+        // ---- 2. one iteration of the rejection loop for every lane that holds a diffuse vertex ----------
+        if (sampling && shade_sample_iter<F>(W, C, rng, tl)) {
+            alive = shade_finish<F>(P, C, tl);
+            if (!alive) {
+                V3 c = de_nan(P.L);
+                sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
+            }
+            sampling = false;
+            finishing = true;
+        }
+        // ---- 3. lanes that are through: close / take a work item, start the next path, store ------------
+        if (finishing && !alive && has_item && s_next >= s_stop) {
+            item_commit(out, pixel, sum, A.fx_clamp);
+            has_item = false;
+        }
+        const bool need_item = finishing && !alive && !has_item;
+        const unsigned m = __ballot_sync(FULL, need_item);
+        if (m && !*exhausted) {
+            unsigned long long base = 0;
+            if (lane == 0) {
+                base = atomicAdd(work_counter, (unsigned long long)__popc(m));
+                if (base >= A.n_items) *exhausted = 1;
+            }
+            base = __shfl_sync(FULL, base, 0);
+            const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
+            if (need_item && item < A.n_items) {
+                decode_item(A, item, pixel, chunk_id, s_next, s_stop);
+                sum = v3(0.f, 0.f, 0.f);
+                has_item = true;
+            }
+        }
+        if (finishing) {
+            if (!alive && has_item && s_next < s_stop) {
+                int i = pixel % (A.mod_ny ? A.ny : A.nx);
+                int j = A.ny - 1 - (pixel / A.nx);
+                int s = s_next++;
+                double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
+                double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
+                float u = xdiv((float)(sx + (double)i), (float)A.nx);
+                float v = xdiv((float)(sy + (double)j), (float)A.ny);
+                philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
+                P.r = camera_get_ray(S.camera, u, v, rng);
+                P.thr = v3(1.f, 1.f, 1.f);
+                P.L = v3(0.f, 0.f, 0.f);
+                P.depth = 0;
+                alive = true;
+            }
+            const int flags = (alive ? kWfAlive : 0) | (has_item ? kWfHasItem : 0);
+            st.sum[slot] = make_float4(sum.x, sum.y, sum.z, __int_as_float(flags));
+            st.item[slot] = make_int4(pixel, chunk_id, s_next, s_stop);
+            if (alive) {
+                st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
+                st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
+                st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
+                st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
+                wf_store_rng(st, slot, rng);
+                n_alive++;
+            }
+        }
+    }
+    return n_alive;
+}
+
 template <uint32_t F>
 __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
-    k_wf_persist(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, float* __restrict__ out,
+    k_wf_persist(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
                  unsigned long long* __restrict__ counters, int per_thread) {
     extern __shared__ float4 smem_hot[];
     __shared__ int s_exhausted;
-    if (threadIdx.x == 0) s_exhausted = 0;
+    __shared__ int s_cursor[2];  // next slot of the shade phase / next 32-slot group of the trace phase
+    if (threadIdx.x == 0) s_exhausted = s_cursor[0] = s_cursor[1] = 0;
     View W = wf_view<F>(S, smem_hot);
     __syncthreads();
-    const int base = blockIdx.x * per_thread * blockDim.x + threadIdx.x;
+    const int n_cta_slots = per_thread * blockDim.x;
+    const int cta_base = blockIdx.x * n_cta_slots;
+    const int lane = threadIdx.x & 31;
     for (int iter = 0;; iter++) {
+#if SRT_WFP_LANE_SCHED
+        const int n_alive = wf_shade_phase<F>(S, W, A, st, sobol, out, counters + 7, cta_base, n_cta_slots, &s_cursor[0],
+                                              &s_exhausted, iter == 0);
+#else
         int n_alive = 0;
-        for (int k = 0; k < per_thread; k++)
-            n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, base + k * blockDim.x, iter == 0,
-                                        &s_exhausted)
+#if SRT_WFP_DYNAMIC
+        for (;;) {
+            int g = 0;
+            if (lane == 0) g = atomicAdd(&s_cursor[0], 32);
+            g = __shfl_sync(0xffffffffu, g, 0);
+            if (g >= n_cta_slots) break;
+            n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, cta_base + g + lane, iter == 0, &s_exhausted)
                            ? 1
                            : 0;
-        if (!__syncthreads_or(n_alive)) break;
-        if (n_alive)
-            for (int k = 0; k < per_thread; k++) wf_trace_slot<F>(W, A, st, base + k * blockDim.x);
+        }
+#else
+        for (int k = 0; k < per_thread; k++)
+            n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, cta_base + k * blockDim.x + threadIdx.x,
+                                        iter == 0, &s_exhausted)
+                           ? 1
+                           : 0;
+#endif
+#endif
+        const int any = __syncthreads_or(n_alive);
+        if (threadIdx.x == 0) s_cursor[0] = 0;  // next read after the barrier below
+        if (!any) break;
+        // trace phase: warps take groups of 32 slots until the CTA's range is through
+#if SRT_WFP_DYNAMIC
+        for (;;) {
+            int g = 0;
+            if (lane == 0) g = atomicAdd(&s_cursor[1], 32);
+            g = __shfl_sync(0xffffffffu, g, 0);
+            if (g >= n_cta_slots) break;
+            wf_trace_slot<F>(W, A, st, cta_base + g + lane);
+        }
+#else
+        for (int k = 0; k < per_thread; k++) wf_trace_slot<F>(W, A, st, cta_base + k * blockDim.x + threadIdx.x);
+#endif
         __syncthreads();
+        if (threadIdx.x == 0) s_cursor[1] = 0;  // next read after the next barrier
     }
 }
 

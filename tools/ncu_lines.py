@@ -57,6 +57,12 @@ def main():
     for (f, _), v in agg.items():
         byfile[f] += v["samples"]
     print("samples by file:", ", ".join(f"{f} {v / ts * 100:.1f}%" for f, v in byfile.most_common()))
+    # where the lanes are lost: warp instructions and samples bucketed by the line's mean active lanes
+    buckets = [(0, 6), (6, 12), (12, 20), (20, 33)]
+    for lo, hi in buckets:
+        sel = [v for v in agg.values() if v["instr"] and lo <= v["thr"] / v["instr"] < hi]
+        print(f"lines with {lo:2d} <= active < {hi:2d}: instr {sum(v['instr'] for v in sel) / ti * 100:5.1f}%  "
+              f"samples {sum(v['samples'] for v in sel) / ts * 100:5.1f}%")
     for key, v in sorted(agg.items(), key=lambda kv: -kv[1]["samples"])[:top]:
         st = ", ".join(f"{h[6:]} {v[h]}" for h in sorted(stall_cols, key=lambda h: -v[h])[:2])
         act = v["thr"] / max(v["instr"], 1)
