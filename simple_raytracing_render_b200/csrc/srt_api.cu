@@ -984,7 +984,8 @@ int pick_wf_variant(const SrtScene* s) {
 // trace + shade passes until a shade pass leaves no slot alive.  Passes are enqueued kWfBatch at a
 // time; after each batch the live count of its last pass is copied to pinned memory, and the host
 // waits for the copy of the PREVIOUS batch only, so the stream never drains while work remains.
-int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, bool persistent) {
+int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, int mode) {
+    const bool persistent = mode >= 2;  // 2: k_wf_persist, 3: k_wf_sorted
     SrtContext* c = s->ctx;
     const size_t smem = (kWfMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
     WfLaunch L = {};
@@ -995,16 +996,22 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, 
     L.counters = c->d_counters;
     L.smem_bytes = smem;
     L.stream = c->stream;
+    // k_wf_sorted keeps its index queues behind the hot tables: Q_N x kSortCap 16-bit entries at most
+    const size_t smem_hot16 = (smem + 15) & ~(size_t)15;
+    const size_t smem_max = smem_hot16 + (size_t)srt::Q_N * srt::kSortCap * sizeof(unsigned short);
     if (c->wf_info[v].trace_blocks_per_sm == 0 || smem > c->wf_info_smem[v]) {
+        L.smem_bytes = smem_max;  // opt-in ceiling for every kernel of the variant
         cudaError_t e = kWfVariants[v](L, &c->wf_info[v]);
+        L.smem_bytes = smem;
         if (e != cudaSuccess) return fail(SRT_E_CUDA, "wavefront variant %d: %s", v, cudaGetErrorString(e));
         c->wf_info_smem[v] = smem;
     }
     const WfVariantInfo& info = c->wf_info[v];
-    const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 2048)) & ~31;
+    const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 4096)) & ~31;
     // persistent form: every CTA owns per_thread x threads slots
     const int p_blocks = std::max(1, info.persist_blocks_per_sm), p_threads = std::max(32, info.persist_threads);
-    const int per_thread = std::max(1, slots_per_sm / (p_blocks * p_threads));
+    int per_thread = std::max(1, slots_per_sm / (p_blocks * p_threads));
+    if (mode == 3) per_thread = std::max(1, std::min(per_thread, srt::kSortCap / p_threads));
     const int p_grid = c->sm_count * p_blocks;
     const int n_slots = persistent ? p_grid * per_thread * p_threads : c->sm_count * slots_per_sm;
     const size_t need = (size_t)n_slots * 144;
@@ -1037,8 +1044,9 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, 
     L.state = &st;
     L.live = c->d_live;
     if (persistent) {  // one launch: shade / trace phases alternate inside the kernel (k_wf_persist)
-        L.stage = 2;
+        L.stage = mode;
         L.per_thread = per_thread;
+        if (mode == 3) L.smem_bytes = smem_hot16 + (size_t)srt::Q_N * per_thread * p_threads * sizeof(unsigned short);
         L.grid = p_grid;
         c->launches++;
         cudaError_t pe = kWfVariants[v](L, nullptr);
@@ -1136,8 +1144,10 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
         s->variant_regs = info.registers;
         s->variant_smem = smem;
     }
-    const bool wf_persistent = wavefront && (wf_env == 2 || (wf_env < 0 && env_int("SRT_WF_PERSIST", 1)));
-    if (wavefront) s->variant = (wf_persistent ? 200 : 100) + wv;
+    // wavefront form: 1 two kernels per bounce, 2 persistent kernel, 3 persistent kernel with sorted queues
+    int wf_mode = !wavefront ? 0 : (wf_env >= 1 && wf_env <= 3 ? wf_env : env_int("SRT_WF_MODE", 3));
+    if (wf_mode == 3 && std::min(count, env_int("SRT_CHUNK", 1)) > 1) wf_mode = 2;  // the queues hold one path per item
+    if (wavefront) s->variant = 100 * wf_mode + wv;
     int blocks_per_sm = std::max(1, info.blocks_per_sm);
 
     // work decomposition (srt_kernels.cuh): an item is `chunk` consecutive Sobol indices of one pixel,
@@ -1194,7 +1204,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     // counters[7] is the work counter
     CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
     if (wavefront) {
-        int rc2 = run_wavefront(s, A, out, wv, wf_persistent);
+        int rc2 = run_wavefront(s, A, out, wv, wf_mode);
         if (rc2) return rc2;
         return finish();
     }

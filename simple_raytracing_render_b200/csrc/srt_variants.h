@@ -69,7 +69,7 @@ struct WfLaunch {
     unsigned long long* counters;
     int* live;    // live[pass] = slots left alive by shade pass `pass`
     int pass;
-    int stage;    // 0: trace, 1: shade, 2: the persistent kernel (both stages as phases)
+    int stage;    // 0: trace, 1: shade, 2: the persistent kernel (both stages as phases), 3: its sorted-queue form
     int per_thread;  // stage 2: slots per thread
     int grid;
     size_t smem_bytes;
@@ -81,6 +81,7 @@ struct WfVariantInfo {
     int trace_blocks_per_sm, shade_blocks_per_sm;
     int trace_registers, shade_registers;
     int persist_blocks_per_sm, persist_registers, persist_threads;
+    int sorted_blocks_per_sm, sorted_registers;
 };
 
 typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);

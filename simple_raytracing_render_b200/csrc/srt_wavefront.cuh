@@ -239,7 +239,7 @@ __global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
 // C2 frame.  CTAs take work items from the same global counter, so load balance is dynamic and a
 // CTA's tail is bounded by chunk x depth iterations over its own slots only.
 #ifndef SRT_WFP_THREADS
-#define SRT_WFP_THREADS 768
+#define SRT_WFP_THREADS 512
 #endif
 #ifndef SRT_WFP_LANE_SCHED
 #define SRT_WFP_LANE_SCHED 0  // 1: wf_shade_phase (rejection loop scheduled per lane); measured slower, see notes
@@ -440,6 +440,202 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
 #endif
         __syncthreads();
         if (threadIdx.x == 0) s_cursor[1] = 0;  // next read after the next barrier
+    }
+}
+
+
+// ---- SORTED persistent form: material-sorted shade queues, generation-sorted trace queues ------------
+// k_wf_persist walks its slots in storage order, so a warp shades whatever mix of materials its 32
+// slots happen to hold (capture E: the shading code ran at 6 of 32 lanes) and traces fresh camera
+// rays next to fifth-bounce rays.  Here the CTA keeps, in shared memory, index queues over its own
+// slots (16-bit indices, `kSortCap` per queue):
+//   * the TRACE phase appends every traced slot to the queue of what it hit — miss, light, diffuse,
+//     Beckmann, metal, glass — and the SHADE phase drains those queues one after the other, 32
+//     entries per warp: all lanes of a warp run the same material's code;
+//   * the SHADE phase appends every continuing path to the `cont` queue and every path it starts to
+//     the `new` queue (lanes that start paths together take consecutive work items: neighbouring
+//     samples of one pixel), and the TRACE phase drains `new` first: coherent camera rays stay together.
+// Appends are one ballot + one shared-memory atomic per warp.  A slot without a path is in no queue:
+// the tail of the frame shrinks with the live set.  Requires one path per work item (chunk == 1).
+constexpr int kSortCap = 8192;  // most slots a CTA may own (the queues live in dynamic shared memory)
+enum { SC_DEAD = 0, SC_MISS, SC_LIGHT, SC_DIFFUSE, SC_BECKMANN, SC_METAL, SC_GLASS, SC_N, TC_NEW = SC_N, TC_CONT, Q_N };
+
+struct SortQueues {
+    unsigned short* idx;  // [Q_N][cap], dynamic shared memory behind the hot tables
+    int cap;
+    int count[Q_N];
+    int cursor[Q_N];
+    int exhausted;
+};
+
+SRT_DEV void q_push(SortQueues& Q, int q, bool pred, int local_slot) {
+    const unsigned m = __ballot_sync(0xffffffffu, pred);
+    if (!m) return;
+    const int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == 0) base = atomicAdd(&Q.count[q], __popc(m));
+    base = __shfl_sync(0xffffffffu, base, 0);
+    if (pred) Q.idx[q * Q.cap + base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)local_slot;
+}
+
+// the next 32 entries of queue q for this warp: returns false when the queue is drained
+SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid) {
+    const int lane = threadIdx.x & 31;
+    int g = 0;
+    if (lane == 0) g = atomicAdd(&Q.cursor[q], 32);
+    g = __shfl_sync(0xffffffffu, g, 0);
+    const int n = Q.count[q];
+    if (g >= n) return false;
+    valid = g + lane < n;
+    local_slot = valid ? (int)Q.idx[q * Q.cap + g + lane] : 0;
+    return true;
+}
+
+template <uint32_t F>
+SRT_DEV int wf_hit_class(const View& W, const Hit& h) {
+    const DScene& S = W.S;
+    if (h.prim < 0) return SC_MISS;
+    int mat_index;
+    if ((F & F_MEDIA) && h.prim >= S.n_prims)
+        mat_index = S.media[h.prim - S.n_prims].phase_material;
+    else
+        mat_index = load_prim(W.dprims + h.prim).material;
+    if (mat_index < 0) return SC_MISS;
+    const int type = __float_as_int(__ldg(reinterpret_cast<const float*>(S.materials + mat_index)));
+    if (type == SRT_MAT_DIFFUSE_LIGHT) return SC_LIGHT;
+    if (type == SRT_MAT_BECKMANN) return SC_BECKMANN;
+    if (type == SRT_MAT_METAL) return SC_METAL;
+    if (type == SRT_MAT_DIELECTRIC || type == SRT_MAT_ISOTROPIC) return SC_GLASS;
+    return SC_DIFFUSE;
+}
+
+template <uint32_t F>
+__global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
+    k_wf_sorted(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
+                unsigned long long* __restrict__ counters, int per_thread) {
+    extern __shared__ float4 smem_hot[];
+    __shared__ SortQueues Q;
+    View W = wf_view<F>(S, smem_hot);
+    const unsigned FULL = 0xffffffffu;
+    const int lane = threadIdx.x & 31;
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const int cap = per_thread * blockDim.x;  // <= kSortCap (srt_api.cu)
+    const int cta_base = blockIdx.x * cap;
+    unsigned long long* work_counter = counters + 7;
+    Tally<false> tl{nullptr};
+    if (threadIdx.x < Q_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
+    if (threadIdx.x == 0) {
+        Q.exhausted = 0;
+        Q.cap = cap;
+        Q.idx = reinterpret_cast<unsigned short*>(smem_hot + ((F & F_SMEM_TABLES) ? ((S.hot_bytes + 15) >> 4) : 0));
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < cap; i += blockDim.x) Q.idx[SC_DEAD * cap + i] = (unsigned short)i;
+    __syncthreads();
+    if (threadIdx.x == 0) Q.count[SC_DEAD] = cap;  // every slot starts without a path
+    __syncthreads();
+    for (;;) {
+        // ---- SHADE: one level of color() per queued slot, class by class; then start new paths ----------
+        for (int c = 0; c < SC_N; c++) {
+            int ls;
+            bool valid;
+            while (q_take(Q, c, ls, valid)) {
+                const int slot = cta_base + ls;
+                bool alive = false;
+                int pixel = 0, s = 0;
+                Philox rng;
+                rng.have = 0;
+                Path P;
+                if (valid && c != SC_DEAD) {
+                    float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
+                    int4 it = st.item[slot];
+                    pixel = it.x;
+                    s = it.y;
+                    P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+                    P.thr = v3(tv.x, tv.y, tv.z);
+                    P.depth = __float_as_int(tv.w);
+                    P.L = v3(lv.x, lv.y, lv.z);
+                    Hit h;
+                    h.t = hv.x;
+                    h.prim = __float_as_int(hv.y);
+                    h.entry = __float_as_int(hv.z);
+                    wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)s, rng);
+                    alive = shade_bounce<F>(W, P, h, A.max_depth, rng, tl);
+                    if (!alive) item_commit(out, pixel, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
+                }
+                const bool cont = alive;
+                const bool need_item = valid && !alive;
+                const unsigned m = __ballot_sync(FULL, need_item);
+                if (m && !*(volatile int*)&Q.exhausted) {
+                    unsigned long long base = 0;
+                    if (lane == 0) {
+                        base = atomicAdd(work_counter, (unsigned long long)__popc(m));
+                        if (base + __popc(m) >= A.n_items) Q.exhausted = 1;
+                    }
+                    base = __shfl_sync(FULL, base, 0);
+                    const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
+                    if (need_item && item < A.n_items) {
+                        pixel = (int)(item / (unsigned)A.n_chunks);
+                        s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
+                        int i = pixel % (A.mod_ny ? A.ny : A.nx);
+                        int j = A.ny - 1 - (pixel / A.nx);
+                        double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
+                        double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
+                        float u = xdiv((float)(sx + (double)i), (float)A.nx);
+                        float v = xdiv((float)(sy + (double)j), (float)A.ny);
+                        philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
+                        P.r = camera_get_ray(S.camera, u, v, rng);
+                        P.thr = v3(1.f, 1.f, 1.f);
+                        P.L = v3(0.f, 0.f, 0.f);
+                        P.depth = 0;
+                        alive = true;
+                    }
+                }
+                if (alive) {
+                    st.item[slot] = make_int4(pixel, s, 0, 0);
+                    st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
+                    st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
+                    st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
+                    st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
+                    wf_store_rng(st, slot, rng);
+                }
+                q_push(Q, TC_CONT, cont, ls);
+                q_push(Q, TC_NEW, alive && !cont, ls);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x < SC_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
+        const int live = Q.count[TC_NEW] + Q.count[TC_CONT];
+        __syncthreads();
+        if (live == 0) break;
+        // ---- TRACE: world->hit for every live slot, camera rays first; queue by what was hit -------------
+        for (int c = TC_NEW; c <= TC_CONT; c++) {
+            int ls;
+            bool valid;
+            while (q_take(Q, c, ls, valid)) {
+                const int slot = cta_base + ls;
+                int cls = SC_MISS;
+                if (valid) {
+                    float4 o = st.ray_o[slot], d = st.ray_d[slot];
+                    Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+                    Philox rng;
+                    rng.have = 0;
+                    if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
+                        int4 it = st.item[slot];
+                        wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)it.y, rng);
+                    }
+                    Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
+                    st.hit[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f);
+                    if (F & F_MEDIA) wf_store_rng(st, slot, rng);
+                    cls = wf_hit_class<F>(W, h);
+                }
+#pragma unroll 1
+                for (int k = SC_MISS; k < SC_N; k++) q_push(Q, k, valid && cls == k, ls);
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x >= TC_NEW && threadIdx.x < Q_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
+        __syncthreads();
     }
 }
 

@@ -24,17 +24,16 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
     auto trace = srt::k_wf_trace<kMask>;
     auto shade = srt::k_wf_shade<kMask>;
     auto persist = srt::k_wf_persist<kMask>;
+    auto sorted = srt::k_wf_sorted<kMask>;
     cudaError_t e;
-    if (L.smem_bytes > 48 * 1024) {
-        e = cudaFuncSetAttribute(trace, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(shade, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
-        if (e != cudaSuccess) return e;
-        e = cudaFuncSetAttribute(persist, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
-        if (e != cudaSuccess) return e;
-    }
-    if (info) {
+    if (info) {  // runs before the first launch with a given shared-memory size (srt_api.cu: run_wavefront)
         info->features = kMask;
+        // static (k_wf_sorted's queues) + dynamic shared memory may exceed the 48 KB default
+        const void* fns[4] = {(const void*)trace, (const void*)shade, (const void*)persist, (const void*)sorted};
+        for (int i = 0; i < 4; i++) {
+            e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+            if (e != cudaSuccess) return e;
+        }
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->trace_blocks_per_sm, trace, srt::kWfThreads, L.smem_bytes);
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->shade_blocks_per_sm, shade, srt::kWfThreads, L.smem_bytes);
@@ -53,10 +52,18 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         if (e != cudaSuccess) return e;
         info->persist_registers = fa.numRegs;
         info->persist_threads = SRT_WFP_THREADS;
+        e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->sorted_blocks_per_sm, sorted, SRT_WFP_THREADS, L.smem_bytes);
+        if (e != cudaSuccess) return e;
+        e = cudaFuncGetAttributes(&fa, sorted);
+        if (e != cudaSuccess) return e;
+        info->sorted_registers = fa.numRegs;
         return cudaSuccess;
     }
     const srt::WfState& st = *static_cast<const srt::WfState*>(L.state);
-    if (L.stage == 2)
+    if (L.stage == 3)
+        sorted<<<L.grid, SRT_WFP_THREADS, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters,
+                                                                    L.per_thread);
+    else if (L.stage == 2)
         persist<<<L.grid, SRT_WFP_THREADS, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters,
                                                                      L.per_thread);
     else if (L.stage == 0)
