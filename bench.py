@@ -119,9 +119,27 @@ class ClockSampler:
 def algorithmic_work(counters, n_pixels, prim_bytes):
     """bytes and flops of one launch from the kernel's own counters."""
     rays, nodes, prims = counters["rays"], counters["node_visits"], counters["prim_tests"]
-    by = 144 * rays + 128 * nodes + prim_bytes * prims + 24 * n_pixels
+    state = 144 * rays + 24 * n_pixels            # ray + hit + path state, accumulation: moves through L2 / HBM
+    geometry = 128 * nodes + prim_bytes * prims   # node and primitive fetches: L1 / shared-memory hits for C1-C4
     fl = 12 * rays + 18 * 4 * nodes + 27 * prims + 130 * max(rays - counters["paths"], 0)
-    return by, fl
+    return state + geometry, fl, state
+
+
+KERNEL_OF_MODE = {0: "k_render", 1: "k_wf_trace + k_wf_shade", 2: "k_wf_persist", 3: "k_wf_sorted"}
+
+
+def measured_traffic(config, kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel, from the committed
+    ncu --set full capture of this configuration (profiles/traffic.json, written by tools/ncu_traffic.py)."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(path) as f:
+            rec = json.load(f).get(config)
+    except (OSError, ValueError):
+        return None
+    if not rec or rec.get("kernel") != kernel:
+        return None
+    return rec.get("dram_bytes_per_launch")
 
 
 def run_reference(args):
@@ -256,7 +274,8 @@ def main():
         cnt = sc.render_counted(params, scratch)
     rpp = cnt["rays"] / max(cnt["paths"], 1)
     prim_bytes = {"spheres": 16, "cornell": 20, "teapot": 48, "soldier": 48, "tessellated": 48}[args.config]
-    abytes, aflops = algorithmic_work(cnt, n_pixels, prim_bytes)
+    abytes, aflops, state_bytes = algorithmic_work(cnt, n_pixels, prim_bytes)
+    kernel_name = KERNEL_OF_MODE.get(int(sc.info()["render_variant"]) // 100, "k_render")
 
     # ---- e2e: HOST buffers through the C ABI, copies inside the timed region ----------------------
     full = render.render_params(nx, ny, ns, s0, s1, seed=SEED)
@@ -312,10 +331,13 @@ def main():
             "mrays_per_s": value * rpp / 1e6, "rays_per_path": rpp,
             "kernel_ms": kernel_ms, "kernel_share_of_step": kernel_ms / ms_per_step,
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
-                         "frac": achieved / hbm_peak, "traffic": None, "peak_source": which,
-                         "kernel": "k_render", "algorithmic_bytes_per_launch": int(abytes),
-                         "note": "working set is L2-resident: the binding limits are FP32 issue and latency, "
-                                 "see fp32 below and DESIGN.md §8"},
+                         "frac": achieved / hbm_peak, "traffic": measured_traffic(args.config, kernel_name),
+                         "peak_source": which, "kernel": kernel_name, "algorithmic_bytes_per_launch": int(abytes),
+                         "state_bytes_per_launch": int(state_bytes), "state_gbps": state_bytes / k_s / 1e9,
+                         "note": "algorithmic bytes (SURVEY 8d) = path state + node / primitive fetches; the "
+                                 "fetches hit L1 / shared memory (scene far below L2), so `achieved` is not DRAM "
+                                 "traffic and may exceed `peak`; `traffic` is the measured DRAM bytes. The binding "
+                                 "limits are instruction issue and latency: see fp32 and DESIGN.md §8"},
             "fp32": {"achieved_tflops": aflops / k_s / 1e12,
                      "nominal_peak_tflops": FP32_LANES * sm_max * 1e6 / 1e12,
                      "measured_peak_tflops": fp32_meas,
