@@ -361,7 +361,7 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
     int ex_rank = 0x7fffffff;
     for (;;) {  // passes (see above)
         float best_t = CUDART_INF_F;
-        int best_rank = -1;
+        int best_rank = -1, best_slot = -1;
         int32_t best_prim = -1;
         uint2 stack[kStackSize];  // (key, ref)
         int sp = 0;
@@ -449,6 +449,7 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
                         best_t = tt;
                         best_rank = rank;
                         best_prim = pp;
+                        best_slot = s;
                     }
                 }
             }
@@ -465,7 +466,27 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
         }
         if (best_rank < 0) return false;
         RayInv inv{xdiv(1.0f, q.kx), xdiv(1.0f, q.ky), xdiv(1.0f, q.kz)};
-        if (ref_reachable(S.ref_nodes + B.ref_base, best_rank, r, inv, t_min, t_max, tl)) {
+        // Reachability shortcut.  Every ancestor box of the reference tree is a union that contains the
+        // winner's own bounding_box() (sphere.h:31-34, triangle.h:53-68; surrounding_box is exact min / max),
+        // and aabb::hit is monotone in the box: float subtraction and the multiplication by the same
+        // 1/d keep the order of the slab planes (the swap for 1/d < 0 keeps it too, a NaN product leaves
+        // tmin / tmax untouched, i.e. only loosens the bigger box), so per axis tmin' <= tmin and
+        // tmax' >= tmax.  A ray that passes aabb::hit on the winner's own box passes it on every
+        // ancestor: no walk down the reference tree (a chain of dependent loads, ~log2 n deep).
+        bool reachable = false;
+        if (kind == BVH_KIND_SPHERE) {
+            float4 g = __ldg(&S.leaf_geom[B.geom_base + best_slot]);
+            reachable = ref_aabb_hit(make_float4(xsub(g.x, g.w), xsub(g.y, g.w), xsub(g.z, g.w), 0.f),
+                                     make_float4(xadd(g.x, g.w), xadd(g.y, g.w), xadd(g.z, g.w), 0.f), r, inv, t_min, t_max);
+        } else if (kind == BVH_KIND_TRIANGLE) {
+            const float4* g = S.leaf_geom + B.geom_base + 3 * (size_t)best_slot;
+            float4 a = __ldg(g), b = __ldg(g + 1), c = __ldg(g + 2);
+            reachable = ref_aabb_hit(
+                make_float4(fminf(fminf(a.x, b.x), c.x), fminf(fminf(a.y, b.y), c.y), fminf(fminf(a.z, b.z), c.z), 0.f),
+                make_float4(fmaxf(fmaxf(a.x, b.x), c.x), fmaxf(fmaxf(a.y, b.y), c.y), fmaxf(fmaxf(a.z, b.z), c.z), 0.f), r,
+                inv, t_min, t_max);
+        }
+        if (reachable || ref_reachable(S.ref_nodes + B.ref_base, best_rank, r, inv, t_min, t_max, tl)) {
             if (best_prim == -2) best_prim = S.groups[S.bvh_items[B.first_item + best_rank]].first_prim;
             t_out = best_t;
             prim_out = best_prim;

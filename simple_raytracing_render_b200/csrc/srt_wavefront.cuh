@@ -478,6 +478,18 @@ SRT_DEV void q_push(SortQueues& Q, int q, bool pred, int local_slot) {
     if (pred) Q.idx[q * Q.cap + base + __popc(m & ((1u << lane) - 1u))] = (unsigned short)local_slot;
 }
 
+// append each valid lane to the queue `q` of its own: lanes with the same q find each other with one
+// match, their lowest lane reserves the range with one shared-memory atomic
+SRT_DEV void q_push_class(SortQueues& Q, bool valid, int q, int local_slot) {
+    const int lane = threadIdx.x & 31;
+    const unsigned peers = __match_any_sync(0xffffffffu, valid ? q : -1);
+    const int leader = __ffs(peers) - 1;
+    int base = 0;
+    if (valid && lane == leader) base = atomicAdd(&Q.count[q], __popc(peers));
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (valid) Q.idx[q * Q.cap + base + __popc(peers & ((1u << lane) - 1u))] = (unsigned short)local_slot;
+}
+
 // the next 32 entries of queue q for this warp: returns false when the queue is drained
 SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid) {
     const int lane = threadIdx.x & 31;
@@ -629,8 +641,7 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                     if (F & F_MEDIA) wf_store_rng(st, slot, rng);
                     cls = wf_hit_class<F>(W, h);
                 }
-#pragma unroll 1
-                for (int k = SC_MISS; k < SC_N; k++) q_push(Q, k, valid && cls == k, ls);
+                q_push_class(Q, valid, cls, ls);
             }
         }
         __syncthreads();
