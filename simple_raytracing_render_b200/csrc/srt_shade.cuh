@@ -444,6 +444,7 @@ SRT_DEV bool shade_sample_iter(const View& W, SampleCtx& C, Philox& rng, Tally<C
     if (W.S.n_lights > 0) {
         if (++C.iters > kMaxRejectIters) return true;
         if (COUNT) tl.c->reject_iters++;
+        philox_fresh(rng);  // one iteration draws at most four numbers (choice, light pick, two coordinates)
         if (rand_f(rng) < 0.5f)  // pdf.h:183-189
             C.sdir = light_random<F>(W, C.p, rng);
         else

@@ -247,6 +247,9 @@ __global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
 #ifndef SRT_WFP_DYNAMIC
 #define SRT_WFP_DYNAMIC 1  // warps take 32-slot groups from a shared-memory cursor instead of a fixed mapping
 #endif
+#ifndef SRT_WFS_TRACE_NEW_FIRST
+#define SRT_WFS_TRACE_NEW_FIRST 0  // 0: continuing (incoherent, slow) rays first, so the phase ends on short groups
+#endif
 #ifndef SRT_WFP_MINBLOCKS
 #define SRT_WFP_MINBLOCKS 1
 #endif
@@ -621,7 +624,8 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         __syncthreads();
         if (live == 0) break;
         // ---- TRACE: world->hit for every live slot, camera rays first; queue by what was hit -------------
-        for (int c = TC_NEW; c <= TC_CONT; c++) {
+        for (int ci = 0; ci < 2; ci++) {
+            const int c = (SRT_WFS_TRACE_NEW_FIRST ? ci == 0 : ci == 1) ? TC_NEW : TC_CONT;
             int ls;
             bool valid;
             while (q_take(Q, c, ls, valid)) {
