@@ -116,6 +116,27 @@ class ClockSampler:
                 "samples": len(sm)}
 
 
+class stdout_to_stderr:
+    """The reference's own code prints to the C stdout (brdf.h:162); the bench line must be the only thing
+    on stdout, so file descriptor 1 points at stderr while the reference runs."""
+
+    def __enter__(self):
+        sys.stdout.flush()
+        self.saved = os.dup(1)
+        os.dup2(2, 1)
+        return self
+
+    def __exit__(self, *exc):
+        try:
+            import ctypes
+            ctypes.CDLL(None).fflush(None)
+        except OSError:
+            pass
+        os.dup2(self.saved, 1)
+        os.close(self.saved)
+        return False
+
+
 def algorithmic_work(counters, n_pixels, prim_bytes):
     """bytes and flops of one launch from the kernel's own counters."""
     rays, nodes, prims = counters["rays"], counters["node_visits"], counters["prim_tests"]
@@ -155,12 +176,13 @@ def run_reference(args):
         return 0
     cores = os.cpu_count() or 1
     sx, sy, ss = cpu_sample(nx, ny, ns)
-    rs = ref.RefBuilder().realize(*scenes.by_name(args.config))
     paths = sx * sy * ss
-    for _ in range(max(args.warmup, 1)):
-        rs.render_timed(sx, sy, ss, cores)
-    times = [rs.render_timed(sx, sy, ss, cores) for _ in range(args.steps)]
-    _, nrays = rs.render_float(max(sx // 4, 8), max(sy // 4, 8), ss, mod_ny=sx == sy)
+    with stdout_to_stderr():
+        rs = ref.RefBuilder().realize(*scenes.by_name(args.config))
+        for _ in range(max(args.warmup, 1)):
+            rs.render_timed(sx, sy, ss, cores)
+        times = [rs.render_timed(sx, sy, ss, cores) for _ in range(args.steps)]
+        _, nrays = rs.render_float(max(sx // 4, 8), max(sy // 4, 8), ss, mod_ny=sx == sy)
     rpp = nrays / float(max(sx // 4, 8) * max(sy // 4, 8) * ss)
     sec = float(np.mean(times))
     v = paths / sec
@@ -372,10 +394,11 @@ def cpu_baseline(config):
     nx, ny, ns, _ = config_of(config)
     sx, sy, ss = cpu_sample(nx, ny, ns)
     cores = os.cpu_count() or 1
-    rs = ref.RefBuilder().realize(*scenes.by_name(config))
-    rs.render_timed(sx, sy, ss, cores)
-    secs = [rs.render_timed(sx, sy, ss, cores) for _ in range(3)]
-    one = rs.render_timed(sx, sy, ss, 1)
+    with stdout_to_stderr():
+        rs = ref.RefBuilder().realize(*scenes.by_name(config))
+        rs.render_timed(sx, sy, ss, cores)
+        secs = [rs.render_timed(sx, sy, ss, cores) for _ in range(3)]
+        one = rs.render_timed(sx, sy, ss, 1)
     paths = sx * sy * ss
     return {"value": paths / float(np.mean(secs)), "unit": "paths/s", "cores": cores, "kind": "reference",
             "sample": f"{sx}x{sy} @ {ss} spp of the same scene/camera ({paths} paths), reference renderthread pool",
