@@ -247,6 +247,9 @@ __global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
 #ifndef SRT_WFP_DYNAMIC
 #define SRT_WFP_DYNAMIC 1  // warps take 32-slot groups from a shared-memory cursor instead of a fixed mapping
 #endif
+#ifndef SRT_WFS_TAIL_GRAIN
+#define SRT_WFS_TAIL_GRAIN 32  // 8 and 16 measured slower (most queues are short, they never leave the tail regime)
+#endif
 #ifndef SRT_WFS_TRACE_NEW_FIRST
 #define SRT_WFS_TRACE_NEW_FIRST 0  // 0: continuing (incoherent, slow) rays first, so the phase ends on short groups
 #endif
@@ -493,15 +496,23 @@ SRT_DEV void q_push_class(SortQueues& Q, bool valid, int q, int local_slot) {
     if (valid) Q.idx[q * Q.cap + base + __popc(peers & ((1u << lane) - 1u))] = (unsigned short)local_slot;
 }
 
-// the next 32 entries of queue q for this warp: returns false when the queue is drained
+// The next entries of queue q for this warp: 32 at a time, and SRT_WFS_TAIL_GRAIN at a time once fewer than
+// one full round of the CTA's warps is left — a group lasts as long as its slowest lane, and the warps
+// that are through wait at the phase barrier for the last group (capture H: 12.7 % of C3's stall samples),
+// so the last entries are spread over all warps in short groups.  Returns false when the queue is drained.
 SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid) {
     const int lane = threadIdx.x & 31;
-    int g = 0;
-    if (lane == 0) g = atomicAdd(&Q.cursor[q], 32);
-    g = __shfl_sync(0xffffffffu, g, 0);
     const int n = Q.count[q];
+    int g = 0, step = 32;
+    if (lane == 0) {
+        const int left = n - *(volatile int*)&Q.cursor[q];
+        step = left > (int)blockDim.x ? 32 : SRT_WFS_TAIL_GRAIN;
+        g = atomicAdd(&Q.cursor[q], step);
+    }
+    g = __shfl_sync(0xffffffffu, g, 0);
+    step = __shfl_sync(0xffffffffu, step, 0);
     if (g >= n) return false;
-    valid = g + lane < n;
+    valid = lane < step && g + lane < n;
     local_slot = valid ? (int)Q.idx[q * Q.cap + g + lane] : 0;
     return true;
 }

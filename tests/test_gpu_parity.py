@@ -101,12 +101,19 @@ def test_device_pointers_are_accepted(trace_scene):
 TRIM = {"teapot": 0.002, "soldier": 0.002}
 
 
-def test_converged_image_relmse_vs_golden(golden_scene):
-    """GPU image at 4x the golden's spp against the reference's single-thread float render."""
+@pytest.mark.parametrize("scheduler", ["auto", "sorted"])
+def test_converged_image_relmse_vs_golden(golden_scene, scheduler, monkeypatch):
+    """GPU image at 4x the golden's spp against the reference's single-thread float render; once with the
+    scheduler the backend picks for this frame size (the fused kernel) and once through the sorted
+    persistent wavefront (k_wf_sorted), which is what full-size frames of BVH scenes run on."""
     name, g, sc = golden_scene
     nx, ny, ns_ref = int(g["img_nx"]), int(g["img_ny"]), int(g["img_ns"])
     ns = 4 * ns_ref
+    if scheduler == "sorted":
+        monkeypatch.setenv("SRT_WAVEFRONT", "3")
     _, accum = sc.render_image(render.render_params(nx, ny, ns), want_accum=True)
+    if scheduler == "sorted":
+        assert sc.info()["render_variant"] // 100 == 3
     x = (accum / float(ns)).astype(np.float64)
     r = g["img"].astype(np.float64)
     terms = ((x - r) ** 2 / (r ** 2 + 1e-2)).reshape(-1)
@@ -120,11 +127,15 @@ def test_converged_image_relmse_vs_golden(golden_scene):
     assert err <= RELMSE_TOL
 
 
-def test_render_is_deterministic_and_shards_add_up(golden_scene):
+@pytest.mark.parametrize("scheduler", ["auto", "sorted"])
+def test_render_is_deterministic_and_shards_add_up(golden_scene, scheduler, monkeypatch):
     """Sample-range shards: [0, ns) == sum of disjoint ranges up to float summation
-    order; the same range twice is bit-identical."""
+    order; the same range twice is bit-identical (fixed-point accumulation: for any schedule, including
+    the wavefront's nondeterministic queue order)."""
     import torch
     name, g, sc = golden_scene
+    if scheduler == "sorted":
+        monkeypatch.setenv("SRT_WAVEFRONT", "3")
     nx, ny, ns = 96, 64, 32
     flags = 0
 
