@@ -1090,11 +1090,14 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, 
     return 0;
 }
 
-// Wavefront by default when the scene has an acceleration structure (hundreds of primitives or more)
-// and the frame is long enough to amortise the passes' launches.
+// Wavefront by default when the scene has an acceleration structure and the frame is a few paths per
+// slot of the pool: measured on B200 (tools/chunk_check.py) the sorted wavefront wins from 1.9 M paths
+// up on C2 / C3 (1.44 vs 1.96 ms at 1200x800 @ 2), which is also what a rank of an 8-GPU C2 frame renders;
+// scenes that are a plain list of primitives (C1) stay on the fused kernel at every size (47 vs 72 ms
+// at 2048x2048 @ 64).
 bool auto_wavefront(const SrtScene* s, const SrtRenderParams* p) {
     long long paths = (long long)p->nx * p->ny * (p->s_end - p->s_begin);
-    return s->dev.n_bvhs > 0 && paths >= (1LL << 24);
+    return s->dev.n_bvhs > 0 && paths >= (1LL << 20);
 }
 
 int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool counting) {
