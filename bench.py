@@ -172,7 +172,7 @@ def run_reference(args):
     from simple_raytracing_render_b200 import scenes
     nx, ny, ns, label = config_of(args.config)
     if not ref.available():
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/libsrt_ref.so was not built"}))
+        emit({"impl": "reference", "unavailable": "oracle/_ref/libsrt_ref.so was not built"})
         return 0
     cores = os.cpu_count() or 1
     sx, sy, ss = cpu_sample(nx, ny, ns)
@@ -187,7 +187,7 @@ def run_reference(args):
     sec = float(np.mean(times))
     v = paths / sec
     sample = f"{sx}x{sy} @ {ss} spp of the same scene/camera ({paths} paths per step), {cores} std::threads"
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "paths/s", "value": v, "unit": "paths/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
@@ -195,11 +195,31 @@ def run_reference(args):
         "mrays_per_s": v * rpp / 1e6, "rays_per_path": rpp,
         "cpu_baseline": {"value": v, "unit": "paths/s", "cores": cores, "kind": "reference", "sample": sample},
         "e2e": {"value": v, "unit": "paths/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
     return 0
 
 
+REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line, on the process's original stdout (see main)."""
+    data = (json.dumps(line) + "\n").encode()
+    if REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(REAL_STDOUT, data)
+
+
 def main():
+    # Libraries print to the C stdout behind Python's back (NCCL its version banner at communicator
+    # creation, the reference's brdf.h a progress line): file descriptor 1 points at stderr for the whole run
+    # and the JSON line goes to a private copy of the original stdout.
+    global REAL_STDOUT
+    sys.stdout.flush()
+    REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -377,7 +397,7 @@ def main():
         }
         if world_size == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline(args.config)
-        print(json.dumps(line))
+        emit(line)
     sc.close()
     ctx.close()
     if world_size > 1:
