@@ -14,6 +14,8 @@ from __future__ import annotations
 
 import math
 
+import os
+
 import numpy as np
 
 from . import scene as S
@@ -264,4 +266,6 @@ def by_name(name: str, **kw):
     if fn is None:
         raise KeyError(name)
     nx, ny, _ = CONFIG_SIZES[name]
+    if name == "tessellated" and "n_side" not in kw and os.environ.get("SRT_TESS_NSIDE"):
+        kw["n_side"] = int(os.environ["SRT_TESS_NSIDE"])  # 2237: the 10 M triangles of BASELINE.json:configs[4]
     return fn(aspect=float(np.float32(nx) / np.float32(ny)), **kw)
