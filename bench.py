@@ -45,7 +45,8 @@ def config_of(name):
              "spheres": "C2 random spheres (bvh_node) 1200x800 @ 64 spp",
              "teapot": "C3 Utah teapot 640k triangles (bvh_node), Beckmann, sky sphere 1024x1024 @ 256 spp",
              "soldier": "C4-like textured Beckmann mesh + env map + MERL-material floor + glass 1920x1080 @ 1024 spp",
-             "tessellated": "C5-like tessellated terrain (2 x 512^2 triangles) + constant_medium 3840x2160 @ 256 spp"}[name]
+             "tessellated": f"C5 tessellated terrain (2 x {int(os.environ.get('SRT_TESS_NSIDE', '512'))}^2 triangles) "
+                            "+ constant_medium 3840x2160 @ 256 spp"}[name]
     return nx, ny, ns, label
 
 

@@ -500,7 +500,7 @@ SRT_DEV void q_push_class(SortQueues& Q, bool valid, int q, int local_slot) {
 // one full round of the CTA's warps is left — a group lasts as long as its slowest lane, and the warps
 // that are through wait at the phase barrier for the last group (capture H: 12.7 % of C3's stall samples),
 // so the last entries are spread over all warps in short groups.  Returns false when the queue is drained.
-SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid) {
+SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid, int& pos) {
     const int lane = threadIdx.x & 31;
     const int n = Q.count[q];
     int g = 0, step = 32;
@@ -512,8 +512,9 @@ SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid) {
     g = __shfl_sync(0xffffffffu, g, 0);
     step = __shfl_sync(0xffffffffu, step, 0);
     if (g >= n) return false;
-    valid = lane < step && g + lane < n;
-    local_slot = valid ? (int)Q.idx[q * Q.cap + g + lane] : 0;
+    pos = g + lane;
+    valid = lane < step && pos < n;
+    local_slot = valid ? (int)Q.idx[q * Q.cap + pos] : 0;
     return true;
 }
 
@@ -541,10 +542,10 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                 unsigned long long* __restrict__ counters, int per_thread) {
     extern __shared__ float4 smem_hot[];
     __shared__ SortQueues Q;
+    __shared__ unsigned long long s_item_base;  // first work item of this pass's regeneration
+    __shared__ int s_item_avail;                // how many of the queued slots get one
     View W = wf_view<F>(S, smem_hot);
-    const unsigned FULL = 0xffffffffu;
     const int lane = threadIdx.x & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
     const int cap = per_thread * blockDim.x;  // <= kSortCap (srt_api.cu)
     const int cta_base = blockIdx.x * cap;
     unsigned long long* work_counter = counters + 7;
@@ -559,87 +560,68 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     for (int i = threadIdx.x; i < cap; i += blockDim.x) Q.idx[SC_DEAD * cap + i] = (unsigned short)i;
     __syncthreads();
     if (threadIdx.x == 0) Q.count[SC_DEAD] = cap;  // every slot starts without a path
-    __syncthreads();
     for (;;) {
-        // ---- SHADE: one level of color() per queued slot, class by class; then start new paths ----------
-        for (int c = 0; c < SC_N; c++) {
-            int ls;
+        // ---- REGENERATE: every slot whose path ended in the last shade phase (queue SC_DEAD) starts the
+        // next path, Raytracing_n.cpp:827-836.  The CTA takes ALL the work items it needs with one atomic
+        // on the global counter; queue position i gets item base + i, so the new camera rays of the CTA
+        // are consecutive samples of one or two pixels, generated by full warps in converged code. --------
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            const int n = Q.count[SC_DEAD];
+            unsigned long long base = 0;
+            int avail = 0;
+            if (n > 0 && !Q.exhausted) {
+                base = atomicAdd(work_counter, (unsigned long long)n);
+                if (base < A.n_items) avail = (int)min((unsigned long long)n, A.n_items - base);
+                if (base + (unsigned long long)n >= A.n_items) Q.exhausted = 1;
+            }
+            s_item_base = base;
+            s_item_avail = avail;
+        }
+        __syncthreads();
+        {
+            const unsigned long long base = s_item_base;
+            const int avail = s_item_avail;
+            int ls, pos;
             bool valid;
-            while (q_take(Q, c, ls, valid)) {
-                const int slot = cta_base + ls;
-                bool alive = false;
-                int pixel = 0, s = 0;
-                Philox rng;
-                rng.have = 0;
-                Path P;
-                if (valid && c != SC_DEAD) {
-                    float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
-                    int4 it = st.item[slot];
-                    pixel = it.x;
-                    s = it.y;
-                    P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-                    P.thr = v3(tv.x, tv.y, tv.z);
-                    P.depth = __float_as_int(tv.w);
-                    P.L = v3(lv.x, lv.y, lv.z);
-                    Hit h;
-                    h.t = hv.x;
-                    h.prim = __float_as_int(hv.y);
-                    h.entry = __float_as_int(hv.z);
-                    wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)s, rng);
-                    alive = shade_bounce<F>(W, P, h, A.max_depth, rng, tl);
-                    if (!alive) item_commit(out, pixel, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
-                }
-                const bool cont = alive;
-                const bool need_item = valid && !alive;
-                const unsigned m = __ballot_sync(FULL, need_item);
-                if (m && !*(volatile int*)&Q.exhausted) {
-                    unsigned long long base = 0;
-                    if (lane == 0) {
-                        base = atomicAdd(work_counter, (unsigned long long)__popc(m));
-                        if (base + __popc(m) >= A.n_items) Q.exhausted = 1;
-                    }
-                    base = __shfl_sync(FULL, base, 0);
-                    const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
-                    if (need_item && item < A.n_items) {
-                        pixel = (int)(item / (unsigned)A.n_chunks);
-                        s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
-                        int i = pixel % (A.mod_ny ? A.ny : A.nx);
-                        int j = A.ny - 1 - (pixel / A.nx);
-                        double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
-                        double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
-                        float u = xdiv((float)(sx + (double)i), (float)A.nx);
-                        float v = xdiv((float)(sy + (double)j), (float)A.ny);
-                        philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-                        P.r = camera_get_ray(S.camera, u, v, rng);
-                        P.thr = v3(1.f, 1.f, 1.f);
-                        P.L = v3(0.f, 0.f, 0.f);
-                        P.depth = 0;
-                        alive = true;
-                    }
-                }
-                if (alive) {
+            while (q_take(Q, SC_DEAD, ls, valid, pos)) {
+                if (pos - lane >= avail) break;  // the rest of the queue gets no item: those slots stay empty
+                const bool start = valid && pos < avail;
+                if (start) {
+                    const int slot = cta_base + ls;
+                    const unsigned long long item = base + (unsigned)pos;
+                    const int pixel = (int)(item / (unsigned)A.n_chunks);
+                    const int s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
+                    const int i = pixel % (A.mod_ny ? A.ny : A.nx);
+                    const int j = A.ny - 1 - (pixel / A.nx);
+                    const double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
+                    const double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
+                    const float u = xdiv((float)(sx + (double)i), (float)A.nx);
+                    const float v = xdiv((float)(sy + (double)j), (float)A.ny);
+                    Philox rng;
+                    philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
+                    const Ray r = camera_get_ray(S.camera, u, v, rng);
                     st.item[slot] = make_int4(pixel, s, 0, 0);
-                    st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
-                    st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
-                    st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
-                    st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
+                    st.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+                    st.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
+                    st.thr[slot] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+                    st.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
                     wf_store_rng(st, slot, rng);
                 }
-                q_push(Q, TC_CONT, cont, ls);
-                q_push(Q, TC_NEW, alive && !cont, ls);
+                q_push(Q, TC_NEW, start, ls);
             }
         }
         __syncthreads();
-        if (threadIdx.x < SC_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
+        if (threadIdx.x < SC_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;  // all shade queues are consumed
         const int live = Q.count[TC_NEW] + Q.count[TC_CONT];
         __syncthreads();
         if (live == 0) break;
-        // ---- TRACE: world->hit for every live slot, camera rays first; queue by what was hit -------------
+        // ---- TRACE: world->hit for every live slot; queue by what was hit ------------------------------
         for (int ci = 0; ci < 2; ci++) {
             const int c = (SRT_WFS_TRACE_NEW_FIRST ? ci == 0 : ci == 1) ? TC_NEW : TC_CONT;
-            int ls;
+            int ls, pos;
             bool valid;
-            while (q_take(Q, c, ls, valid)) {
+            while (q_take(Q, c, ls, valid, pos)) {
                 const int slot = cta_base + ls;
                 int cls = SC_MISS;
                 if (valid) {
@@ -662,6 +644,42 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         __syncthreads();
         if (threadIdx.x >= TC_NEW && threadIdx.x < Q_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
         __syncthreads();
+        // ---- SHADE: one level of color() per queued slot, material by material -------------------------
+        for (int c = SC_MISS; c < SC_N; c++) {
+            int ls, pos;
+            bool valid;
+            while (q_take(Q, c, ls, valid, pos)) {
+                const int slot = cta_base + ls;
+                bool alive = false;
+                if (valid) {
+                    float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
+                    int4 it = st.item[slot];
+                    Path P;
+                    P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+                    P.thr = v3(tv.x, tv.y, tv.z);
+                    P.depth = __float_as_int(tv.w);
+                    P.L = v3(lv.x, lv.y, lv.z);
+                    Hit h;
+                    h.t = hv.x;
+                    h.prim = __float_as_int(hv.y);
+                    h.entry = __float_as_int(hv.z);
+                    Philox rng;
+                    wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)it.y, rng);
+                    alive = shade_bounce<F>(W, P, h, A.max_depth, rng, tl);
+                    if (alive) {
+                        st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
+                        st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
+                        st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
+                        st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
+                        wf_store_rng(st, slot, rng);
+                    } else {
+                        item_commit(out, it.x, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
+                    }
+                }
+                q_push(Q, TC_CONT, alive, ls);
+                q_push(Q, SC_DEAD, valid && !alive, ls);
+            }
+        }
     }
 }
 
