@@ -92,6 +92,10 @@ typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
      : (n) == 1 ? (SRT_VM_SPHERES | F_SMEM_TABLES)             \
      : (n) == 2 ? (SRT_VM_MESH)                                \
                 : (SRT_VM_FULL))
+// threads of the one persistent CTA per SM (k_wf_persist / k_wf_sorted).  Measured (profiles/r01_notes.md,
+// capture K): the sphere-BVH variant needs 107 registers and is best at 640 threads (96 registers, 20
+// warps); the mesh and full variants spill there and are best at 512 (128 registers).
+#define SRT_WF_VARIANT_PERSIST_THREADS(n) ((n) <= 1 ? 640 : 512)
 #define SRT_WF_VARIANT_TRACE_MINBLOCKS(n) 3
 #define SRT_WF_VARIANT_SHADE_MINBLOCKS(n) 3
 

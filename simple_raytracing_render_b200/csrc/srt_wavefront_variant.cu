@@ -11,6 +11,9 @@
 #ifndef SRT_WF_SHADE_MINBLOCKS
 #define SRT_WF_SHADE_MINBLOCKS SRT_WF_VARIANT_SHADE_MINBLOCKS(SRT_WF_VARIANT)
 #endif
+#ifndef SRT_WFP_THREADS
+#define SRT_WFP_THREADS SRT_WF_VARIANT_PERSIST_THREADS(SRT_WF_VARIANT)
+#endif
 #include "srt_wavefront.cuh"
 
 #define SRT_CAT2(a, b) a##b
