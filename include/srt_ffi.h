@@ -233,7 +233,9 @@ typedef struct SrtSceneDesc {
 /* ---- render parameters: CRender(maxDepth,width,height,num_ray,thread_count,filePath)
  *      (Render.h:20) and the globals at Raytracing_n.cpp:33-43 --------------------------------- */
 #define SRT_COMPAT_PIXEL_MOD_NY 1u /* i = curpixel % ny as at Raytracing_n.cpp:827 (square images only) */
-#define SRT_RENDER_WAVEFRONT 2u    /* block-local wavefront scheduler instead of the per-thread path loop */
+#define SRT_RENDER_WAVEFRONT 2u    /* ask for the persistent sorted wavefront instead of the per-thread
+                                      path loop; without the flag the backend picks it for scenes with an
+                                      acceleration structure from 2^20 paths per call up.  Same image either way. */
 
 typedef struct SrtRenderParams {
     int32_t nx, ny;      /* Raytracing_n.cpp:39-40 */
