@@ -364,7 +364,25 @@ int srt_scene_destroy(SrtScene* s) {
     return 0;
 }
 
+// SRT_SCENE_TIMING=1: per-stage host times of srt_scene_create on stderr
+struct StageTimer {
+    bool on;
+    std::chrono::steady_clock::time_point t0;
+    StageTimer() : on(env_int_early("SRT_SCENE_TIMING")), t0(std::chrono::steady_clock::now()) {}
+    static bool env_int_early(const char* n) {
+        const char* v = getenv(n);
+        return v && *v && atoi(v) != 0;
+    }
+    void tick(const char* what) {
+        if (!on) return;
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[srt_scene_create] %-28s %8.2f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) {
+    StageTimer stage;
     if (!ctx || !desc || !out) return fail(SRT_E_INVALID, "null argument");
     *out = nullptr;
     const SrtSceneDesc& d = *desc;
@@ -412,9 +430,12 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
             all_tri = all_tri && single && d.prims[g.first_prim].type == SRT_PRIM_TRIANGLE;
         }
         WideBvh wb;
+        stage.tick("item boxes");
         build_wide_bvh(boxes.data(), n, wb);
+        stage.tick("build_wide_bvh");
         std::vector<RefNode> rt;
         build_ref_tree(d.bvh_item_boxes + 6 * (size_t)sb.first_item, n, rt);
+        stage.tick("build_ref_tree");
         DBvh& B = bvhs[bi];
         B.kind = all_sphere ? BVH_KIND_SPHERE : (all_tri ? BVH_KIND_TRIANGLE : BVH_KIND_GENERIC);
         B.first_item = sb.first_item;
@@ -449,6 +470,7 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
         }
     }
 
+    stage.tick("leaf arrays");
     // ---- flat primitive records (index == primitive id) ------------------------------------------
     uint32_t feat = 0;
     auto make_dprim = [&](int type, int index, int material, uint32_t flags) {
@@ -653,6 +675,7 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     SrtScene* s = new SrtScene();
     s->ctx = ctx;
     s->blob_bytes = lay.total + 256;
+    stage.tick("records, entries, layout");
     cudaError_t e = cudaMalloc(&s->d_blob, s->blob_bytes);
     if (e != cudaSuccess) {
         delete s;
@@ -678,8 +701,10 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
         s->d_merl.push_back(p);
         SCENE_TRY(cudaMemcpyAsync(p, d.merl_tables[i], sizeof(double) * 3 * 90 * 90 * 180, cudaMemcpyHostToDevice, ctx->stream));
     }
+    stage.tick("cudaMalloc + copies enqueued");
     if (d.n_merl) SCENE_TRY(cudaMemcpyAsync(s->d_blob + o_merltab, s->d_merl.data(), sizeof(double*) * s->d_merl.size(), cudaMemcpyHostToDevice, ctx->stream));
     SCENE_TRY(cudaStreamSynchronize(ctx->stream));
+    stage.tick("upload complete");
 #undef SCENE_TRY
 
     DScene& D = s->dev;

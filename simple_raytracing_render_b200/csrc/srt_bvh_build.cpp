@@ -4,6 +4,9 @@
 #include <algorithm>
 #include <atomic>
 #include <cfloat>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
 #include <cmath>
 #include <cstring>
 #include <future>
@@ -51,6 +54,7 @@ struct Builder {
     const float* boxes;
     std::vector<int32_t>& order;
     std::vector<BinNode> nodes;
+    std::vector<float> cent;  // [n][3] box centroids, computed once
     std::atomic<int32_t> next_node{0};
     std::atomic<int> live_tasks{0};
     int max_tasks;
@@ -58,56 +62,130 @@ struct Builder {
     Builder(const float* b, int n, std::vector<int32_t>& ord) : boxes(b), order(ord) {
         nodes.resize(std::max(1, 2 * n));
         max_tasks = (int)std::max(1u, std::thread::hardware_concurrency());
+        cent.resize(3 * (size_t)n);
+        for_chunks(0, n, [&](int f, int c, int) {
+            for (int i = f; i < f + c; i++) {
+                const float* bx = boxes + 6 * (size_t)i;
+                for (int a = 0; a < 3; a++) cent[3 * (size_t)i + a] = 0.5f * (bx[a] + bx[3 + a]);
+            }
+        });
     }
 
     int32_t alloc() { return next_node.fetch_add(1); }
 
-    void centroid(int item, float* c) const {
-        const float* b = boxes + 6 * (size_t)item;
-        for (int a = 0; a < 3; a++) c[a] = 0.5f * (b[a] + b[3 + a]);
+    // how many threads a pass over `count` items is worth (the top levels of the tree only)
+    int chunks_for(int count) const { return count >= (1 << 17) ? std::min(max_tasks, std::max(1, count >> 16)) : 1; }
+
+    // f(first, count, chunk_index) over [first, first + count) split into chunks_for(count) pieces
+    template <class F>
+    void for_chunks(int first, int count, F f) {
+        const int T = chunks_for(count);
+        if (T <= 1) {
+            f(first, count, 0);
+            return;
+        }
+        std::vector<std::thread> th;
+        th.reserve(T - 1);
+        const int per = (count + T - 1) / T;
+        for (int t = 1; t < T; t++) {
+            int lo = first + t * per, n = std::min(per, first + count - lo);
+            if (n > 0) th.emplace_back([=, &f] { f(lo, n, t); });
+        }
+        f(first, std::min(per, count), 0);
+        for (auto& x : th) x.join();
     }
+
+    struct Bins {
+        Box box[3][kBins];
+        int cnt[3][kBins];
+        void reset() {
+            for (int a = 0; a < 3; a++)
+                for (int b = 0; b < kBins; b++) {
+                    box[a][b].reset();
+                    cnt[a][b] = 0;
+                }
+        }
+    };
 
     int32_t build(int first, int count) {
         int32_t me = alloc();
         BinNode& nd = nodes[me];
+        // pass 1: node box and centroid box (per-chunk partial boxes, merged: min / max are order-free)
+        const int T = chunks_for(count);
+        Box part_one[2];
+        std::vector<Box> part_many;
+        if (T > 1) part_many.resize(2 * (size_t)T);
+        Box* part = T > 1 ? part_many.data() : part_one;  // no heap traffic in the ~n small nodes
+        for (int t = 0; t < 2 * T; t++) part[t].reset();
+        for_chunks(first, count, [&](int f, int c, int t) {
+            Box nb, cbx;
+            nb.reset();
+            cbx.reset();
+            for (int i = f; i < f + c; i++) {
+                const int item = order[i];
+                nb.grow(boxes + 6 * (size_t)item);
+                const float* cc = &cent[3 * (size_t)item];
+                for (int a = 0; a < 3; a++) {
+                    cbx.lo[a] = std::min(cbx.lo[a], cc[a]);
+                    cbx.hi[a] = std::max(cbx.hi[a], cc[a]);
+                }
+            }
+            part[2 * t] = nb;
+            part[2 * t + 1] = cbx;
+        });
         nd.box.reset();
         Box cb;
         cb.reset();
-        for (int i = first; i < first + count; i++) {
-            const float* b = boxes + 6 * (size_t)order[i];
-            nd.box.grow(b);
-            float c[3];
-            centroid(order[i], c);
-            float cc[6] = {c[0], c[1], c[2], c[0], c[1], c[2]};
-            cb.grow(cc);
+        for (int t = 0; t < T; t++) {
+            nd.box.grow(part[2 * t]);
+            cb.grow(part[2 * t + 1]);
         }
         nd.left = nd.right = -1;
         nd.first = first;
         nd.count = count;
         if (count <= 1) return me;
 
-        // binned SAH over the three axes
+        // pass 2: binned SAH, the three axes in one sweep over the items
+        float ext[3], scale[3];
+        bool use_axis[3];
+        for (int axis = 0; axis < 3; axis++) {
+            ext[axis] = cb.hi[axis] - cb.lo[axis];
+            use_axis[axis] = ext[axis] > 0.f;
+            scale[axis] = use_axis[axis] ? (float)kBins / ext[axis] : 0.f;
+        }
+        Bins bins_one;
+        std::vector<Bins> bins_many;
+        if (T > 1) bins_many.resize((size_t)T);
+        Bins* bins = T > 1 ? bins_many.data() : &bins_one;
+        for_chunks(first, count, [&](int f, int c, int t) {
+            Bins& B = bins[t];
+            B.reset();
+            for (int i = f; i < f + c; i++) {
+                const int item = order[i];
+                const float* bx = boxes + 6 * (size_t)item;
+                const float* cc = &cent[3 * (size_t)item];
+                for (int axis = 0; axis < 3; axis++) {
+                    if (!use_axis[axis]) continue;
+                    int b = (int)((cc[axis] - cb.lo[axis]) * scale[axis]);
+                    b = std::min(kBins - 1, std::max(0, b));
+                    B.cnt[axis][b]++;
+                    B.box[axis][b].grow(bx);
+                }
+            }
+        });
+        for (int t = 1; t < T; t++)
+            for (int axis = 0; axis < 3; axis++)
+                for (int b = 0; b < kBins; b++) {
+                    bins[0].cnt[axis][b] += bins[t].cnt[axis][b];
+                    bins[0].box[axis][b].grow(bins[t].box[axis][b]);
+                }
         float best_cost = FLT_MAX;
         int best_axis = -1, best_split = -1;
         float parent_area = nd.box.half_area();
         for (int axis = 0; axis < 3; axis++) {
-            float ext = cb.hi[axis] - cb.lo[axis];
-            if (!(ext > 0.f)) continue;
-            Box bin_box[kBins];
-            int bin_cnt[kBins];
-            for (int b = 0; b < kBins; b++) {
-                bin_box[b].reset();
-                bin_cnt[b] = 0;
-            }
-            float scale = (float)kBins / ext;
-            for (int i = first; i < first + count; i++) {
-                float c[3];
-                centroid(order[i], c);
-                int b = (int)((c[axis] - cb.lo[axis]) * scale);
-                b = std::min(kBins - 1, std::max(0, b));
-                bin_cnt[b]++;
-                bin_box[b].grow(boxes + 6 * (size_t)order[i]);
-            }
+            if (!use_axis[axis]) continue;
+            const Box* bin_box = bins[0].box[axis];
+            const int* bin_cnt = bins[0].cnt[axis];
             float right_area[kBins];
             int right_cnt[kBins];
             Box acc;
@@ -138,13 +216,10 @@ struct Builder {
             float split_cost = kTraversalCost + kIntersectCost * best_cost / std::max(parent_area, 1e-30f);
             float leaf_cost = kIntersectCost * count;
             if (count <= kMaxLeaf && leaf_cost <= split_cost) return me;
-            float ext = cb.hi[best_axis] - cb.lo[best_axis];
-            float scale = (float)kBins / ext;
-            float lo = cb.lo[best_axis];
+            const float bscale = scale[best_axis];
+            const float lo = cb.lo[best_axis];
             auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](int32_t item) {
-                float c[3];
-                centroid(item, c);
-                int b = (int)((c[best_axis] - lo) * scale);
+                int b = (int)((cent[3 * (size_t)item + best_axis] - lo) * bscale);
                 b = std::min(kBins - 1, std::max(0, b));
                 return b <= best_split;
             });
@@ -157,7 +232,7 @@ struct Builder {
         }
         int lc = mid - first, rc = count - lc;
         int32_t l, r;
-        bool spawn = lc > 65536 && rc > 65536 && live_tasks.load() < max_tasks;
+        bool spawn = lc > 4096 && rc > 4096 && live_tasks.load() < max_tasks;
         if (spawn) {
             live_tasks.fetch_add(1);
             auto fut = std::async(std::launch::async, [&, first, lc] { return build(first, lc); });
@@ -257,14 +332,23 @@ struct Collapser {
 void build_wide_bvh(const float* boxes, int n, WideBvh& out) {
     out.order.resize(n);
     for (int i = 0; i < n; i++) out.order[i] = i;
+    auto T0 = std::chrono::steady_clock::now();
     Builder b(boxes, n, out.order);
+    auto T1 = std::chrono::steady_clock::now();
     b.build(0, n);
+    auto T2 = std::chrono::steady_clock::now();
     out.nodes.clear();
     out.nodes.reserve((size_t)n / 2 + 4);
     Collapser c(b.nodes, out.nodes);
     c.root_area = std::max(b.nodes[0].box.half_area(), 1e-30f);
     c.emit(0);
     out.sah_cost = (float)c.sah;
+    if (getenv("SRT_SCENE_TIMING")) {
+        auto T3 = std::chrono::steady_clock::now();
+        auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+        fprintf(stderr, "[build_wide_bvh] n %d: setup %.1f ms, binary SAH build %.1f ms, collapse %.1f ms\n", n, ms(T0, T1),
+                ms(T1, T2), ms(T2, T3));
+    }
 }
 
 namespace {
