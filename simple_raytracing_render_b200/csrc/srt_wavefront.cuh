@@ -568,50 +568,56 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         // next path, Raytracing_n.cpp:827-836.  The CTA takes ALL the work items it needs with one atomic
         // on the global counter; queue position i gets item base + i, so the new camera rays of the CTA
         // are consecutive samples of one or two pixels, generated by full warps in converged code. --------
+        // once the global counter has run out no slot can be restarted: the drain at the end of the frame
+        // skips this pass and its two barriers.  The flag is read BEFORE the barrier: thread 0 sets it
+        // between the two barriers below, so every thread of the CTA sees the same value here.
+        const int exhausted_before = Q.exhausted;
         __syncthreads();
-        if (threadIdx.x == 0) {
-            const int n = Q.count[SC_DEAD];
-            unsigned long long base = 0;
-            int avail = 0;
-            if (n > 0 && !Q.exhausted) {
-                base = atomicAdd(work_counter, (unsigned long long)n);
-                if (base < A.n_items) avail = (int)min((unsigned long long)n, A.n_items - base);
-                if (base + (unsigned long long)n >= A.n_items) Q.exhausted = 1;
-            }
-            s_item_base = base;
-            s_item_avail = avail;
-        }
-        __syncthreads();
-        {
-            const unsigned long long base = s_item_base;
-            const int avail = s_item_avail;
-            int ls, pos;
-            bool valid;
-            while (q_take(Q, SC_DEAD, ls, valid, pos)) {
-                if (pos - lane >= avail) break;  // the rest of the queue gets no item: those slots stay empty
-                const bool start = valid && pos < avail;
-                if (start) {
-                    const int slot = cta_base + ls;
-                    const unsigned long long item = base + (unsigned)pos;
-                    const int pixel = (int)(item / (unsigned)A.n_chunks);
-                    const int s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
-                    const int i = pixel % (A.mod_ny ? A.ny : A.nx);
-                    const int j = A.ny - 1 - (pixel / A.nx);
-                    const double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
-                    const double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
-                    const float u = xdiv((float)(sx + (double)i), (float)A.nx);
-                    const float v = xdiv((float)(sy + (double)j), (float)A.ny);
-                    Philox rng;
-                    philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-                    const Ray r = camera_get_ray(S.camera, u, v, rng);
-                    st.item[slot] = make_int4(pixel, s, 0, 0);
-                    st.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-                    st.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
-                    st.thr[slot] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
-                    st.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-                    wf_store_rng(st, slot, rng);
+        if (!exhausted_before) {
+            if (threadIdx.x == 0) {
+                const int n = Q.count[SC_DEAD];
+                unsigned long long base = 0;
+                int avail = 0;
+                if (n > 0 && !Q.exhausted) {
+                    base = atomicAdd(work_counter, (unsigned long long)n);
+                    if (base < A.n_items) avail = (int)min((unsigned long long)n, A.n_items - base);
+                    if (base + (unsigned long long)n >= A.n_items) Q.exhausted = 1;
                 }
-                q_push(Q, TC_NEW, start, ls);
+                s_item_base = base;
+                s_item_avail = avail;
+            }
+            __syncthreads();
+            {
+                const unsigned long long base = s_item_base;
+                const int avail = s_item_avail;
+                int ls, pos;
+                bool valid;
+                while (q_take(Q, SC_DEAD, ls, valid, pos)) {
+                    if (pos - lane >= avail) break;  // the rest of the queue gets no item: those slots stay empty
+                    const bool start = valid && pos < avail;
+                    if (start) {
+                        const int slot = cta_base + ls;
+                        const unsigned long long item = base + (unsigned)pos;
+                        const int pixel = (int)(item / (unsigned)A.n_chunks);
+                        const int s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
+                        const int i = pixel % (A.mod_ny ? A.ny : A.nx);
+                        const int j = A.ny - 1 - (pixel / A.nx);
+                        const double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
+                        const double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
+                        const float u = xdiv((float)(sx + (double)i), (float)A.nx);
+                        const float v = xdiv((float)(sy + (double)j), (float)A.ny);
+                        Philox rng;
+                        philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
+                        const Ray r = camera_get_ray(S.camera, u, v, rng);
+                        st.item[slot] = make_int4(pixel, s, 0, 0);
+                        st.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
+                        st.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
+                        st.thr[slot] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
+                        st.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
+                        wf_store_rng(st, slot, rng);
+                    }
+                    q_push(Q, TC_NEW, start, ls);
+                }
             }
         }
         __syncthreads();
