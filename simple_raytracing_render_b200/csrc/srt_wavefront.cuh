@@ -631,6 +631,7 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         // gathered ray held 8 % of the stall samples).
         for (int ci = 0; ci < 2; ci++) {
             const int c = (SRT_WFS_TRACE_NEW_FIRST ? ci == 0 : ci == 1) ? TC_NEW : TC_CONT;
+            if (Q.count[c] == 0) continue;
             int ls, pos, ls_next = 0;
             bool valid, valid_next = false;
             float4 o = make_float4(0.f, 0.f, 0.f, 0.f), d = o, o_next = o, d_next = o;
@@ -681,6 +682,7 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         __syncthreads();
         // ---- SHADE: one level of color() per queued slot, material by material -------------------------
         for (int c = SC_MISS; c < SC_N; c++) {
+            if (Q.count[c] == 0) continue;  // nothing of this material: no trip to the cursor
             int ls, pos;
             bool valid;
             while (q_take(Q, c, ls, valid, pos)) {
