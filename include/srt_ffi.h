@@ -29,7 +29,7 @@
 extern "C" {
 #endif
 
-#define SRT_ABI_VERSION 1
+#define SRT_ABI_VERSION 2
 
 /* ---- status codes ------------------------------------------------------------------------ */
 enum {
@@ -257,6 +257,9 @@ typedef struct SrtCounters {
     uint64_t kernel_launches; /* kernels launched by this library on this context so far */
     uint64_t culled_rays;  /* continuation rays the reference traces with an all-zero throughput
                               (they cannot change the sample); the backend does not trace them */
+    uint64_t stack_overflows; /* wide-BVH traversals whose per-thread stack was full when a subtree had to be
+                                 postponed, since the context was created (every kernel, not only the counted
+                                 replay).  MUST be 0: a non-zero value means a closest hit may be wrong. */
 } SrtCounters;
 
 typedef struct SrtSceneInfo {
@@ -271,6 +274,10 @@ typedef struct SrtSceneInfo {
     int32_t render_registers;     /* registers per thread of that variant */
     int32_t render_blocks_per_sm; /* its resident blocks per SM */
     int64_t hot_table_bytes; /* entries + instance ops + primitive records + lights */
+    int32_t bvh_max_depth;   /* deepest wide-BVH leaf over all bvhs (levels of inner nodes above it) */
+    int32_t bvh_builder;     /* 0: host binned SAH (srt_bvh_build.cpp), 1: device LBVH (srt_lbvh.cuh) */
+    float upload_ms;         /* host -> device copies of srt_scene_create */
+    int32_t _pad;
 } SrtSceneInfo;
 
 typedef struct SrtContext SrtContext;
@@ -301,6 +308,13 @@ int srt_scene_info(const SrtScene* scene, SrtSceneInfo* out);
  * (hitable.h:17-25).  All pointers may be host or device memory (detected per pointer). */
 int srt_trace_closest(SrtScene* scene, const float* rays, int64_t n, int32_t* prim_id, float* t,
                       float* rec);
+
+/* The camera rays of the sample loop: for every pixel (in `curpixel` order) and every Sobol index s in
+ * [s_begin, s_end): u = (sobol[s][0] + i) / nx, v = (sobol[s][1] + j) / ny, camera::get_ray(u, v)
+ * (Raytracing_n.cpp:827-836, camera.h:51-59), generated by the SAME device routine the render kernels start
+ * their paths with (same Philox counters: a ray here is the ray srt_render traces for that pixel and sample).
+ * rays_out: [nx*ny*(s_end-s_begin)][7] = origin, direction, time; host or device pointer. */
+int srt_primary_rays(SrtScene* scene, const SrtRenderParams* params, float* rays_out);
 
 /* mixture-density probe used by the light-sampling branch: for each (origin, direction) pair
  * returns hitable_list::pdf_value over the light list (hitable_list.h:54-62, pdf.h:162-164).
@@ -351,6 +365,11 @@ int srt_selftest_division(SrtContext* ctx, const float* a, const float* b, int64
  * (16 chains per thread, 8 CTAs x 256 threads per SM, best of 6 launches) — the measured denominator of
  * the FP32 roofline fraction, since MEASURED_PEAKS.json carries HBM and tensor peaks only. */
 int srt_measure_fp32_peak(SrtContext* ctx, double* tflops);
+
+/* Measurement aid (bench.py): L2-resident streaming read bandwidth of this GPU in GB/s — every SM reads a
+ * 32 MiB buffer (a quarter of the 126 MB L2) over and over with 128-bit loads, best of 6 launches after a
+ * warm-up pass that brings the buffer into L2.  The measured denominator of the L2 roofline fraction. */
+int srt_measure_l2_peak(SrtContext* ctx, double* gbps);
 
 /* Host-side helpers (no device work): the reference's Sobol table (Raytracing_n.cpp:721-812,
  * D = 2; direction numbers of contents/sobol/new-joe-kuo-6.21201 line 2) as u32 numerators of

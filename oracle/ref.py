@@ -103,6 +103,8 @@ def lib():
         "ref_primary_rays": (C.c_int, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_uint64, C.c_int, C.c_void_p]),
         "ref_trace": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
         "ref_light_pdf": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_void_p]),
+        "ref_light_random": (C.c_int, [C.c_int, C.c_void_p, C.c_int64, C.c_uint64, C.c_void_p]),
+        "ref_triangle_soup_bvh": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.c_int]),
         "ref_render_float": (C.c_int, [C.c_int] * 7 + [C.c_uint64, C.c_int, C.c_void_p, C.c_void_p]),
         "ref_render_timed": (C.c_double, [C.c_int] * 6 + [C.c_uint64, C.c_void_p]),
         "ref_crender_run": (C.c_int, [C.c_int] * 5 + [C.c_char_p, C.c_char_p]),
@@ -188,6 +190,14 @@ class RefScene:
         od = np.ascontiguousarray(od, np.float32).reshape(-1, 6)
         out = np.zeros(len(od), np.float32)
         if lib().ref_light_pdf(self.h, od.ctypes.data, len(od), out.ctypes.data) != 0:
+            raise RuntimeError(_err())
+        return out
+
+    def light_random(self, o: np.ndarray, seed=1) -> np.ndarray:
+        """hitable_list::random over the light list for origins o [n][3] (the reference's own sampler)."""
+        o = np.ascontiguousarray(o, np.float32).reshape(-1, 3)
+        out = np.zeros_like(o)
+        if lib().ref_light_random(self.h, o.ctypes.data, len(o), seed, out.ctypes.data) != 0:
             raise RuntimeError(_err())
         return out
 
@@ -351,11 +361,9 @@ class RefBuilder:
         elif isinstance(o, S.triangle_soup):
             # `new bvh_node(triangles, n, 0, 1)` over real triangle objects (Raytracing_n.cpp:286, :349)
             m = self._mat(o.mat)
-            ids = np.empty(len(o.pos), np.int32)
-            for k in range(len(o.pos)):
-                ids[k] = L.ref_triangle(o.pos[k].ctypes.data, o.uv[k].ctypes.data, o.nrm[k].ctypes.data, m)
+            pos, uv, nrm = (np.ascontiguousarray(a, np.float32) for a in (o.pos, o.uv, o.nrm))
             L.ref_set_seed(int(o.seed_at_build))
-            h = L.ref_bvh_node(ids.ctypes.data_as(C.POINTER(C.c_int32)), len(ids), 0.0, 1.0)
+            h = L.ref_triangle_soup_bvh(pos.ctypes.data, uv.ctypes.data, nrm.ctypes.data, len(pos), m)
         elif isinstance(o, S.bvh_node):
             hs = (C.c_int32 * max(1, len(o.items)))(*[self._hit(x) for x in o.items])
             # the reference's constructor draws its split axes from the global drand48 stream

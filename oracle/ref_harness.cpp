@@ -341,6 +341,21 @@ int ref_bvh_node(const int* hs, int n, float t0, float t1) {
     for (int i = 0; i < n; i++) l[i] = get<hitable>(hs[i], K_HIT);
     return put(K_HIT, new bvh_node(l, n, t0, t1));
 }
+// `new bvh_node(triangles, n, 0, 1)` over n real triangle objects built from arrays in one call (what
+// RefBuilder does one ref_triangle() at a time; 10 M Python round trips are too slow).  pos [n][9],
+// uv [n][6], nrm [n][9].  The objects are not registered one by one; prim ids come from the flattener.
+int ref_triangle_soup_bvh(const float* pos, const float* uv, const float* nrm, int64_t n, int mat) {
+    material* m = get<material>(mat, K_MAT);
+    hitable** l = new hitable*[n > 0 ? n : 1];
+    for (int64_t i = 0; i < n; i++) {
+        const float* p = pos + 9 * i;
+        const float* u = uv + 6 * i;
+        const float* q = nrm + 9 * i;
+        l[i] = new triangle(vec3(p), vec3(p + 3), vec3(p + 6), m, vec3(u[0], u[1], 0), vec3(u[2], u[3], 0),
+                            vec3(u[4], u[5], 0), vec3(q), vec3(q + 3), vec3(q + 6));
+    }
+    return put(K_HIT, new bvh_node(l, (int)n, 0, 1));
+}
 // teapot.h:76-166 -> bvh_node over its triangles (Raytracing_n.cpp:348-350).  triangleCount is
 // zeroed and the triangles' n0..n2 set to the face normal through public members first.
 int ref_teapot_bvh(float scale, int mat, int* n_tris_out) {
@@ -548,6 +563,21 @@ int ref_light_pdf(int scene, const float* od, int64_t n, float* out) {
     for (int64_t i = 0; i < n; i++) {
         const float* q = od + 6 * i;
         out[i] = s->hlist->pdf_value(vec3(q[0], q[1], q[2]), vec3(q[3], q[4], q[5]));
+    }
+    return 0;
+}
+
+// ---- light sampling: hitable_pdf::generate -> hitable_list::random (pdf.h:166-168, hitable_list.h:64-67)
+//      with the reference's own drand48 stream.  o: [n][3]; out: [n][3] directions. -----------------
+int ref_light_random(int scene, const float* o, int64_t n, uint64_t rng_seed, float* out) {
+    Scene* s = get<Scene>(scene, K_SCENE);
+    if (!s || !s->hlist) return -1;
+    seed = rng_seed;
+    for (int64_t i = 0; i < n; i++) {
+        vec3 d = s->hlist->random(vec3(o[3 * i], o[3 * i + 1], o[3 * i + 2]));
+        out[3 * i] = d.e[0];
+        out[3 * i + 1] = d.e[1];
+        out[3 * i + 2] = d.e[2];
     }
     return 0;
 }

@@ -1,5 +1,5 @@
 // oracle/shim.h — force-included (g++ -include) in front of the UNMODIFIED reference translation
-// unit so that it compiles with g++ on Linux.  TEST INFRASTRUCTURE ONLY (see oracle/README.md).
+// unit so that it compiles with g++ on Linux.  TEST INFRASTRUCTURE ONLY.
 //
 // Why each line exists:
 //   * Raytracing_n/mathf.h:6-8 defines the macros __m, __c, __a, which collide with identifiers

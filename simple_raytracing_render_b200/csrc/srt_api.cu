@@ -45,7 +45,8 @@ struct SrtContext {
     int sm_count = 0;
     unsigned long long launches = 0;
     SrtCounters last = {};
-    unsigned long long* d_counters = nullptr;  // 8 x u64
+    unsigned long long* d_counters = nullptr;  // 16 x u64: [0..6] SrtCounters of a counted replay, [7] work counter,
+                                               // [8] wide-BVH stack overflows (DScene::diag), never reset
     uint8_t* d_rgb8 = nullptr;                 // resolve staging for host outputs
     size_t rgb8_cap = 0;
     uint8_t* h_rgb8 = nullptr;  // pinned
@@ -71,6 +72,10 @@ struct SrtContext {
     WfVariantInfo wf_info[SRT_N_WF_VARIANTS] = {};
     size_t wf_info_smem[SRT_N_WF_VARIANTS] = {};
     unsigned long long wf_passes = 0;  // passes enqueued by the last wavefront render
+    // persisting-L2 window over the slot pool (run_wavefront)
+    size_t l2_persist_max = 0, l2_window_max = 0;
+    const void* l2_window_base = nullptr;
+    size_t l2_window_bytes = 0;
 };
 
 struct SrtScene {
@@ -322,8 +327,10 @@ int srt_context_create(int device, void* cuda_stream, SrtContext** out) {
     cudaDeviceProp prop;
     CUDA_TRY(cudaGetDeviceProperties(&prop, device));
     c->sm_count = prop.multiProcessorCount;
-    CUDA_TRY(cudaMalloc(&c->d_counters, 8 * sizeof(unsigned long long)));
-    CUDA_TRY(cudaMemset(c->d_counters, 0, 8 * sizeof(unsigned long long)));
+    c->l2_persist_max = (size_t)std::max(0, prop.persistingL2CacheMaxSize);
+    c->l2_window_max = (size_t)std::max(0, prop.accessPolicyMaxWindowSize);
+    CUDA_TRY(cudaMalloc(&c->d_counters, 16 * sizeof(unsigned long long)));
+    CUDA_TRY(cudaMemset(c->d_counters, 0, 16 * sizeof(unsigned long long)));
     *out = c;
     return 0;
 }
@@ -398,7 +405,7 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     std::vector<int32_t> leaf_rank;
     std::vector<float4> leaf_geom;
     float top_sah = 0.f;
-    int top_items = 0;
+    int top_items = 0, max_depth = 0;
     for (int bi = 0; bi < d.n_bvhs; bi++) {
         const SrtBvh& sb = d.bvhs[bi];
         int n = sb.item_count;
@@ -464,6 +471,7 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
                 leaf_geom.push_back(float4{q[6], q[7], q[8], 0.f});
             }
         }
+        max_depth = std::max(max_depth, wb.max_depth);
         if (n > top_items) {
             top_items = n;
             top_sah = wb.sah_cost;
@@ -739,6 +747,7 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     D.n_textures = d.n_textures;
     D.n_bvhs = d.n_bvhs;
     D.n_ops = d.n_ops;
+    D.diag = ctx->d_counters + 8;
     D.hot_bytes = (uint32_t)(hot_end - o_entries);
     D.features = feat;
     D.camera = d.camera;
@@ -755,6 +764,8 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     s->info.bvh_node_bytes = (int64_t)(wide.size() * sizeof(WideNode4));
     s->info.device_bytes = (int64_t)s->blob_bytes + (int64_t)d.n_merl * 8 * 3 * 90 * 90 * 180;
     s->info.sah_cost = top_sah;
+    s->info.bvh_max_depth = max_depth;
+    s->info.bvh_builder = 0;
     s->info.build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
     *out = s;
     return 0;
@@ -893,6 +904,41 @@ int srt_measure_fp32_peak(SrtContext* c, double* tflops) {
     return 0;
 }
 
+int srt_measure_l2_peak(SrtContext* c, double* gbps) {
+    if (!c || !gbps) return fail(SRT_E_INVALID, "null argument");
+    CUDA_TRY(cudaSetDevice(c->device));
+    const size_t bytes = 32u << 20;
+    const long long n_vec = (long long)(bytes / sizeof(float4));
+    const int threads = 512, blocks = c->sm_count * 2, passes = 4;
+    float4* buf = nullptr;
+    float* sink = nullptr;
+    CUDA_TRY(cudaMalloc(&buf, bytes));
+    CUDA_TRY(cudaMalloc(&sink, sizeof(float) * threads * (size_t)blocks));
+    CUDA_TRY(cudaMemsetAsync(buf, 0, bytes, c->stream));
+    cudaEvent_t e0, e1;
+    CUDA_TRY(cudaEventCreate(&e0));
+    CUDA_TRY(cudaEventCreate(&e1));
+    double best = 0.0;
+    for (int rep = 0; rep < 7; rep++) {  // the first repetition brings the buffer into L2
+        CUDA_TRY(cudaEventRecord(e0, c->stream));
+        srt::k_l2_peak<<<blocks, threads, 0, c->stream>>>(buf, n_vec, passes, sink);
+        CUDA_TRY(cudaEventRecord(e1, c->stream));
+        CUDA_TRY(cudaEventSynchronize(e1));
+        c->launches++;
+        float ms = 0.f;
+        CUDA_TRY(cudaEventElapsedTime(&ms, e0, e1));
+        double moved = (double)bytes * passes * blocks;
+        if (rep > 0 && ms > 0.f) best = std::max(best, moved / (ms * 1e-3) / 1e9);
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(buf);
+    cudaFree(sink);
+    CUDA_TRY(cudaGetLastError());
+    *gbps = best;
+    return 0;
+}
+
 int srt_sobol_points_u32(uint32_t N, uint32_t* out) {
     // Raytracing_n.cpp:721-812 with D = 2: gray-code order, dimension 1 all m = 1, dimension 2 from
     // line 2 of new-joe-kuo-6.21201 ("2 1 0 1": s = 1, a = 0, m1 = 1).
@@ -986,18 +1032,22 @@ int pick_variant(const SrtScene* s, bool counting) {
 }
 
 const WfVariantFn kWfVariants[SRT_N_WF_VARIANTS] = {srt_wavefront_variant_0, srt_wavefront_variant_1, srt_wavefront_variant_2,
-                                                     srt_wavefront_variant_3};
+                                                     srt_wavefront_variant_3, srt_wavefront_variant_4};
 constexpr uint32_t kWfMask[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_MASK(0), SRT_WF_VARIANT_MASK(1), SRT_WF_VARIANT_MASK(2),
-                                                 SRT_WF_VARIANT_MASK(3)};
+                                                 SRT_WF_VARIANT_MASK(3), SRT_WF_VARIANT_MASK(4)};
+constexpr int kWfCounting[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_COUNTING(0), SRT_WF_VARIANT_COUNTING(1),
+                                                SRT_WF_VARIANT_COUNTING(2), SRT_WF_VARIANT_COUNTING(3),
+                                                SRT_WF_VARIANT_COUNTING(4)};
 constexpr int kWfMaxPasses = 1 << 20;
 constexpr int kWfBatch = 8;  // passes enqueued between two polls of the live count
 
-int pick_wf_variant(const SrtScene* s) {
+int pick_wf_variant(const SrtScene* s, bool counting) {
     uint32_t need = s->dev.features & F_ALL_SCENE;
     bool smem_ok = s->dev.hot_bytes <= kMaxHotSmem && !env_int("SRT_NO_SMEM", 0);
-    int forced = env_int("SRT_WF_VARIANT", -1);
+    int forced = counting ? -1 : env_int("SRT_WF_VARIANT", -1);
     for (int v = 0; v < SRT_N_WF_VARIANTS; v++) {
         if (forced >= 0 && v != forced) continue;
+        if (kWfCounting[v] != (counting ? 1 : 0)) continue;
         if ((kWfMask[v] & F_SMEM_TABLES) && !smem_ok) continue;
         if ((kWfMask[v] & need) != need) continue;
         return v;
@@ -1047,6 +1097,28 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, 
         c->wf_cap = 0;
         CUDA_TRY(cudaMalloc(&c->d_wf, need));
         c->wf_cap = need;
+    }
+    // Persisting-L2 window over the slot pool.  The pool is rewritten a few hundred times per frame and is
+    // sized to live in L2; without a policy L2 evicts (and writes back) part of it all frame long — measured
+    // 6 GB (C2) to 200 GB (C5-like) of DRAM writes per frame that no algorithm needs (profiles/r01_notes.md,
+    // captures L, N).  With hitProp = persisting the pool's lines stay resident in the set-aside part of L2;
+    // everything else (scene, image) uses the rest as before.  SRT_L2_PERSIST=0 switches it off (A/B).
+    if (env_int("SRT_L2_PERSIST", 1) && c->l2_persist_max > 0 && c->l2_window_max > 0 &&
+        (c->l2_window_base != c->d_wf || c->l2_window_bytes != need)) {
+        const size_t window = std::min(need, c->l2_window_max);
+        const size_t setaside = std::min(window, c->l2_persist_max);
+        // best effort: a stream or driver that refuses the policy renders exactly as before
+        cudaError_t pe = cudaDeviceSetLimit(cudaLimitPersistingL2CacheSize, setaside);
+        cudaStreamAttrValue at = {};
+        at.accessPolicyWindow.base_ptr = c->d_wf;
+        at.accessPolicyWindow.num_bytes = window;
+        at.accessPolicyWindow.hitRatio = (float)std::min(1.0, (double)setaside / (double)window);
+        at.accessPolicyWindow.hitProp = cudaAccessPropertyPersisting;
+        at.accessPolicyWindow.missProp = cudaAccessPropertyStreaming;
+        if (pe == cudaSuccess) pe = cudaStreamSetAttribute(c->stream, cudaStreamAttributeAccessPolicyWindow, &at);
+        if (pe != cudaSuccess) cudaGetLastError();
+        c->l2_window_base = c->d_wf;
+        c->l2_window_bytes = need;
     }
     if (!c->d_live) {
         CUDA_TRY(cudaMalloc(&c->d_live, sizeof(int) * kWfMaxPasses));
@@ -1136,10 +1208,17 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     // (DESIGN.md 5.1): scenes made of a handful of primitives stay on the fused kernel, whose whole
     // frame is shorter than the wavefront's ramp-up and tail.
     int wf_env = env_int("SRT_WAVEFRONT", -1);
-    bool wavefront = !counting && (wf_env >= 0 ? wf_env != 0
-                                               : ((p->flags & SRT_RENDER_WAVEFRONT) != 0 || auto_wavefront(s, p)));
-    int wv = wavefront ? pick_wf_variant(s) : -1;
+    // a counted replay runs on the instrumented build of the scheduler the plain call would pick
+    bool wavefront = wf_env >= 0 ? wf_env != 0 : ((p->flags & SRT_RENDER_WAVEFRONT) != 0 || auto_wavefront(s, p));
+    int wv = wavefront ? pick_wf_variant(s, counting) : -1;
     if (wv < 0) wavefront = false;
+    // wavefront form: 1 two kernels per bounce, 2 persistent kernel, 3 persistent kernel with sorted queues
+    int wf_mode = !wavefront ? 0 : (wf_env >= 1 && wf_env <= 3 ? wf_env : env_int("SRT_WF_MODE", 3));
+    if (wf_mode == 3 && std::min(count, env_int("SRT_CHUNK", 1)) > 1) wf_mode = 2;  // the queues hold one path per item
+    if (wavefront && counting && wf_mode != 3) {  // only the sorted scheduler has an instrumented build
+        wavefront = false;
+        wf_mode = 0;
+    }
     int v = pick_variant(s, counting);
     if (v < 0) return fail(SRT_E_UNSUPPORTED, "no render-kernel variant covers feature mask 0x%x", s->dev.features);
     size_t smem = (kVariantMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
@@ -1172,10 +1251,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
         s->variant_regs = info.registers;
         s->variant_smem = smem;
     }
-    // wavefront form: 1 two kernels per bounce, 2 persistent kernel, 3 persistent kernel with sorted queues
-    int wf_mode = !wavefront ? 0 : (wf_env >= 1 && wf_env <= 3 ? wf_env : env_int("SRT_WF_MODE", 3));
-    if (wf_mode == 3 && std::min(count, env_int("SRT_CHUNK", 1)) > 1) wf_mode = 2;  // the queues hold one path per item
-    if (wavefront) s->variant = 100 * wf_mode + wv;
+    if (wavefront && !counting) s->variant = 100 * wf_mode + wv;
     int blocks_per_sm = std::max(1, info.blocks_per_sm);
 
     // work decomposition (srt_kernels.cuh): an item is `chunk` consecutive Sobol indices of one pixel,
@@ -1259,6 +1335,30 @@ int srt_render(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_device) {
     return launch_render(s, p, accum_rgb_device, false);
 }
 
+int srt_primary_rays(SrtScene* s, const SrtRenderParams* p, float* rays_out) {
+    if (!s || !rays_out) return fail(SRT_E_INVALID, "null argument");
+    int rc = check_params(p);
+    if (rc) return rc;
+    SrtContext* c = s->ctx;
+    CUDA_TRY(cudaSetDevice(c->device));
+    const long long n = (long long)p->nx * p->ny * (p->s_end - p->s_begin);
+    if (n <= 0) return 0;
+    if ((rc = ensure_sobol(c, (uint32_t)p->s_end))) return rc;
+    DevOut o;
+    if ((rc = o.init(rays_out, sizeof(float) * 7 * (size_t)n))) return rc;
+    srt::RenderArgs A = {};
+    A.nx = p->nx;
+    A.ny = p->ny;
+    A.s_begin = p->s_begin;
+    A.s_end = p->s_end;
+    A.seed = p->seed;
+    A.mod_ny = (p->flags & SRT_COMPAT_PIXEL_MOD_NY) ? 1 : 0;
+    srt::k_primary_rays<<<(unsigned)((n + 127) / 128), 128, 0, c->stream>>>(s->dev.camera, A, c->d_sobol, (float*)o.ptr);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return o.finish(c->stream);
+}
+
 int srt_render_counted(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_device, SrtCounters* out) {
     if (!s || !accum_rgb_device) return fail(SRT_E_INVALID, "null argument");
     int rc = check_params(p);
@@ -1268,7 +1368,7 @@ int srt_render_counted(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_d
     CUDA_TRY(cudaMemsetAsync(c->d_counters, 0, 8 * sizeof(unsigned long long), c->stream));
     rc = launch_render(s, p, accum_rgb_device, true);
     if (rc) return rc;
-    unsigned long long h[8];
+    unsigned long long h[9];
     CUDA_TRY(cudaMemcpyAsync(h, c->d_counters, sizeof h, cudaMemcpyDeviceToHost, c->stream));
     CUDA_TRY(cudaStreamSynchronize(c->stream));
     c->last.paths = h[0];
@@ -1279,6 +1379,7 @@ int srt_render_counted(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_d
     c->last.reject_iters = h[5];
     c->last.kernel_launches = c->launches;
     c->last.culled_rays = h[6];
+    c->last.stack_overflows = h[8];
     if (out) *out = c->last;
     return 0;
 }
@@ -1287,6 +1388,12 @@ int srt_counters_get(const SrtContext* ctx, SrtCounters* out) {
     if (!ctx || !out) return fail(SRT_E_INVALID, "null argument");
     *out = ctx->last;
     out->kernel_launches = ctx->launches;
+    // the overflow tally is live (every kernel of the context adds to it): read it behind the queued work
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    unsigned long long ov = 0;
+    CUDA_TRY(cudaMemcpyAsync(&ov, ctx->d_counters + 8, sizeof ov, cudaMemcpyDeviceToHost, ctx->stream));
+    CUDA_TRY(cudaStreamSynchronize(ctx->stream));
+    out->stack_overflows = ov;
     return 0;
 }
 

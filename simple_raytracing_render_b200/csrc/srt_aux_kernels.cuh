@@ -45,6 +45,28 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene S, const float* __
     }
 }
 
+// The camera rays of the sample loop (Raytracing_n.cpp:827-836, camera.h:51-59) through start_path, the routine
+// every render scheduler starts its paths with.  One thread per (pixel, sample); rays: [n_pixels * count][7].
+__global__ void __launch_bounds__(128) k_primary_rays(SrtCamera cam, RenderArgs A, const uint32_t* __restrict__ sobol,
+                                                      float* __restrict__ rays) {
+    const long long n = (long long)A.nx * A.ny * (A.s_end - A.s_begin);
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const int count = A.s_end - A.s_begin;
+    const int pixel = (int)(i / count);
+    const int s = A.s_begin + (int)(i - (long long)pixel * count);
+    Philox rng;
+    const Ray r = start_path(cam, A, sobol, pixel, s, rng);
+    float* o = rays + 7 * i;
+    o[0] = r.o.x;
+    o[1] = r.o.y;
+    o[2] = r.o.z;
+    o[3] = r.d.x;
+    o[4] = r.d.y;
+    o[5] = r.d.z;
+    o[6] = r.time;
+}
+
 // hitable_list::pdf_value over the light list (hitable_list.h:54-62) for (origin, direction) pairs.
 __global__ void __launch_bounds__(128) k_light_pdf(DScene S, const float* __restrict__ od, long long n,
                                                    float* __restrict__ out) {
@@ -113,6 +135,39 @@ __global__ void __launch_bounds__(256) k_fp32_peak(float* __restrict__ out, int 
 #pragma unroll
     for (int k = 0; k < 16; k++) s += a[k];
     if (s == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = s;  // never true: keeps the chains alive
+}
+
+// Measured L2 roofline denominator (bench.py): every CTA streams the whole buffer (L2-resident: 32 MiB) with
+// 128-bit loads, `passes` times, each CTA starting at a different offset so that the SMs do not march
+// through the slices in lockstep.  n_vec must be a multiple of blockDim.x * 4.
+__global__ void __launch_bounds__(512) k_l2_peak(const float4* __restrict__ buf, long long n_vec, int passes,
+                                                 float* __restrict__ out) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    const long long stride = (long long)blockDim.x;
+    const long long start = ((long long)blockIdx.x * 7919 * stride * 4) % n_vec;
+    for (int p = 0; p < passes; p++) {
+        long long i = start + threadIdx.x;
+        for (long long k = 0; k < n_vec; k += 4 * stride) {
+            float4 a, b, c, d;
+            // ld.global.cg: cache at L2 only (the point is the L2 -> SM path, not L1 hits)
+            long long i0 = i, i1 = i + stride, i2 = i + 2 * stride, i3 = i + 3 * stride;
+            i0 -= i0 >= n_vec ? n_vec : 0;
+            i1 -= i1 >= n_vec ? n_vec : 0;
+            i2 -= i2 >= n_vec ? n_vec : 0;
+            i3 -= i3 >= n_vec ? n_vec : 0;
+            a = __ldcg(buf + i0);
+            b = __ldcg(buf + i1);
+            c = __ldcg(buf + i2);
+            d = __ldcg(buf + i3);
+            acc.x += a.x + b.x + c.x + d.x;
+            acc.y += a.y + b.y + c.y + d.y;
+            acc.z += a.z + b.z + c.z + d.z;
+            acc.w += a.w + b.w + c.w + d.w;
+            i += 4 * stride;
+            i -= i >= n_vec ? n_vec : 0;
+        }
+    }
+    if (acc.x + acc.y + acc.z + acc.w == 123.456f) out[blockIdx.x * blockDim.x + threadIdx.x] = acc.x;
 }
 
 }  // namespace srt

@@ -255,6 +255,7 @@ struct Collapser {
     std::vector<WideNode4>& out;
     double sah = 0.0;
     float root_area;
+    int max_depth = 0;
 
     Collapser(const std::vector<BinNode>& b, std::vector<WideNode4>& o) : bn(b), out(o) {}
 
@@ -281,7 +282,8 @@ struct Collapser {
     }
 
     // emit a wide node for binary node `b` (must be inner, or the single-leaf root)
-    int32_t emit(int32_t b) {
+    int32_t emit(int32_t b, int depth = 1) {
+        max_depth = std::max(max_depth, depth);
         int32_t me = (int32_t)out.size();
         out.emplace_back();
         int32_t kids[4];
@@ -319,7 +321,7 @@ struct Collapser {
                 set_slot(out[me], i, &k.box, ~k.first, k.count);
                 sah += kIntersectCost * k.count * k.box.half_area() / root_area;
             } else {
-                int32_t c = emit(kids[i]);
+                int32_t c = emit(kids[i], depth + 1);
                 set_slot(out[me], i, &k.box, c, 0);
             }
         }
@@ -343,6 +345,7 @@ void build_wide_bvh(const float* boxes, int n, WideBvh& out) {
     c.root_area = std::max(b.nodes[0].box.half_area(), 1e-30f);
     c.emit(0);
     out.sah_cost = (float)c.sah;
+    out.max_depth = c.max_depth;
     if (getenv("SRT_SCENE_TIMING")) {
         auto T3 = std::chrono::steady_clock::now();
         auto ms = [](auto a, auto b) { return std::chrono::duration<double, std::milli>(b - a).count(); };

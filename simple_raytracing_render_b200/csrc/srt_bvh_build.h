@@ -20,6 +20,7 @@ struct WideBvh {
     std::vector<WideNode4> nodes;  // nodes[0] is the root; child indices are relative to it
     std::vector<int32_t> order;    // leaf slot -> item index
     float sah_cost = 0.f;
+    int max_depth = 0;  // inner-node levels above the deepest leaf (the traversal stack holds <= 3 per level)
 };
 
 // boxes: [n][6] = min xyz, max xyz (already padded by the caller).  n >= 1.

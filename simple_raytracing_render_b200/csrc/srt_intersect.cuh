@@ -17,7 +17,7 @@
 namespace srt {
 
 struct Counters {  // per-thread tallies of an instrumented launch (SrtCounters)
-    unsigned long long rays, probe_rays, node_visits, prim_tests, reject_iters, culled_rays;
+    unsigned long long rays, probe_rays, node_visits, prim_tests, reject_iters, culled_rays, paths;
     int dbg;  // counting build only: this lane traces the path selected by SRT_DEBUG_PIXEL / _SAMPLE
 };
 
@@ -310,6 +310,11 @@ SRT_DEV bool ref_reachable(const RefNode* root, int rank, const Ray& r, RayInv i
 // it is checked for the WINNER only: a pass finds the best candidate strictly after the exclusion
 // bound (ex_t, ex_rank) in the order "smaller t first, then higher rank"; if that candidate turns
 // out unreachable it becomes the new bound and the search repeats.  One pass in all but ~1e-6 of rays.
+// The stack holds the postponed children of the current root-to-node path: at most 3 per level of OUR tree.
+// A full stack is a COUNTED condition (DScene::diag -> SrtCounters::stack_overflows, asserted 0 by the tests
+// on every configuration including the 10 M-triangle one): the postponed subtree would be lost, so the
+// caller must be able to see it.  srt_bvh_build.cpp reports the tree's depth (SrtSceneInfo::bvh_max_depth);
+// near-first descent with cull-on-pop keeps the occupied depth far below 3 x depth in practice.
 constexpr int kStackSize = 48;
 
 // Wide-node step helpers.  Children that pass the slab test are ordered near-to-far with a 5-comparator
@@ -400,6 +405,10 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
                 key_sort2(key[1], key[3]);
                 key_sort2(key[1], key[2]);
                 // push far-to-near, continue with the nearest
+                if (key[1] != kKeyNone && sp > kStackSize - 3) {  // (rare) not enough room for up to three
+                    const int want = (key[3] != kKeyNone) + (key[2] != kKeyNone) + 1;
+                    if (sp + want > kStackSize) atomicAdd(S.diag, 1ull);
+                }
                 if (key[3] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[3], (uint32_t)ref_select(refs, key[3]));
                 if (key[2] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[2], (uint32_t)ref_select(refs, key[2]));
                 if (key[1] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[1], (uint32_t)ref_select(refs, key[1]));

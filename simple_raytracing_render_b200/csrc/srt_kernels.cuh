@@ -49,6 +49,21 @@ SRT_DEV void item_commit(long long* __restrict__ fx, int pixel, V3 sum, float cl
 
 SRT_DEV View global_view(const DScene& S) { return View{S, S.entries, S.ops, S.dprims, S.lights}; }
 
+// The start of one path: pixel mapping, Sobol jitter and camera::get_ray as the sample loop does them
+// (Raytracing_n.cpp:827-836: `float u = float(samplepoints[s][0] + i) / float(nx)`), with the path's Philox
+// stream initialised on (pixel, global Sobol index).  Every scheduler and srt_primary_rays call this one routine.
+SRT_DEV Ray start_path(const SrtCamera& cam, const RenderArgs& A, const uint32_t* __restrict__ sobol, int pixel, int s,
+                       Philox& rng) {
+    const int i = pixel % (A.mod_ny ? A.ny : A.nx);
+    const int j = A.ny - 1 - (pixel / A.nx);
+    const double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
+    const double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
+    const float u = xdiv((float)(sx + (double)i), (float)A.nx);
+    const float v = xdiv((float)(sy + (double)j), (float)A.ny);
+    philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
+    return camera_get_ray(cam, u, v, rng);
+}
+
 // The sample loop of renderthread (Raytracing_n.cpp:826-848) and color() (:55-106) for every pixel,
 // as a persistent grid of autonomous warps:
 //
@@ -101,7 +116,7 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
     const int n_pixels = A.nx * A.ny;
     unsigned long long* work_counter = counters + 7;
 
-    Counters cnt = {0, 0, 0, 0, 0, 0, 0};
+    Counters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
     Tally<COUNT> tl{&cnt};
     unsigned long long paths = 0;
 
@@ -156,16 +171,8 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
                 w_cur += min((unsigned)__popc(m), avail);
             }
             if (!alive && has_item && s_next < s_stop) {
-                // float u = float(samplepoints[s][0] + i) / float(nx)   (Raytracing_n.cpp:827-836)
-                int i = pixel % (A.mod_ny ? A.ny : A.nx);
-                int j = A.ny - 1 - (pixel / A.nx);
                 int s = s_next++;
-                double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
-                double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
-                float u = xdiv((float)(sx + (double)i), (float)A.nx);
-                float v = xdiv((float)(sy + (double)j), (float)A.ny);
-                philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-                P.r = camera_get_ray(S.camera, u, v, rng);
+                P.r = start_path(S.camera, A, sobol, pixel, s, rng);
                 P.thr = v3(1.f, 1.f, 1.f);
                 P.L = v3(0.f, 0.f, 0.f);
                 P.depth = 0;

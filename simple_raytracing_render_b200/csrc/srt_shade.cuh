@@ -216,10 +216,12 @@ SRT_DEV float light_pdf_value(const View& W, V3 o, V3 v, Tally<COUNT> tl) {
             V3 c = v3(pr.g.x, pr.g.y, pr.g.z);
             float t;
             if (sphere_hit(c, pr.g.w, q, 0.001f, kFltMax, t)) {
-                V3 co = fm::sub(c, o);
-                float cos_theta_max = sqrtf(1.f - pr.g.w * pr.g.w / fm::dot(co, co));
-                float solid_angle = fm::kTwoPi * (1.f - cos_theta_max);
-                pdf = 1.f / solid_angle;
+                // 1 - cos_theta_max cancels badly for a small or distant sphere: rounded exactly as the
+                // reference rounds it (float up to the product with the double 2 * M_PI), the rest is cheap
+                V3 co = c - o;
+                float cos_theta_max = xsqrt(xsub(1.f, xdiv(xmul(pr.g.w, pr.g.w), dot(co, co))));
+                float solid_angle = (float)(2.0 * kPi * (double)xsub(1.f, cos_theta_max));
+                pdf = xdiv(1.f, solid_angle);
             }
         } else if ((F & F_LIGHT_ENV) && pr.type == SRT_PRIM_ENV_SPHERE) {
             pdf = 1.f;  // env_sphere.h:48-50
@@ -230,16 +232,18 @@ SRT_DEV float light_pdf_value(const View& W, V3 o, V3 v, Tally<COUNT> tl) {
             V3 p0 = v3(p), p1 = v3(p + 3), p2 = v3(p + 6);
             float t, uu, vv;
             if (tri_hit(p0, p1, p2, o, tri_dir(q.r), false, t, uu, vv)) {
-                float w = 1.f - uu - vv;
-                V3 nrm = fm::normalize(fm::madd(v3(n), w, fm::madd(v3(n + 3), uu, fm::scale(v3(n + 6), vv))));
-                V3 v01 = fm::sub(p1, p0), v02 = fm::sub(p2, p0);
-                float l01 = fm::length(v01), l02 = fm::length(v02);
-                float cos102 = fm::dot(v01, v02) / (l01 * l02);
-                float sin102 = sqrtf(1.f - cos102 * cos102);
-                float area = 0.5f * l01 * l02 * sin102;
-                float distance_square = t * t * q.a;
-                float cosine = fabsf(fm::dot(v, nrm)) * rsqrtf(q.a);
-                pdf = distance_square / (cosine * area);
+                // triangle.h:72-84 operation by operation (sin from 1 - cos^2 cancels for thin triangles)
+                float w = xsub(xsub(1.0f, uu), vv);
+                V3 nrm = unit_vector(w * v3(n) + uu * v3(n + 3) + vv * v3(n + 6));  // rec.normal, triangle.h:179-183
+                V3 v01 = p1 - p0, v02 = p2 - p0;
+                float l01 = length(v01), l02 = length(v02);
+                float cos102 = dot(v01 / l01, v02 / l02);
+                float sin102 = xsqrt(xsub(1.f, xmul(cos102, cos102)));
+                float h = xmul(l02, sin102);
+                float area = (float)(0.5 * (double)l01 * (double)h);
+                float distance_square = xmul(xmul(t, t), q.a);
+                float cosine = xdiv(fabsf(dot(v, nrm)), xsqrt(q.a));
+                pdf = xdiv(distance_square, xmul(cosine, area));
             }
         }
         sum = fmaf(weight, pdf, sum);

@@ -178,6 +178,7 @@ struct DScene {
     const double* const* merl;
     int32_t n_entries, n_prims, n_lights, n_media;
     int32_t n_materials, n_textures, n_bvhs, n_ops;
+    unsigned long long* diag;  // [0]: wide-BVH stack overflows since the context was created (SrtCounters)
     uint32_t hot_bytes;  // bytes from `entries` to the end of `lights` (16-byte multiple)
     uint32_t features;   // F_* mask of the scene
     SrtCamera camera;

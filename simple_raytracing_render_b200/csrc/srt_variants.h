@@ -86,12 +86,15 @@ struct WfVariantInfo {
 
 typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
 
-#define SRT_N_WF_VARIANTS 4
+// variant 4 is the COUNTING build of k_wf_sorted (all features, tables in global memory): srt_render_counted
+// replays a launch on it, so that the work counters come from the scheduler that was timed
+#define SRT_N_WF_VARIANTS 5
 #define SRT_WF_VARIANT_MASK(n)                                 \
     ((n) == 0   ? (SRT_VM_LIST | F_SMEM_TABLES)                \
      : (n) == 1 ? (SRT_VM_SPHERES | F_SMEM_TABLES)             \
      : (n) == 2 ? (SRT_VM_MESH)                                \
                 : (SRT_VM_FULL))
+#define SRT_WF_VARIANT_COUNTING(n) ((n) == 4)
 // threads of the one persistent CTA per SM (k_wf_persist / k_wf_sorted).  Measured (profiles/r01_notes.md,
 // capture K): the sphere-BVH variant needs 107 registers and is best at 640 threads (96 registers, 20
 // warps); the mesh and full variants spill there and are best at 512 (128 registers).
@@ -103,6 +106,7 @@ cudaError_t srt_wavefront_variant_0(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_1(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_2(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_3(const WfLaunch&, WfVariantInfo*);
+cudaError_t srt_wavefront_variant_4(const WfLaunch&, WfVariantInfo*);
 
 cudaError_t srt_render_variant_0(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_1(const RenderLaunch&, RenderVariantInfo*);

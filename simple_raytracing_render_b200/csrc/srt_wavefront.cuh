@@ -182,15 +182,8 @@ SRT_DEV bool wf_shade_slot(const DScene& S, const View& W, const RenderArgs& A, 
         }
     }
     if (!alive && has_item && s_next < s_stop) {
-        int i = pixel % (A.mod_ny ? A.ny : A.nx);
-        int j = A.ny - 1 - (pixel / A.nx);
         int s = s_next++;
-        double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
-        double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
-        float u = xdiv((float)(sx + (double)i), (float)A.nx);
-        float v = xdiv((float)(sy + (double)j), (float)A.ny);
-        philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-        P.r = camera_get_ray(S.camera, u, v, rng);
+        P.r = start_path(S.camera, A, sobol, pixel, s, rng);
         P.thr = v3(1.f, 1.f, 1.f);
         P.L = v3(0.f, 0.f, 0.f);
         P.depth = 0;
@@ -365,15 +358,8 @@ SRT_DEV int wf_shade_phase(const DScene& S, const View& W, const RenderArgs& A, 
         }
         if (finishing) {
             if (!alive && has_item && s_next < s_stop) {
-                int i = pixel % (A.mod_ny ? A.ny : A.nx);
-                int j = A.ny - 1 - (pixel / A.nx);
                 int s = s_next++;
-                double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
-                double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
-                float u = xdiv((float)(sx + (double)i), (float)A.nx);
-                float v = xdiv((float)(sy + (double)j), (float)A.ny);
-                philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-                P.r = camera_get_ray(S.camera, u, v, rng);
+                P.r = start_path(S.camera, A, sobol, pixel, s, rng);
                 P.thr = v3(1.f, 1.f, 1.f);
                 P.L = v3(0.f, 0.f, 0.f);
                 P.depth = 0;
@@ -539,7 +525,7 @@ SRT_DEV int wf_hit_class(const View& W, const Hit& h) {
     return SC_DIFFUSE;
 }
 
-template <uint32_t F>
+template <uint32_t F, bool COUNT>
 __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     k_wf_sorted(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
                 unsigned long long* __restrict__ counters, int per_thread) {
@@ -552,7 +538,10 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     const int cap = per_thread * blockDim.x;  // <= kSortCap (srt_api.cu)
     const int cta_base = blockIdx.x * cap;
     unsigned long long* work_counter = counters + 7;
-    Tally<false> tl{nullptr};
+    // COUNT: the instrumented build of THIS kernel (srt_render_counted): same schedule, same paths, plus the
+    // per-thread tallies of SrtCounters (the shipping kernel's own visit / test counters)
+    Counters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
+    Tally<COUNT> tl{&cnt};
     if (threadIdx.x < Q_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
     if (threadIdx.x == 0) {
         Q.exhausted = 0;
@@ -600,15 +589,9 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                         const unsigned long long item = base + (unsigned)pos;
                         const int pixel = (int)(item / (unsigned)A.n_chunks);
                         const int s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
-                        const int i = pixel % (A.mod_ny ? A.ny : A.nx);
-                        const int j = A.ny - 1 - (pixel / A.nx);
-                        const double sx = (double)__ldg(&sobol[2 * s]) * 2.3283064365386963e-10;
-                        const double sy = (double)__ldg(&sobol[2 * s + 1]) * 2.3283064365386963e-10;
-                        const float u = xdiv((float)(sx + (double)i), (float)A.nx);
-                        const float v = xdiv((float)(sy + (double)j), (float)A.ny);
                         Philox rng;
-                        philox_init(rng, A.seed, (uint32_t)pixel, (uint32_t)s);
-                        const Ray r = camera_get_ray(S.camera, u, v, rng);
+                        const Ray r = start_path(S.camera, A, sobol, pixel, s, rng);
+                        if (COUNT) cnt.paths++;
                         st.item[slot] = make_int4(pixel, s, 0, 0);
                         st.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
                         st.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
@@ -656,6 +639,7 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                         int4 it = st.item[slot];
                         wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)it.y, rng);
                     }
+                    if (COUNT) cnt.rays++;
                     Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
                     st.hit[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f);
                     if (F & F_MEDIA) wf_store_rng(st, slot, rng);
@@ -717,6 +701,15 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                 q_push(Q, SC_DEAD, valid && !alive, ls);
             }
         }
+    }
+    if (COUNT) {
+        atomicAdd(&counters[0], cnt.paths);
+        atomicAdd(&counters[1], cnt.rays);
+        atomicAdd(&counters[2], cnt.probe_rays);
+        atomicAdd(&counters[3], cnt.node_visits);
+        atomicAdd(&counters[4], cnt.prim_tests);
+        atomicAdd(&counters[5], cnt.reject_iters);
+        atomicAdd(&counters[6], cnt.culled_rays);
     }
 }
 

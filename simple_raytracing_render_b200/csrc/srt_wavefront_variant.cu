@@ -1,5 +1,6 @@
-// srt_wavefront_variant.cu — one instantiation of the wavefront kernel pair (srt_wavefront.cuh);
-// compiled SRT_N_WF_VARIANTS times with -DSRT_WF_VARIANT=<n> (srt_variants.h).
+// srt_wavefront_variant.cu — one instantiation of the wavefront kernels (srt_wavefront.cuh);
+// compiled SRT_N_WF_VARIANTS times with -DSRT_WF_VARIANT=<n> (srt_variants.h).  The counting variant
+// instantiates the instrumented k_wf_sorted only (stage 3): it is what srt_render_counted replays.
 #ifndef SRT_WF_VARIANT
 #error "compile with -DSRT_WF_VARIANT=<n>"
 #endif
@@ -21,19 +22,26 @@
 
 namespace {
 constexpr uint32_t kMask = SRT_WF_VARIANT_MASK(SRT_WF_VARIANT);
+constexpr bool kCount = SRT_WF_VARIANT_COUNTING(SRT_WF_VARIANT);
 }
 
 cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, WfVariantInfo* info) {
+    auto sorted = srt::k_wf_sorted<kMask, kCount>;
+    cudaError_t e;
+    cudaFuncAttributes fa;
+#if !SRT_WF_VARIANT_COUNTING(SRT_WF_VARIANT)
     auto trace = srt::k_wf_trace<kMask>;
     auto shade = srt::k_wf_shade<kMask>;
     auto persist = srt::k_wf_persist<kMask>;
-    auto sorted = srt::k_wf_sorted<kMask>;
-    cudaError_t e;
+#endif
     if (info) {  // runs before the first launch with a given shared-memory size (srt_api.cu: run_wavefront)
         info->features = kMask;
         // static (k_wf_sorted's queues) + dynamic shared memory may exceed the 48 KB default
-        const void* fns[4] = {(const void*)trace, (const void*)shade, (const void*)persist, (const void*)sorted};
-        for (int i = 0; i < 4; i++) {
+        e = cudaFuncSetAttribute((const void*)sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
+        if (e != cudaSuccess) return e;
+#if !SRT_WF_VARIANT_COUNTING(SRT_WF_VARIANT)
+        const void* fns[3] = {(const void*)trace, (const void*)shade, (const void*)persist};
+        for (int i = 0; i < 3; i++) {
             e = cudaFuncSetAttribute(fns[i], cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
             if (e != cudaSuccess) return e;
         }
@@ -41,7 +49,6 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         if (e != cudaSuccess) return e;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->shade_blocks_per_sm, shade, srt::kWfThreads, L.smem_bytes);
         if (e != cudaSuccess) return e;
-        cudaFuncAttributes fa;
         e = cudaFuncGetAttributes(&fa, trace);
         if (e != cudaSuccess) return e;
         info->trace_registers = fa.numRegs;
@@ -54,6 +61,11 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         e = cudaFuncGetAttributes(&fa, persist);
         if (e != cudaSuccess) return e;
         info->persist_registers = fa.numRegs;
+#else
+        info->trace_blocks_per_sm = info->shade_blocks_per_sm = 1;
+        info->trace_registers = info->shade_registers = info->persist_registers = 0;
+        info->persist_blocks_per_sm = 1;
+#endif
         info->persist_threads = SRT_WFP_THREADS;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->sorted_blocks_per_sm, sorted, SRT_WFP_THREADS, L.smem_bytes);
         if (e != cudaSuccess) return e;
@@ -63,10 +75,13 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         return cudaSuccess;
     }
     const srt::WfState& st = *static_cast<const srt::WfState*>(L.state);
-    if (L.stage == 3)
+    if (L.stage == 3) {
         sorted<<<L.grid, SRT_WFP_THREADS, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters,
                                                                     L.per_thread);
-    else if (L.stage == 2)
+        return cudaGetLastError();
+    }
+#if !SRT_WF_VARIANT_COUNTING(SRT_WF_VARIANT)
+    if (L.stage == 2)
         persist<<<L.grid, SRT_WFP_THREADS, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters,
                                                                      L.per_thread);
     else if (L.stage == 0)
@@ -75,4 +90,7 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         shade<<<L.grid, srt::kWfThreads, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters, L.live,
                                                                    L.pass);
     return cudaGetLastError();
+#else
+    return cudaErrorInvalidValue;  // the counting build exists for the sorted scheduler only
+#endif
 }

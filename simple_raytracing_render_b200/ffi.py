@@ -15,7 +15,7 @@ from typing import List, Optional
 
 import numpy as np
 
-SRT_ABI_VERSION = 1
+SRT_ABI_VERSION = 2
 
 # status codes
 SRT_OK, SRT_E_INVALID, SRT_E_UNSUPPORTED, SRT_E_CUDA, SRT_E_NOMEM, SRT_E_NODEVICE = 0, -1, -2, -3, -4, -5
@@ -97,7 +97,7 @@ class SrtRenderParams(C.Structure):
 class SrtCounters(C.Structure):
     _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("probe_rays", C.c_uint64),
                 ("node_visits", C.c_uint64), ("prim_tests", C.c_uint64), ("reject_iters", C.c_uint64),
-                ("kernel_launches", C.c_uint64), ("culled_rays", C.c_uint64)]
+                ("kernel_launches", C.c_uint64), ("culled_rays", C.c_uint64), ("stack_overflows", C.c_uint64)]
 
     def as_dict(self):
         return {n: int(getattr(self, n)) for n, _ in self._fields_ if not n.startswith("_")}
@@ -108,10 +108,11 @@ class SrtSceneInfo(C.Structure):
                 ("bvh_nodes", C.c_int64), ("bvh_node_bytes", C.c_int64), ("device_bytes", C.c_int64),
                 ("sah_cost", C.c_float), ("build_ms", C.c_float), ("features", C.c_uint32),
                 ("render_variant", C.c_int32), ("render_registers", C.c_int32), ("render_blocks_per_sm", C.c_int32),
-                ("hot_table_bytes", C.c_int64)]
+                ("hot_table_bytes", C.c_int64), ("bvh_max_depth", C.c_int32), ("bvh_builder", C.c_int32),
+                ("upload_ms", C.c_float), ("_pad", C.c_int32)]
 
     def as_dict(self):
-        return {n: getattr(self, n) for n, _ in self._fields_}
+        return {n: getattr(self, n) for n, _ in self._fields_ if not n.startswith("_")}
 
 
 def _arr(a, dt, shape_tail=()):
@@ -342,6 +343,7 @@ _SIGNATURES = {
     "srt_scene_destroy": (C.c_int, [C.c_void_p]),
     "srt_scene_info": (C.c_int, [C.c_void_p, C.POINTER(SrtSceneInfo)]),
     "srt_trace_closest": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "srt_primary_rays": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
     "srt_light_pdf": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "srt_render": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
     "srt_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
@@ -351,6 +353,7 @@ _SIGNATURES = {
     "srt_sobol_points_u32": (C.c_int, [C.c_uint32, C.c_void_p]),
     "srt_merl_lookup": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
     "srt_measure_fp32_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
+    "srt_measure_l2_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "srt_selftest_division": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_int64, C.POINTER(C.c_uint64)]),
 }
 

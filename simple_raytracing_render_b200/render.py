@@ -62,6 +62,12 @@ class Context:
         ffi.check(self.lib, self.lib.srt_measure_fp32_peak(self.h, C.byref(v)))
         return float(v.value)
 
+    def measure_l2_peak(self) -> float:
+        """GB/s of an L2-resident streaming read on this GPU (srt_measure_l2_peak)."""
+        v = C.c_double(0.0)
+        ffi.check(self.lib, self.lib.srt_measure_l2_peak(self.h, C.byref(v)))
+        return float(v.value)
+
     def resolve(self, accum_dev, n_pixels: int, n_samples: int, rgb8_out):
         ffi.check(self.lib, self.lib.srt_resolve(self.h, _ptr(accum_dev), int(n_pixels), int(n_samples), _ptr(rgb8_out)))
 
@@ -128,6 +134,14 @@ class Scene:
         ffi.check(self.lib, self.lib.srt_trace_closest(self.h, rays.ctypes.data, n, ids.ctypes.data, t.ctypes.data,
                                                        rec.ctypes.data if want_rec else None))
         return ids, t, rec
+
+    def primary_rays(self, params: ffi.SrtRenderParams) -> np.ndarray:
+        """The camera rays the render kernels start their paths with: [ny*nx*(s_end-s_begin)][7] in
+        (curpixel, s) order (Raytracing_n.cpp:827-836, camera.h:51-59)."""
+        n = params.nx * params.ny * (params.s_end - params.s_begin)
+        rays = np.zeros((n, 7), np.float32)
+        ffi.check(self.lib, self.lib.srt_primary_rays(self.h, C.byref(params), rays.ctypes.data))
+        return rays
 
     def light_pdf(self, od: np.ndarray) -> np.ndarray:
         od = np.ascontiguousarray(od, np.float32).reshape(-1, 6)

@@ -129,8 +129,13 @@ def perlin_tables():
     set_seed(1)
     ran = np.zeros((256, 3), f32)
     for i in range(256):
-        v = np.array([f32(-1 + 2 * drand48()), f32(-1 + 2 * drand48()), f32(-1 + 2 * drand48())], f32)
-        ran[i] = unit_vector(v)
+        # perlin.h:70 `vec3(-1 + 2 * drand48(), -1 + 2 * drand48(), -1 + 2 * drand48())`: the order of the three
+        # draws is unspecified in C++; g++ (the oracle) and MSVC (the reference's compiler) both evaluate
+        # constructor arguments right to left, so z takes the first draw
+        z = f32(-1 + 2 * drand48())
+        y = f32(-1 + 2 * drand48())
+        x = f32(-1 + 2 * drand48())
+        ran[i] = unit_vector(np.array([x, y, z], f32))
     perms = []
     for _ in range(3):
         p = list(range(256))

@@ -20,8 +20,9 @@ import numpy as np
 
 from . import scene as S
 from .scene import (beckmann, box, brdfmaterial, bvh_node, camera, checker_texture, constant_medium, constant_texture, dielectric,
-                    diffuse_light, flip_normals, hitable_list, image_texture, lambertian, metal, rotate_x, rotate_y,
-                    sphere, teapot_bvh, translate, triangle_soup, vec3, xy_rect, xz_rect, yz_rect)
+                    diffuse_light, env_sphere, flip_normals, hitable_list, image_texture, lambertian, metal, moving_sphere,
+                    noise_texture, orennayar, rotate_x, rotate_y, sphere, teapot_bvh, translate, triangle, triangle_soup,
+                    vec3, xy_rect, xz_rect, yz_rect)
 
 CONFIG_SIZES = {
     "cornell": (512, 512, 16),
@@ -29,6 +30,10 @@ CONFIG_SIZES = {
     "teapot": (1024, 1024, 256),
     "soldier": (1920, 1080, 1024),
     "tessellated": (3840, 2160, 256),
+    # parity-only scenes (no BASELINE.json config): every reference class C1-C5 leave out
+    "final": (500, 500, 64),
+    "zoo": (480, 320, 64),
+    "zoo_env": (480, 320, 64),
 }
 
 
@@ -260,9 +265,195 @@ def tessellated_medium(aspect: float = 16.0 / 9.0, n_side: int = 512, seed: int 
     return world, hlist, cam
 
 
+def synthetic_earth(nx: int = 512, ny: int = 256) -> np.ndarray:
+    """Stand-in for contents/textures/earthmap.jpg (cannot travel to the GPU box): continents of
+    low-frequency noise over an ocean gradient, RGB8."""
+    v, u = np.mgrid[0:ny, 0:nx].astype(np.float64)
+    u, v = u / nx, v / ny
+    h = (np.sin(u * 2 * np.pi * 3.0 + 1.3) * np.cos(v * np.pi * 4.0) + 0.6 * np.sin(u * 2 * np.pi * 7.0 + v * 9.0)
+         + 0.3 * np.cos(u * 2 * np.pi * 13.0 - v * 17.0))
+    land = h > 0.25
+    ocean = np.stack([0.05 + 0.1 * v, 0.2 + 0.2 * v, 0.5 + 0.3 * (1 - v)], -1)
+    ground = np.stack([0.2 + 0.3 * np.clip(h, 0, 1), 0.45 - 0.15 * np.clip(h, 0, 1), 0.12 + 0 * h], -1)
+    img = np.where(land[..., None], ground, ocean)
+    ice = (v < 0.08) | (v > 0.93)
+    img = np.where(ice[..., None], 0.92, img)
+    return np.clip(img * 255.0 + 0.5, 0, 255).astype(np.uint8)
+
+
+def book_final(aspect: float = 1.0, seed: int = 1, nb: int = 20, ns: int = 1000, media: bool = True):
+    """The reference's own `final` scene function (Raytracing_n.cpp:475-533), line by line: a bvh_node of
+    `box` leaves (a generic bvh: every leaf is a hitable_list of six rects), a moving_sphere, glass and
+    fuzzy-metal spheres, two constant_medium volumes (one inside a glass boundary, one around the whole
+    scene), an image-textured and a noise-textured sphere, and a rotated / translated bvh_node of 1000
+    spheres.  earthmap.jpg is replaced by a synthetic RGB8 map (the asset cannot travel)."""
+    S.set_seed(seed)
+    white = lambertian(constant_texture(vec3(0.73, 0.73, 0.73)))
+    ground = lambertian(constant_texture(vec3(0.48, 0.83, 0.53)))
+    boxlist = []
+    f32 = np.float32
+    for i in range(nb):
+        for j in range(nb):
+            w = f32(100)
+            x0 = f32(-1000 + i * w)
+            z0 = f32(-1000 + j * w)
+            y0 = f32(0)
+            x1 = f32(x0 + w)
+            y1 = f32(100 * (S.drand48() + 0.01))
+            z1 = f32(z0 + w)
+            boxlist.append(box(vec3(x0, y0, z0), vec3(x1, y1, z1), ground))
+    lst = [bvh_node(boxlist, len(boxlist), 0, 1)]
+    light = diffuse_light(constant_texture(vec3(7, 7, 7)))
+    lst.append(flip_normals(xz_rect(123, 423, 147, 412, 554, light)))
+    center = vec3(400, 400, 200)
+    lst.append(moving_sphere(center, center + vec3(30, 0, 0), 0, 1, 50,
+                             lambertian(constant_texture(vec3(0.7, 0.3, 0.1)))))
+    lst.append(sphere(vec3(260, 150, 45), 50, dielectric(1.5)))
+    lst.append(sphere(vec3(0, 150, 145), 50, metal(vec3(0.8, 0.8, 0.9), 1.0)))
+    boundary = sphere(vec3(360, 150, 145), 70, dielectric(1.5))
+    lst.append(boundary)
+    if media:  # constant_medium::hit is random: closest-hit parity is checked on the twin without the volumes
+        lst.append(constant_medium(boundary, 0.2, constant_texture(vec3(0.2, 0.4, 0.9))))
+        boundary = sphere(vec3(0, 0, 0), 5000, dielectric(1.5))
+        lst.append(constant_medium(boundary, 0.0001, constant_texture(vec3(1.0, 1.0, 1.0))))
+    emat = lambertian(image_texture(synthetic_earth()))
+    lst.append(sphere(vec3(400, 200, 400), 100, emat))
+    pertext = noise_texture(0.1)
+    lst.append(sphere(vec3(220, 280, 300), 80, lambertian(pertext)))
+    boxlist2 = [sphere(vec3(165 * S.drand48(), 165 * S.drand48(), 165 * S.drand48()), 10, white) for _ in range(ns)]
+    lst.append(translate(rotate_y(bvh_node(boxlist2, ns, 0.0, 1.0), 15), vec3(-100, 270, 395)))
+    world = hitable_list(lst, len(lst))
+    cam = camera(vec3(478, 278, -600), vec3(278, 278, 0), vec3(0, 1, 0), 40.0, aspect, 0.0, 10.0, 0.0, 1.0)
+    hlist = hitable_list([flip_normals(xz_rect(123, 423, 147, 412, 554, None))], 1)
+    return world, hlist, cam
+
+
+def feature_zoo(aspect: float = 1.5, seed: int = 1, media: bool = True):
+    """Parity scene for the reference classes no BASELINE.json config instantiates: orennayar +
+    onrennayar_pdf (material.h:127-149, pdf.h:61-116), moving_sphere alone and inside a generic bvh_node
+    (moving_sphere.h:24-58), noise_texture + perlin (texture.h:35-46, perlin.h:7-58), a sphere and a
+    triangle in the light list (sphere.h:69-86, triangle.h:70-94), triangles inside a hitable_list (they
+    ignore t_max and overwrite nearer hits, triangle.h:117-187), a checker over an image texture, and a
+    constant_medium inside a `box` boundary (constant_medium.h:19-50)."""
+    S.set_seed(seed)
+    noise = lambertian(noise_texture(1.5))
+    oren = orennayar(constant_texture(vec3(0.8, 0.45, 0.3)), 25.0)
+    oren_noise = orennayar(noise_texture(4.0), 60.0)
+    mover = lambertian(constant_texture(vec3(0.2, 0.4, 0.8)))
+    lamp = diffuse_light(constant_texture(vec3(9, 9, 8)))
+    lamp2 = diffuse_light(constant_texture(vec3(6, 7, 9)))
+    chk = lambertian(checker_texture(image_texture(synthetic_albedo(128)), constant_texture(vec3(0.9, 0.9, 0.9))))
+    # triangle light: counter-clockwise seen from below, so that its normal points down (emission is
+    # one-sided, material.h:348-354)
+    t_light = (vec3(-2.5, 4.5, 2.0), vec3(0.5, 4.5, -1.5), vec3(2.5, 4.5, 2.0))
+    s_light = (vec3(3.2, 2.6, -1.0), 0.55)
+    small = []
+    for k in range(24):  # a generic bvh: spheres, moving spheres and boxes as leaves
+        cx, cz = -4.5 + 9.0 * S.drand48(), 1.0 + 3.5 * S.drand48()
+        r = 0.12 + 0.18 * S.drand48()
+        m = [oren, mover, chk, metal(vec3(0.8, 0.8, 0.7), 0.3)][k % 4]
+        if k % 3 == 0:
+            small.append(moving_sphere(vec3(cx, r, cz), vec3(cx, r + 0.4, cz), 0.0, 1.0, r, m))
+        elif k % 3 == 1:
+            small.append(sphere(vec3(cx, r, cz), r, m))
+        else:
+            small.append(box(vec3(cx - r, 0, cz - r), vec3(cx + r, 2 * r, cz + r), m))
+    lst = [
+        triangle(*t_light, lamp),
+        xz_rect(-8, 8, -6, 8, 0, noise),
+        flip_normals(xy_rect(-8, 8, 0, 8, 8, chk)),
+        sphere(vec3(0, 1, 0), 1.0, oren),
+        sphere(vec3(-2.2, 0.8, -1.2), 0.8, oren_noise),
+        moving_sphere(vec3(2.0, 0.6, -1.5), vec3(2.0, 1.2, -1.5), 0.0, 1.0, 0.6, mover),
+        sphere(s_light[0], s_light[1], lamp2),
+        bvh_node(small, len(small), 0.0, 1.0),
+        triangle(vec3(-5, 0.2, 3), vec3(-4, 2.2, 3), vec3(-3, 0.2, 3), oren),  # late in the list: seen through everything
+    ]
+    if media:
+        fog = box(vec3(-1.5, 0.0, -3.5), vec3(1.0, 1.2, -2.5), dielectric(1.5))
+        lst.append(constant_medium(fog, 0.8, constant_texture(vec3(0.9, 0.8, 0.7))))
+    world = hitable_list(lst, len(lst))
+    hlist = hitable_list([sphere(s_light[0], s_light[1], None), triangle(*t_light, None)], 2)
+    cam = camera(vec3(0, 3.0, -10), vec3(0, 1.2, 0), vec3(0, 1, 0), 38.0, aspect, 0.05, 10.0, 0.0, 1.0)
+    return world, hlist, cam
+
+
+def zoo_env(aspect: float = 1.5, seed: int = 1):
+    """Parity scene for env_sphere as a world object and as a light (env_sphere.h:27-50): its hit() ignores
+    (t_min, t_max) and always reports a hit, so it stands FIRST in the world list (anything later that is
+    nearer replaces it); in the light list its pdf_value is 1 whatever the direction, which ends the
+    `while (pdf_val == 0)` loop at once, and its random() points away from the centre (NaN from inside).
+    Also a light-list element without pdf_value / random (an xy_rect: hitable.h:31-32)."""
+    S.set_seed(seed)
+    sky = diffuse_light(image_texture(synthetic_sky(256, 128)))
+    oren = orennayar(constant_texture(vec3(0.7, 0.7, 0.6)), 40.0)
+    lamp = diffuse_light(constant_texture(vec3(12, 12, 12)))
+    lst = [
+        env_sphere(vec3(0, 1, 0), 60.0, sky),
+        xz_rect(-12, 12, -12, 12, 0, oren),
+        sphere(vec3(-1.6, 1, 0), 1.0, metal(vec3(0.9, 0.8, 0.6), 0.05)),
+        sphere(vec3(1.6, 1, 0), 1.0, lambertian(constant_texture(vec3(0.3, 0.6, 0.4)))),
+        flip_normals(xz_rect(-2, 2, -2, 2, 6, lamp)),
+    ]
+    world = hitable_list(lst, len(lst))
+    hlist = hitable_list([flip_normals(xz_rect(-2, 2, -2, 2, 6, None)), env_sphere(vec3(0, 1, 0), 60.0, None),
+                          xy_rect(-1, 1, 0, 2, 5, None)], 3)
+    cam = camera(vec3(0, 2.5, -9), vec3(0, 1, 0), vec3(0, 1, 0), 35.0, aspect, 0.0, 10.0, 0.0, 0.0)
+    return world, hlist, cam
+
+
+def texture_probe(kind: str = "noise", aspect: float = 1.0):
+    """One emissive surface filling the view: every pixel's radiance is texture::value at the primary hit
+    (diffuse_light::emitted, material.h:348-354), so an image compares the texture arithmetic directly —
+    noise_texture + perlin (texture.h:35-46, perlin.h:7-58), checker_texture (texture.h:9-23) and
+    image_texture through rect (aarect.h) and sphere uv (hitable.h:10-15, texture.h:58-70)."""
+    if kind == "noise":
+        tex = noise_texture(2.0)
+    elif kind == "checker":
+        tex = checker_texture(noise_texture(0.7), constant_texture(vec3(0.9, 0.2, 0.1)))
+    elif kind in ("image", "image_sphere"):
+        tex = image_texture(synthetic_albedo(64))
+    else:
+        raise KeyError(kind)
+    lamp = diffuse_light(tex)
+    if kind == "image_sphere":
+        lst = [sphere(vec3(0, 0, 0), 2.0, lamp)]
+        cam = camera(vec3(0, 1.5, -6), vec3(0, 0, 0), vec3(0, 1, 0), 45.0, aspect, 0.0, 10.0, 0.0, 0.0)
+    else:
+        lst = [xz_rect(-5, 5, -5, 5, 0, lamp)]
+        cam = camera(vec3(0.3, 7, -2), vec3(0, 0, 0), vec3(0, 1, 0), 50.0, aspect, 0.0, 10.0, 0.0, 0.0)
+    return hitable_list(lst, len(lst)), hitable_list([], 0), cam
+
+
+def oren_only(aspect: float = 1.0, sigma: float = 45.0):
+    """orennayar + onrennayar_pdf (material.h:127-149, pdf.h:61-116) and nothing else that scatters: a rough
+    floor and a rough sphere under one sampled rect light."""
+    oren = orennayar(constant_texture(vec3(0.75, 0.6, 0.5)), sigma)
+    lamp = diffuse_light(constant_texture(vec3(10, 10, 10)))
+    lst = [xz_rect(-6, 6, -6, 6, 0, oren), sphere(vec3(0, 1, 0), 1.0, oren),
+           flip_normals(xz_rect(-1.5, 1.5, -1.5, 1.5, 5, lamp))]
+    hlist = hitable_list([flip_normals(xz_rect(-1.5, 1.5, -1.5, 1.5, 5, None))], 1)
+    cam = camera(vec3(0, 3, -7), vec3(0, 0.8, 0), vec3(0, 1, 0), 40.0, aspect, 0.0, 10.0, 0.0, 0.0)
+    return hitable_list(lst, len(lst)), hlist, cam
+
+
+def medium_probe(boundary_kind: str = "sphere", density: float = 0.7):
+    """A constant_medium and nothing else (constant_medium.h:19-50): rays either scatter inside it (id =
+    n_prims + 0) or miss.  Boundaries: a sphere, or a `box` (hitable_list of six flipped / unflipped rects)."""
+    glass = dielectric(1.5)
+    if boundary_kind == "sphere":
+        b = sphere(vec3(0, 0, 0), 1.0, glass)
+    else:
+        b = box(vec3(-1.0, -0.6, -0.8), vec3(1.0, 0.6, 0.8), glass)
+    world = hitable_list([constant_medium(b, density, constant_texture(vec3(1, 1, 1)))], 1)
+    cam = camera(vec3(0, 0, -5), vec3(0, 0, 0), vec3(0, 1, 0), 40.0, 1.0, 0.0, 10.0, 0.0, 0.0)
+    return world, hitable_list([], 0), cam
+
+
 def by_name(name: str, **kw):
     fn = {"cornell": cornell_box_classic, "spheres": random_spheres, "teapot": teapot_beckmann,
-          "soldier": soldier_like, "tessellated": tessellated_medium}.get(name)
+          "soldier": soldier_like, "tessellated": tessellated_medium, "final": book_final, "zoo": feature_zoo,
+          "zoo_env": zoo_env}.get(name)
     if fn is None:
         raise KeyError(name)
     nx, ny, _ = CONFIG_SIZES[name]

@@ -39,6 +39,25 @@ def gpu_ctx(backend_lib):
     ctx.close()
 
 
+def record_parity(key, values):
+    """Measured parity figures (relMSE per scene and scheduler, t errors, ray counts ...) are merged into one
+    JSON file next to the test run; the copy of a GPU-box run is committed as profiles/r02_parity.json."""
+    import json
+    path = os.environ.get("SRT_PARITY_JSON", os.path.join(ROOT, "gpurun_out", "parity.json"))
+    try:
+        os.makedirs(os.path.dirname(path), exist_ok=True)
+        try:
+            with open(path) as f:
+                data = json.load(f)
+        except (OSError, ValueError):
+            data = {}
+        data[key] = values
+        with open(path, "w") as f:
+            json.dump(data, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
+
+
 _SCENES, _REF_SCENES = {}, {}
 
 # the sizes the golden vectors were made at (tests/golden/make_golden.py); "<name>:trace" is the variant
@@ -46,6 +65,8 @@ _SCENES, _REF_SCENES = {}, {}
 SCENE_KW = {
     "tessellated": {"n_side": 128},
     "tessellated:trace": {"n_side": 128, "fog": False},
+    "final:trace": {"media": False},
+    "zoo:trace": {"media": False},
 }
 
 

@@ -17,6 +17,7 @@ sys.path.insert(0, ROOT)
 
 sys.path.insert(0, os.path.dirname(HERE))
 from conftest import get_scene, trace_name  # noqa: E402
+from make_golden_rays import medium_rays  # noqa: E402
 from oracle import ref  # noqa: E402
 from simple_raytracing_render_b200 import scenes  # noqa: E402
 
@@ -52,29 +53,75 @@ def merl_kat():
     np.savez_compressed(os.path.join(HERE, "merl.npz"), angles=a, rgb=ref.merl_lookup(m, a))
 
 
-def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny):
+def zero_unset_uv(rs, ids, rec):
+    """moving_sphere::hit never writes rec.u / rec.v (moving_sphere.h:32-48): what the oracle reports there
+    is whatever its stack held.  The vectors carry 0 for those hits."""
+    from simple_raytracing_render_b200 import ffi
+    prims = rs.flat().prims
+    if len(prims) == 0:
+        return
+    moving = np.zeros(len(ids), bool)
+    ok = (ids >= 0) & (ids < len(prims))
+    moving[ok] = prims["type"][ids[ok]] == ffi.PRIM_MOVING_SPHERE
+    rec[moving, 0:2] = 0.0
+
+
+def scene_vectors(name, nx, ny, ns_rays, ns_img, img_nx, img_ny, extended=False):
     world, hlist, cam = get_scene(name)
     rs_img = ref.RefBuilder().realize(world, hlist, cam)
     rs = rs_img if trace_name(name) == name else ref.RefBuilder().realize(*get_scene(trace_name(name)))
     mod_ny = nx == ny
     rays = rs.primary_rays(nx, ny, ns_rays, seed=1, mod_ny=mod_ny)
     ids, t, rec = rs.trace(rays)
+    zero_unset_uv(rs, ids, rec)
     rng = np.random.default_rng(7)
     # secondary-like rays: from hit points towards random directions (un-normalised, as light samples are)
     hit = ids >= 0
     o = rec[hit][:, 2:5][:4096]
     d = rng.normal(size=o.shape).astype(np.float32) * rng.uniform(0.2, 300, size=(len(o), 1)).astype(np.float32)
-    rays2 = np.concatenate([o, d, np.zeros((len(o), 1), np.float32)], 1).astype(np.float32)
+    tm = rng.uniform(0, 1, size=(len(o), 1)) if extended else np.zeros((len(o), 1))  # moving_sphere.h:19-21
+    rays2 = np.concatenate([o, d, tm], 1).astype(np.float32)
     ids2, t2, rec2 = rs.trace(rays2)
+    zero_unset_uv(rs, ids2, rec2)
     od = np.concatenate([o, d], 1).astype(np.float32)
     lp = rs.light_pdf(od)
+    extra = {}
+    if extended:  # directions drawn by the reference's own hitable_list::random: they do reach the light shapes
+        aim = rs.light_random(o, seed=3)
+        extra["light_aim_od"] = np.concatenate([o, aim], 1).astype(np.float32)
+        extra["light_aim_pdf"] = rs.light_pdf(extra["light_aim_od"])
     img, nrays = rs_img.render_float(img_nx, img_ny, ns_img, mod_ny=img_nx == img_ny)
     np.savez_compressed(os.path.join(HERE, f"{name}.npz"), nx=nx, ny=ny, ns_rays=ns_rays,
                         rays=rays, ids=ids, t=t, rec=rec, rays2=rays2, ids2=ids2, t2=t2, rec2=rec2,
                         light_od=od, light_pdf=lp, img=img / ns_img, img_nx=img_nx, img_ny=img_ny, img_ns=ns_img,
-                        img_rays=nrays)
+                        img_rays=nrays, **extra)
     print(name, "hits", int(hit.sum()), "of", len(ids), "img mean", float(img.mean() / ns_img), "rays/path",
           nrays / (img_nx * img_ny * ns_img))
+
+
+def feature_vectors():
+    """tests/golden/features.npz: texture-probe images (every pixel is texture::value at the primary hit),
+    the Oren-Nayar-only scene, and the constant_medium transmittance statistics of the reference."""
+    out = {}
+    for kind in ("noise", "checker", "image", "image_sphere"):
+        rs = ref.RefBuilder().realize(*scenes.texture_probe(kind))
+        img, _ = rs.render_float(64, 64, 4, mod_ny=True)
+        out[f"tex_{kind}"] = img / 4.0
+    rs = ref.RefBuilder().realize(*scenes.oren_only())
+    img, nrays = rs.render_float(32, 32, 8192, mod_ny=True)
+    out["oren_img"], out["oren_ns"], out["oren_rays"] = img / 8192.0, 8192, nrays
+    for kind in ("sphere", "box"):
+        world, hlist, cam = scenes.medium_probe(kind)
+        rs = ref.RefBuilder().realize(world, hlist, cam)
+        rays = medium_rays(kind, 1_000_000, 21)
+        ids, t, _ = rs.trace(rays, seed=5, want_rec=False)
+        sc = ids >= 0
+        out[f"medium_{kind}_scatter_frac"] = float(sc.mean())
+        out[f"medium_{kind}_mean_t"] = float(t[sc].astype(np.float64).mean())
+        out[f"medium_{kind}_mean_t2"] = float((t[sc].astype(np.float64) ** 2).mean())
+        out[f"medium_{kind}_ids"] = np.unique(ids)
+        print("medium", kind, "scatter fraction", sc.mean(), "mean t", t[sc].mean(), "ids", np.unique(ids))
+    np.savez_compressed(os.path.join(HERE, "features.npz"), **out)
 
 
 if __name__ == "__main__":
@@ -82,9 +129,14 @@ if __name__ == "__main__":
     if only == ["merl"]:
         merl_kat()
         sys.exit(0)
+    if only == ["features"]:
+        feature_vectors()
+        sys.exit(0)
     if only:
         cfg = {"cornell": (64, 64, 2, 4096, 48, 48), "spheres": (96, 64, 2, 16384, 48, 32), "teapot": (96, 96, 1, 4096, 40, 40),
-               "soldier": (96, 54, 2, 4096, 48, 27), "tessellated": (96, 54, 2, 4096, 48, 27)}
+               "soldier": (96, 54, 2, 4096, 48, 27), "tessellated": (96, 54, 2, 4096, 48, 27),
+               "final": (96, 96, 2, 4096, 40, 40, True), "zoo": (96, 64, 2, 4096, 48, 32, True),
+               "zoo_env": (96, 64, 2, 4096, 48, 32, True)}
         for name in only:
             scene_vectors(name, *cfg[name])
         sys.exit(0)
@@ -95,3 +147,7 @@ if __name__ == "__main__":
     scene_vectors("teapot", 96, 96, 1, 4096, 40, 40)
     scene_vectors("soldier", 96, 54, 2, 4096, 48, 27)
     scene_vectors("tessellated", 96, 54, 2, 4096, 48, 27)
+    scene_vectors("final", 96, 96, 2, 4096, 40, 40, True)
+    scene_vectors("zoo", 96, 64, 2, 4096, 48, 32, True)
+    scene_vectors("zoo_env", 96, 64, 2, 4096, 48, 32, True)
+    feature_vectors()

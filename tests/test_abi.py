@@ -33,7 +33,8 @@ def test_struct_sizes_match_c_layout():
     # field-for-field mirrors of the C structs (x86-64 SysV)
     assert ffi.PRIM_DT.itemsize == 16 and ffi.ENTRY_DT.itemsize == 24 and ffi.OP_DT.itemsize == 16
     assert ffi.MATERIAL_DT.itemsize == 32 and ffi.TEXTURE_DT.itemsize == 24 and ffi.CAMERA_DT.itemsize == 96
-    assert C.sizeof(ffi.SrtCamera) == 96 and C.sizeof(ffi.SrtRenderParams) == 32 and C.sizeof(ffi.SrtCounters) == 64
+    assert C.sizeof(ffi.SrtCamera) == 96 and C.sizeof(ffi.SrtRenderParams) == 32 and C.sizeof(ffi.SrtCounters) == 72
+    assert C.sizeof(ffi.SrtSceneInfo) == 88
 
 
 def test_no_cpu_fallback_without_gpu(backend_lib):

@@ -12,7 +12,7 @@ import os
 import numpy as np
 import pytest
 
-from conftest import GOLDEN, get_ref_scene, get_scene, trace_name
+from conftest import GOLDEN, get_ref_scene, get_scene, record_parity, trace_name
 from simple_raytracing_render_b200 import ffi, render, scenes, scene as S
 
 pytestmark = pytest.mark.gpu
@@ -27,7 +27,12 @@ def rel_mse(x, r):
     return float(np.mean((x - r) ** 2 / (r ** 2 + 1e-2)))
 
 
-@pytest.fixture(scope="module", params=["cornell", "spheres", "teapot", "soldier", "tessellated"])
+# C1-C5 of BASELINE.json:configs, then the parity-only scenes that instantiate every reference class those
+# leave out (scenes.py: book_final, feature_zoo, zoo_env)
+ALL_SCENES = ["cornell", "spheres", "teapot", "soldier", "tessellated", "final", "zoo", "zoo_env"]
+
+
+@pytest.fixture(scope="module", params=ALL_SCENES)
 def golden_scene(request, gpu_ctx):
     name = request.param
     g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
@@ -60,25 +65,50 @@ def _check_hits(gid, gt, rid, rt):
 def test_primary_hits_match_golden(trace_scene):
     name, g, sc = trace_scene
     gid, gt, grec = sc.trace_closest(g["rays"])
-    _check_hits(gid, gt, g["ids"], g["t"])
+    worst = _check_hits(gid, gt, g["ids"], g["t"])
     # the whole hit_record (u, v, p, normal) of hitable.h:17-25
     hit = g["ids"] >= 0
     assert np.allclose(grec[hit], g["rec"][hit], rtol=1e-5, atol=1e-4)
+    record_parity(f"primary_hits/{name}", {"rays": int(len(gid)), "id_mismatches": 0, "max_rel_t_err": worst,
+                                           "t_bit_equal": float(np.mean(gt[hit] == g["t"][hit])) if hit.any() else 1.0})
+    assert sc.ctx.counters()["stack_overflows"] == 0
 
 
 def test_secondary_hits_match_golden(trace_scene):
-    """Un-normalised directions from surface points (what hitable_pdf samples produce)."""
+    """Un-normalised directions from surface points (what hitable_pdf samples produce); random ray times
+    for the scenes with moving spheres."""
     name, g, sc = trace_scene
-    gid, gt, _ = sc.trace_closest(g["rays2"])
-    _check_hits(gid, gt, g["ids2"], g["t2"])
+    gid, gt, grec = sc.trace_closest(g["rays2"])
+    worst = _check_hits(gid, gt, g["ids2"], g["t2"])
+    hit = g["ids2"] >= 0
+    assert np.allclose(grec[hit], g["rec2"][hit], rtol=1e-5, atol=1e-4)
+    record_parity(f"secondary_hits/{name}", {"rays": int(len(gid)), "id_mismatches": 0, "max_rel_t_err": worst})
+    assert sc.ctx.counters()["stack_overflows"] == 0
+
+
+def _check_light_pdf(got, want):
+    """hitable_list::pdf_value: the zero / NaN pattern (which light shapes the ray reaches) is exact; values
+    within 1e-5 relative (the density arithmetic after the exact hit test)."""
+    assert np.array_equal(np.isnan(got), np.isnan(want))
+    ok = ~np.isnan(want)
+    assert np.array_equal(got[ok] == 0, want[ok] == 0)
+    assert np.allclose(got[ok], want[ok], rtol=1e-5, atol=0)
+    nz = ok & (want != 0)
+    return float(np.max(np.abs(got[nz] - want[nz]) / np.abs(want[nz]))) if nz.any() else 0.0
 
 
 def test_light_pdf_matches_golden(trace_scene):
     name, g, sc = trace_scene
-    got = sc.light_pdf(g["light_od"])
-    want = g["light_pdf"]
-    assert np.array_equal(got == 0, want == 0)
-    assert np.allclose(got, want, rtol=1e-5, atol=0)
+    worst = _check_light_pdf(sc.light_pdf(g["light_od"]), g["light_pdf"])
+    rec = {"random_directions": int(len(g["light_pdf"])), "max_rel_err": worst,
+           "nonzero": int(np.count_nonzero(np.nan_to_num(g["light_pdf"])))}
+    if "light_aim_od" in g.files:
+        # directions drawn by the reference's own hitable_list::random (sphere.h:80-86, triangle.h:89-94,
+        # env_sphere.h:40-46, aarect.h:57-60): they reach the shapes, so every density formula is exercised
+        worst = _check_light_pdf(sc.light_pdf(g["light_aim_od"]), g["light_aim_pdf"])
+        rec.update({"aimed_directions": int(len(g["light_aim_pdf"])), "aimed_max_rel_err": worst,
+                    "aimed_nonzero": int(np.count_nonzero(np.nan_to_num(g["light_aim_pdf"])))})
+    record_parity(f"light_pdf/{name}", rec)
 
 
 def test_device_pointers_are_accepted(trace_scene):
@@ -123,6 +153,11 @@ def test_converged_image_relmse_vs_golden(golden_scene, scheduler, monkeypatch):
     xm, rm = x.reshape(-1)[keep].mean(), r.reshape(-1)[keep].mean()
     print(f"{name}: relMSE {err:.3e} (untrimmed {err_all:.3e}; gpu {ns} spp vs reference {ns_ref} spp), "
           f"means {xm:.4f} / {rm:.4f}")
+    record_parity(f"image_relmse/{name}/{scheduler}",
+                  {"relmse": err, "relmse_untrimmed": err_all, "trim": TRIM.get(name, 0.0), "nx": nx, "ny": ny,
+                   "gpu_spp": ns, "reference_spp": ns_ref, "gpu_mean": float(xm), "reference_mean": float(rm),
+                   "kernel_variant": int(sc.info()["render_variant"])})
+    assert sc.ctx.counters()["stack_overflows"] == 0
     assert abs(xm - rm) <= 0.02 * rm
     assert err <= RELMSE_TOL
 
@@ -169,7 +204,10 @@ def test_resolve_matches_reference_quantisation(gpu_ctx):
     assert np.array_equal(out, want)
 
 
-def test_counters_are_consistent(golden_scene):
+def test_counters_are_consistent(golden_scene, monkeypatch):
+    """srt_render_counted replays a launch on the instrumented build of the scheduler the plain call runs:
+    k_render for small frames, k_wf_sorted (the kernel bench.py times) when the sorted wavefront is
+    selected.  Both walk the same paths (same Philox counters), so their tallies agree."""
     import torch
     name, g, sc = golden_scene
     nx, ny, ns = 64, 64, 8
@@ -177,6 +215,7 @@ def test_counters_are_consistent(golden_scene):
     c = sc.render_counted(render.render_params(nx, ny, ns), buf)
     assert c["paths"] == nx * ny * ns
     assert c["rays"] >= c["paths"] and c["prim_tests"] > 0
+    assert c["stack_overflows"] == 0
     # the reference's own rays/path for this scene (golden img_rays) within a few percent
     ref_rpp = float(g["img_rays"]) / (int(g["img_nx"]) * int(g["img_ny"]) * int(g["img_ns"]))
     # The backend stops a path whose throughput is exactly zero (it cannot change the sample); the
@@ -184,6 +223,16 @@ def test_counters_are_consistent(golden_scene):
     # rays + culled is a lower bound of the reference's count and not far below it.
     got = (c["rays"] + c["culled_rays"]) / c["paths"]
     assert 0.85 * ref_rpp <= got <= 1.02 * ref_rpp
+    monkeypatch.setenv("SRT_WAVEFRONT", "3")
+    buf2 = torch.zeros_like(buf)
+    w = sc.render_counted(render.render_params(nx, ny, ns), buf2)
+    assert w["paths"] == c["paths"]
+    for k in ("rays", "culled_rays", "probe_rays", "node_visits", "prim_tests", "reject_iters"):
+        assert abs(w[k] - c[k]) <= 0.01 * max(c[k], 100), (k, w[k], c[k])
+    a, b = buf.cpu().numpy(), buf2.cpu().numpy()
+    assert np.isclose(a, b, rtol=1e-3, atol=1e-4).mean() >= 0.995
+    record_parity(f"counters/{name}", {"fused": c, "sorted_wavefront": w, "reference_rays_per_path": ref_rpp,
+                                       "gpu_rays_plus_culled_per_path": got})
 
 
 # ---- live oracle (oracle/_ref/libsrt_ref.so travelled with the snapshot) ---------------------------

@@ -83,7 +83,7 @@ def test_golden_scene_vectors_match_live_reference(oracle):
     """The committed closest-hit vectors are what the reference computes today."""
     from simple_raytracing_render_b200 import scenes
     from conftest import get_ref_scene, trace_name
-    for name in ("cornell", "spheres", "teapot", "soldier", "tessellated"):
+    for name in ("cornell", "spheres", "teapot", "soldier", "tessellated", "final", "zoo", "zoo_env"):
         g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
         rs = get_ref_scene(oracle, trace_name(name))
         n = 2000
@@ -91,7 +91,29 @@ def test_golden_scene_vectors_match_live_reference(oracle):
         assert np.array_equal(ids, g["ids"][:n])
         assert np.array_equal(t, g["t"][:n])
         lp = rs.light_pdf(g["light_od"][:n])
-        assert np.array_equal(lp, g["light_pdf"][:n])
+        assert np.array_equal(lp, g["light_pdf"][:n], equal_nan=True)
+        if "light_aim_od" in g.files:
+            lp = rs.light_pdf(g["light_aim_od"][:n])
+            assert np.array_equal(lp, g["light_aim_pdf"][:n], equal_nan=True)
+            assert np.array_equal(rs.light_random(g["light_aim_od"][:n, :3], seed=3), g["light_aim_od"][:n, 3:],
+                                  equal_nan=True)
+
+
+def test_feature_vectors_match_live_reference(oracle):
+    """tests/golden/features.npz: the texture-probe images and the constant_medium statistics are what the
+    reference computes today."""
+    import sys
+    sys.path.insert(0, GOLDEN)
+    from make_golden_rays import medium_rays
+    from simple_raytracing_render_b200 import scenes
+    f = np.load(os.path.join(GOLDEN, "features.npz"))
+    for kind in ("noise", "image_sphere"):
+        img, _ = oracle.RefBuilder().realize(*scenes.texture_probe(kind)).render_float(64, 64, 4, mod_ny=True)
+        assert np.array_equal(img / 4.0, f[f"tex_{kind}"])
+    rs = oracle.RefBuilder().realize(*scenes.medium_probe("sphere"))
+    ids, t, _ = rs.trace(medium_rays("sphere", 1_000_000, 21)[:100_000], seed=5, want_rec=False)
+    # the first 100 k rays of the same drand48 stream: the same scatter decisions as the golden run's prefix
+    assert abs((ids >= 0).mean() - float(f["medium_sphere_scatter_frac"])) < 0.01
 
 
 def test_uninitialised_beckmann_pdf_reads_about_zero_in_this_process(oracle):
