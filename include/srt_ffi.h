@@ -376,6 +376,13 @@ int srt_measure_l2_peak(SrtContext* ctx, double* gbps);
  * x / 2^32.  out: [n][2]. */
 int srt_sobol_points_u32(uint32_t n, uint32_t* out);
 
+/* Host-side helper (no device work) for the flatteners: the in-order leaf sequence of the reference's
+ * `new bvh_node(l, n, t0, t1)` (bvh.h:96-119) over n items whose bounding-box minima are mins[n][3] — random
+ * axis from the global drand48 stream (mathf.h:12-19; *seed is its state on entry and on return), qsort with
+ * the never-equal comparators (bvh.h:21-55), median split.  order_out[k] = input index of the k-th leaf: the
+ * order in which SrtSceneDesc.bvh_items must list them.  Multi-threaded (10 M items: a few seconds). */
+int srt_ref_bvh_leaf_order(const float* mins, int64_t n, uint64_t* seed, int32_t* order_out);
+
 #ifdef __cplusplus
 }
 #endif

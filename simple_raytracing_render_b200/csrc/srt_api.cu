@@ -939,6 +939,16 @@ int srt_measure_l2_peak(SrtContext* c, double* gbps) {
     return 0;
 }
 
+int srt_ref_bvh_leaf_order(const float* mins, int64_t n, uint64_t* seed, int32_t* order_out) {
+    if (n < 0 || n > 0x7fffffffLL) return fail(SRT_E_INVALID, "bad item count");
+    if (n > 0 && (!mins || !order_out)) return fail(SRT_E_INVALID, "null argument");
+    if (!seed) return fail(SRT_E_INVALID, "seed is null");
+    unsigned long long s = *seed;
+    ref_bvh_leaf_order(mins, (long long)n, &s, order_out);
+    *seed = s;
+    return 0;
+}
+
 int srt_sobol_points_u32(uint32_t N, uint32_t* out) {
     // Raytracing_n.cpp:721-812 with D = 2: gray-code order, dimension 1 all m = 1, dimension 2 from
     // line 2 of new-joe-kuo-6.21201 ("2 1 0 1": s = 1, a = 0, m1 = 1).

@@ -395,3 +395,74 @@ void build_ref_tree(const float* item_boxes, int n, std::vector<RefNode>& out) {
     out.reserve((size_t)n);
     ref_build(item_boxes, 0, n, out);
 }
+
+// ---- reference bvh_node order replay (bvh.h:96-119) ----------------------------------------------------------
+namespace {
+struct RefOrder {
+    const float* mins;
+    int32_t* order;
+    std::vector<uint8_t> axis;  // per node, depth-first numbering
+    std::atomic<int> live{0};
+    int max_tasks;
+
+    static long long node_count(long long n) {  // nodes of the subtree over n leaves
+        if (n <= 2) return 1;
+        return 1 + node_count(n / 2) + node_count(n - n / 2);
+    }
+
+    void sort_slice(long long lo, long long n, int ax, std::vector<std::pair<float, int32_t>>& tmp) {
+        tmp.resize((size_t)n);
+        for (long long i = 0; i < n; i++) tmp[(size_t)i] = {mins[3 * (size_t)order[lo + i] + ax], (int32_t)i};
+        // ascending keys, equal keys in reverse input order (the never-equal comparator under glibc's merge sort)
+        std::sort(tmp.begin(), tmp.end(), [](const std::pair<float, int32_t>& a, const std::pair<float, int32_t>& b) {
+            if (a.first < b.first) return true;
+            if (b.first < a.first) return false;
+            return a.second > b.second;
+        });
+        std::vector<int32_t> moved((size_t)n);
+        for (long long i = 0; i < n; i++) moved[(size_t)i] = order[lo + tmp[(size_t)i].second];
+        std::memcpy(order + lo, moved.data(), sizeof(int32_t) * (size_t)n);
+    }
+
+    void build(long long lo, long long n, long long node) {
+        std::vector<std::pair<float, int32_t>> tmp;
+        build_rec(lo, n, node, tmp);
+    }
+
+    void build_rec(long long lo, long long n, long long node, std::vector<std::pair<float, int32_t>>& tmp) {
+        sort_slice(lo, n, axis[(size_t)node], tmp);
+        if (n <= 2) return;
+        const long long nl = n / 2, nr = n - nl;
+        const long long left_node = node + 1, right_node = node + 1 + node_count(nl);
+        if (n > (1 << 15) && live.load() < max_tasks) {
+            live.fetch_add(1);
+            auto fut = std::async(std::launch::async, [=] { build(lo, nl, left_node); });
+            build_rec(lo + nl, nr, right_node, tmp);
+            fut.get();
+            live.fetch_sub(1);
+        } else {
+            build_rec(lo, nl, left_node, tmp);
+            build_rec(lo + nl, nr, right_node, tmp);
+        }
+    }
+};
+}  // namespace
+
+void ref_bvh_leaf_order(const float* mins, long long n, unsigned long long* seed, int32_t* order_out) {
+    for (long long i = 0; i < n; i++) order_out[i] = (int32_t)i;
+    if (n <= 0) return;
+    RefOrder R;
+    R.mins = mins;
+    R.order = order_out;
+    R.max_tasks = (int)std::max(1u, std::thread::hardware_concurrency());
+    const long long nodes = RefOrder::node_count(n);
+    R.axis.resize((size_t)nodes);
+    unsigned long long s = *seed & 0xFFFFFFFFFFFFull;
+    for (long long k = 0; k < nodes; k++) {  // mathf.h:14-19; the constructor draws before it recurses
+        s = (0x5DEECE66Dull * s + 0xB16ull) & 0xFFFFFFFFFFFFull;  // __a, __c of mathf.h:6-8
+        const double r = (double)(s >> 16) / 4294967296.0;
+        R.axis[(size_t)k] = (uint8_t)(int)(3 * r);
+    }
+    *seed = s;
+    R.build(0, n, 0);
+}

@@ -30,4 +30,12 @@ void build_wide_bvh(const float* boxes, int n, WideBvh& out);
 // out[0] is the root; child indices are relative to out[0].
 void build_ref_tree(const float* item_boxes, int n, std::vector<RefNode>& out);
 
+// The in-order leaf sequence of the reference's `new bvh_node(l, n, t0, t1)` (bvh.h:96-119): at every node, in
+// depth-first order, axis = int(3 * drand48()) from the global 48-bit LCG (mathf.h:12-19), qsort of the node's
+// slice by box minimum on that axis with a comparator that never returns 0 (bvh.h:21-55; glibc's merge sort
+// then leaves equal keys in REVERSE input order), split at n / 2.  mins: [n][3]; order_out[k] = input index of
+// the k-th leaf; *seed is the LCG state on entry and on return (one draw per node).  Multi-threaded: the axis
+// of every node is fixed by the tree shape alone, so the draws are made up front and the sorts run as tasks.
+void ref_bvh_leaf_order(const float* mins, long long n, unsigned long long* seed, int32_t* order_out);
+
 #endif

@@ -437,6 +437,16 @@ def _ref_sorted_order(keys: np.ndarray) -> np.ndarray:
 def _ref_bvh_leaf_order(mins: np.ndarray) -> np.ndarray:
     """In-order leaf sequence of `new bvh_node(l, n, t0, t1)` (bvh.h:96-119): at every node draw
     axis = int(3*drand48()), qsort the node's slice by box-min on that axis, split at n/2."""
+    if len(mins) >= 4096:
+        # large meshes: the same replay in the backend's host code (srt_ref_bvh_leaf_order, multi-threaded);
+        # tests/test_flatten.py checks both forms against the live reference
+        lib = ffi.load_backend()
+        m = np.ascontiguousarray(mins, f32)
+        out = np.empty(len(m), np.int32)
+        sd = ctypes.c_uint64(get_seed())
+        ffi.check(lib, lib.srt_ref_bvh_leaf_order(m.ctypes.data, len(m), ctypes.byref(sd), out.ctypes.data))
+        set_seed(int(sd.value))
+        return out.astype(np.int64)
     order = np.arange(len(mins), dtype=np.int64)
 
     def build(lo: int, n: int):

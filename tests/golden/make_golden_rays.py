@@ -16,3 +16,13 @@ def medium_rays(kind, n, seed):
     d = target - o
     d *= rng.uniform(0.2, 3.0, size=(n, 1)) / np.linalg.norm(d, axis=1, keepdims=True)
     return np.concatenate([o, d, np.zeros((n, 1))], 1).astype(np.float32)
+
+
+def tess10m_random_rays(n=100_000, seed=9):
+    """Random rays inside the bounds of the 10 M-triangle C5 scene (scenes.tessellated_medium, n_side = 2237):
+    un-normalised directions, a fiftieth of them parallel to the ground plane."""
+    rng = np.random.default_rng(seed)
+    o = rng.uniform([0, 0, 0], [555, 180, 555], size=(n, 3))
+    d = rng.standard_normal((n, 3)) * rng.uniform(0.1, 50, size=(n, 1))
+    d[: n // 50, 1] = 0.0
+    return np.concatenate([o, d, np.zeros((n, 1))], 1).astype(np.float32)
