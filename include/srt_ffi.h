@@ -334,6 +334,19 @@ int srt_render(SrtScene* scene, const SrtRenderParams* params, float* accum_rgb_
 int srt_resolve(SrtContext* ctx, const float* accum_rgb_device, int64_t n_pixels, int32_t n_samples,
                 uint8_t* rgb8_out);
 
+/* The sharded form of srt_render + srt_resolve.  srt_render_fixed ADDS the radiance
+ * sums of Sobol indices [s_begin, s_end) into fixed_device, a DEVICE buffer of nx*ny*3 int64 holding sums in
+ * fixed point with 31 fractional bits (the representation the render kernels accumulate in: integer addition
+ * is associative, so a pixel's sum does not depend on the order in which paths finish — nor on how the
+ * sample range was split over GPUs: buffers of different shards add with an exact integer reduce, e.g.
+ * ncclReduce(ncclInt64, ncclSum), and the image is bit-identical for any number of GPUs).
+ * srt_resolve_fixed: mean -> sqrt -> int(255.99 c) -> clamp (Raytracing_n.cpp:848-862) of such a buffer
+ * holding n_samples per pixel; rgb8_out: host or device pointer, or NULL; accum_out_device (optional):
+ * the float sums srt_render would have produced; clear != 0 zeroes the buffer for the next frame. */
+int srt_render_fixed(SrtScene* scene, const SrtRenderParams* params, int64_t* fixed_device);
+int srt_resolve_fixed(SrtContext* ctx, int64_t* fixed_device, int64_t n_pixels, int32_t n_samples, uint8_t* rgb8_out,
+                      float* accum_out_device, int clear);
+
 /* Whole-image convenience with HOST buffers: zero an internal accumulation buffer, srt_render
  * over [s_begin, s_end), srt_resolve, copy back.  rgb8_host: nx*ny*3 bytes; accum_host (optional,
  * may be NULL): nx*ny*3 floats of linear radiance sums.

@@ -1207,7 +1207,10 @@ bool auto_wavefront(const SrtScene* s, const SrtRenderParams* p) {
     return s->dev.n_bvhs > 0 && paths >= (1LL << 20);
 }
 
-int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool counting) {
+// accum != null: the radiance sums are ADDED to the caller's float buffer (through the context's fixed-point
+// buffer and k_fixed_to_accum).  fixed_out != null: the kernels add their 2^-31 fixed-point sums straight
+// into the caller's int64 buffer and nothing else is launched.
+int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool counting, long long* fixed_out = nullptr) {
     SrtContext* c = s->ctx;
     int count = p->s_end - p->s_begin;
     if (count == 0) return 0;
@@ -1283,7 +1286,8 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     A.chunk = chunk;
     A.n_chunks = n_chunks;
     A.n_items = (unsigned long long)n_pixels * (unsigned long long)n_chunks;
-    A.fx_clamp = 4.0e9f / (float)count;
+    // per-sample clamp such that a whole pixel (all ns samples, over every shard) stays inside int64
+    A.fx_clamp = 4.0e9f / (float)std::max(count, p->ns);
     A.regen_threshold = std::max(1, std::min(32, env_int("SRT_REGEN", 8)));
     A.grab = std::max(32, env_int("SRT_GRAB", 128));
     A.cta_sync = std::max(0, std::min(2, env_int("SRT_CTA_SYNC", 0)));
@@ -1292,7 +1296,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
 
     // the kernels accumulate into the context's fixed-point buffer; k_fixed_to_accum adds it to the
     // caller's float buffer and leaves it zero for the next render
-    {
+    if (!fixed_out) {
         size_t need = sizeof(long long) * 3 * (size_t)n_pixels;
         if (c->fixed_cap < need) {
             CUDA_TRY(cudaStreamSynchronize(c->stream));
@@ -1306,8 +1310,9 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
         if (c->fixed_dirty) CUDA_TRY(cudaMemsetAsync(c->d_fixed, 0, c->fixed_cap, c->stream));
         c->fixed_dirty = true;
     }
-    long long* out = c->d_fixed;
+    long long* out = fixed_out ? fixed_out : c->d_fixed;
     auto finish = [&]() -> int {
+        if (fixed_out) return 0;
         long long nv = 3 * n_pixels;
         srt::k_fixed_to_accum<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(c->d_fixed, nv, accum);
         c->launches++;
@@ -1343,6 +1348,45 @@ int srt_render(SrtScene* s, const SrtRenderParams* p, float* accum_rgb_device) {
     if (rc) return rc;
     CUDA_TRY(cudaSetDevice(s->ctx->device));
     return launch_render(s, p, accum_rgb_device, false);
+}
+
+int srt_render_fixed(SrtScene* s, const SrtRenderParams* p, int64_t* fixed_device) {
+    if (!s || !fixed_device) return fail(SRT_E_INVALID, "null argument");
+    int rc = check_params(p);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(s->ctx->device));
+    static_assert(sizeof(long long) == sizeof(int64_t), "int64_t is long long on this ABI");
+    return launch_render(s, p, nullptr, false, reinterpret_cast<long long*>(fixed_device));
+}
+
+int srt_resolve_fixed(SrtContext* c, int64_t* fixed_device, int64_t n_pixels, int32_t n_samples, uint8_t* rgb8_out,
+                      float* accum_out_device, int clear) {
+    if (!c || !fixed_device) return fail(SRT_E_INVALID, "null argument");
+    if (n_pixels <= 0) return 0;
+    CUDA_TRY(cudaSetDevice(c->device));
+    size_t nv = 3 * (size_t)n_pixels;
+    bool dev_out = rgb8_out == nullptr || is_device_pointer(rgb8_out);
+    uint8_t* dst = rgb8_out;
+    if (!dev_out) {
+        if (c->rgb8_cap < nv) {
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_rgb8);
+            c->d_rgb8 = nullptr;
+            c->rgb8_cap = 0;
+            CUDA_TRY(cudaMalloc(&c->d_rgb8, nv));
+            c->rgb8_cap = nv;
+        }
+        dst = c->d_rgb8;
+    }
+    srt::k_resolve_fixed<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(
+        reinterpret_cast<long long*>(fixed_device), (long long)nv, (float)n_samples, dst, accum_out_device, clear);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    if (!dev_out) {
+        CUDA_TRY(cudaMemcpyAsync(rgb8_out, dst, nv, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    return 0;
 }
 
 int srt_primary_rays(SrtScene* s, const SrtRenderParams* p, float* rays_out) {
@@ -1443,19 +1487,45 @@ int srt_render_image(SrtScene* s, const SrtRenderParams* p, uint8_t* rgb8_host, 
     SrtContext* c = s->ctx;
     CUDA_TRY(cudaSetDevice(c->device));
     size_t nv = 3 * (size_t)p->nx * p->ny;
-    if (c->accum_cap < nv) {
-        CUDA_TRY(cudaStreamSynchronize(c->stream));
-        cudaFree(c->d_accum);
-        c->d_accum = nullptr;
-        c->accum_cap = 0;
-        CUDA_TRY(cudaMalloc(&c->d_accum, sizeof(float) * nv));
-        c->accum_cap = nv;
+    // the kernels add into the context's fixed-point buffer (zero between renders); ONE more kernel turns it
+    // into the 8-bit image (and the float sums when asked for) and clears it again
+    {
+        size_t need = sizeof(long long) * nv;
+        if (c->fixed_cap < need) {
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_fixed);
+            c->d_fixed = nullptr;
+            c->fixed_cap = 0;
+            CUDA_TRY(cudaMalloc(&c->d_fixed, need));
+            c->fixed_cap = need;
+            c->fixed_dirty = true;
+        }
+        if (c->fixed_dirty) CUDA_TRY(cudaMemsetAsync(c->d_fixed, 0, c->fixed_cap, c->stream));
+        c->fixed_dirty = true;
     }
-    CUDA_TRY(cudaMemsetAsync(c->d_accum, 0, sizeof(float) * nv, c->stream));
-    rc = launch_render(s, p, c->d_accum, false);
+    float* d_acc = nullptr;
+    if (accum_host) {
+        if (c->accum_cap < nv) {
+            CUDA_TRY(cudaStreamSynchronize(c->stream));
+            cudaFree(c->d_accum);
+            c->d_accum = nullptr;
+            c->accum_cap = 0;
+            CUDA_TRY(cudaMalloc(&c->d_accum, sizeof(float) * nv));
+            c->accum_cap = nv;
+        }
+        d_acc = c->d_accum;
+    }
+    rc = launch_render(s, p, nullptr, false, c->d_fixed);
     if (rc) return rc;
-    if (accum_host) CUDA_TRY(cudaMemcpyAsync(accum_host, c->d_accum, sizeof(float) * nv, cudaMemcpyDeviceToHost, c->stream));
-    return srt_resolve(c, c->d_accum, (int64_t)p->nx * p->ny, p->s_end - p->s_begin, rgb8_host);
+    rc = srt_resolve_fixed(c, reinterpret_cast<int64_t*>(c->d_fixed), (int64_t)p->nx * p->ny, p->s_end - p->s_begin,
+                           rgb8_host, d_acc, 1);
+    if (rc) return rc;
+    c->fixed_dirty = false;
+    if (accum_host) {
+        CUDA_TRY(cudaMemcpyAsync(accum_host, c->d_accum, sizeof(float) * nv, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+    }
+    return 0;
 }
 
 }  // extern "C"

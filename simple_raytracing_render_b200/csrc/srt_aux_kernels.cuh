@@ -102,6 +102,27 @@ __global__ void __launch_bounds__(256) k_resolve(const float* __restrict__ accum
     out[i] = (uint8_t)v;
 }
 
+// The fixed-point sums of a whole render (all shards already added) straight to the 8-bit image: the two
+// kernels above in one pass, same float operations in the same order (the float sum a caller of srt_render
+// would hold is (float)(fixed * 2^-31) added to 0), so the bytes equal those of srt_render + srt_resolve.
+// accum_out (optional) receives that float sum; clear != 0 leaves the buffer zero for the next render.
+__global__ void __launch_bounds__(256) k_resolve_fixed(long long* __restrict__ fixed, long long n_values, float ns,
+                                                       uint8_t* __restrict__ out, float* __restrict__ accum_out, int clear) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n_values) return;
+    float sum = (float)((double)fixed[i] * 4.656612873077392578125e-10);
+    if (clear) fixed[i] = 0;
+    if (accum_out) accum_out[i] = sum;
+    if (out) {
+        float k = (float)(1.0 / (double)ns);
+        float c = xsqrt(xmul(sum, k));
+        int v = (int)(255.99 * (double)c);
+        v = v > 255 ? 255 : v;
+        v = v < 0 ? 0 : v;
+        out[i] = (uint8_t)v;
+    }
+}
+
 __global__ void k_merl_lookup(const double* __restrict__ table, const double* __restrict__ angles, long long n,
                               double* __restrict__ rgb) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

@@ -346,6 +346,8 @@ _SIGNATURES = {
     "srt_primary_rays": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
     "srt_light_pdf": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p]),
     "srt_render": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
+    "srt_render_fixed": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
+    "srt_resolve_fixed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int]),
     "srt_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "srt_render_image": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p, C.c_void_p]),
     "srt_render_counted": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p, C.POINTER(SrtCounters)]),

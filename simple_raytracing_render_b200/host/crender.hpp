@@ -157,7 +157,13 @@ inline void CRender::Run() {
         status() = rc;
         error_text() = b.last_error();
         std::cerr << "CRender::Run: " << backend_error() << "\n";
-    } else if (filePath) {
+    } else {
+        // the render is complete whether or not a file was asked for: a host that polls isfinished /
+        // finishedPixel as the reference's progress display does (Raytracing_n.cpp:819-825) must see it
+        finishedPixel = nx * ny;
+        isfinished = true;
+    }
+    if (rc == 0 && filePath) {
         outfile.open(filePath, std::ios_base::out);
         outfile << "P3\n" << nx << " " << ny << "\n255\n";  // Raytracing_n.cpp:886
         std::string text;
@@ -169,8 +175,6 @@ inline void CRender::Run() {
         }
         outfile << text;
         outfile.close();
-        finishedPixel = nx * ny;
-        isfinished = true;
     }
     if (scene) b.scene_destroy(scene);
     if (ctx) b.context_destroy(ctx);

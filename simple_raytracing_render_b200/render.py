@@ -71,6 +71,11 @@ class Context:
     def resolve(self, accum_dev, n_pixels: int, n_samples: int, rgb8_out):
         ffi.check(self.lib, self.lib.srt_resolve(self.h, _ptr(accum_dev), int(n_pixels), int(n_samples), _ptr(rgb8_out)))
 
+    def resolve_fixed(self, fixed_dev, n_pixels: int, n_samples: int, rgb8_out=None, accum_out_dev=None, clear=True):
+        """int64 fixed-point sums (srt_render_fixed, all shards added) -> 8-bit image (srt_resolve_fixed)."""
+        ffi.check(self.lib, self.lib.srt_resolve_fixed(self.h, _ptr(fixed_dev), int(n_pixels), int(n_samples),
+                                                       _ptr(rgb8_out), _ptr(accum_out_dev), 1 if clear else 0))
+
     def close(self):
         if self.h:
             self.lib.srt_context_destroy(self.h)
@@ -158,6 +163,11 @@ class Scene:
     def render(self, params: ffi.SrtRenderParams, accum_dev):
         """ADD the radiance sums of Sobol indices [s_begin, s_end) into a DEVICE buffer (async)."""
         ffi.check(self.lib, self.lib.srt_render(self.h, C.byref(params), _ptr(accum_dev)))
+
+    def render_fixed(self, params: ffi.SrtRenderParams, fixed_dev):
+        """ADD the 2^-31 fixed-point radiance sums of Sobol indices [s_begin, s_end) into a DEVICE int64
+        buffer (async): the shard form, reduced across GPUs with an exact integer sum."""
+        ffi.check(self.lib, self.lib.srt_render_fixed(self.h, C.byref(params), _ptr(fixed_dev)))
 
     def render_counted(self, params: ffi.SrtRenderParams, accum_dev) -> dict:
         c = ffi.SrtCounters()

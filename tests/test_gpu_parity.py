@@ -187,6 +187,33 @@ def test_render_is_deterministic_and_shards_add_up(golden_scene, scheduler, monk
     assert np.isfinite(whole).all() and whole.mean() > 0
 
 
+def test_fixed_point_shards_are_bit_identical(golden_scene):
+    """srt_render_fixed / srt_resolve_fixed (the multi-GPU form): the int64 sums of disjoint
+    sample ranges add up to the unsharded buffer EXACTLY (integer addition), and resolving them gives the very
+    bytes srt_render_image produces."""
+    import torch
+    name, g, sc = golden_scene
+    nx, ny, ns = 96, 64, 32
+
+    def run(ranges):
+        buf = torch.zeros(nx * ny * 3, dtype=torch.int64, device="cuda")
+        for a, b in ranges:
+            sc.render_fixed(render.render_params(nx, ny, ns, a, b), buf)
+        sc.ctx.synchronize()
+        return buf
+
+    whole = run([(0, ns)])
+    parts = run([(0, 5), (5, 16), (16, 32)])
+    assert torch.equal(whole, parts)
+    rgb = np.zeros((nx * ny, 3), np.uint8)
+    acc = torch.zeros(nx * ny * 3, dtype=torch.float32, device="cuda")
+    sc.ctx.resolve_fixed(parts, nx * ny, ns, rgb, acc, clear=True)
+    assert int(parts.abs().max()) == 0  # cleared for the next frame
+    want_rgb, want_acc = sc.render_image(render.render_params(nx, ny, ns), want_accum=True)
+    assert np.array_equal(rgb, want_rgb)
+    assert np.array_equal(acc.cpu().numpy().reshape(-1, 3), want_acc)
+
+
 def test_resolve_matches_reference_quantisation(gpu_ctx):
     """mean -> sqrt -> int(255.99 c) -> clamp (Raytracing_n.cpp:848-862)."""
     import torch

@@ -44,6 +44,10 @@ def _worker(rank, world, port, ns, n, out_dir):
         t = torch.from_numpy(acc.copy())
         multigpu.reduce_accum(t, dst=0)
         np.save(os.path.join(out_dir, f"rank{rank}.npy"), t.numpy())
+        # the fixed-point form (srt_render_fixed): int64 sums with 31 fractional bits, reduced exactly
+        fx = torch.from_numpy(np.round(acc.astype(np.float64) * 2.0 ** 31).astype(np.int64))
+        multigpu.reduce_accum(fx, dst=0)
+        np.save(os.path.join(out_dir, f"fixed{rank}.npy"), fx.numpy())
         np.save(os.path.join(out_dir, f"own{rank}.npy"), acc)
     finally:
         dist.destroy_process_group()
@@ -61,6 +65,8 @@ def test_two_rank_reduce_equals_unsharded(tmp_path):
         whole += _contribution(s, n)
     got = np.load(tmp_path / "rank0.npy")
     assert np.array_equal(got, whole)  # contributions are exact in float32: order cannot matter
+    fixed = np.load(tmp_path / "fixed0.npy")
+    assert fixed.dtype == np.int64 and np.array_equal(fixed, np.round(whole.astype(np.float64) * 2.0 ** 31).astype(np.int64))
     own = [np.load(tmp_path / f"own{r}.npy") for r in range(world)]
     assert np.array_equal(own[0] + own[1], whole)
 
