@@ -311,11 +311,14 @@ SRT_DEV bool ref_reachable(const RefNode* root, int rank, const Ray& r, RayInv i
 // bound (ex_t, ex_rank) in the order "smaller t first, then higher rank"; if that candidate turns
 // out unreachable it becomes the new bound and the search repeats.  One pass in all but ~1e-6 of rays.
 // The stack holds the postponed children of the current root-to-node path: at most 3 per level of OUR tree.
-// A full stack is a COUNTED condition (DScene::diag -> SrtCounters::stack_overflows, asserted 0 by the tests
+// A stack that fills up completely is a COUNTED condition (DScene::diag -> SrtCounters::stack_overflows, asserted 0 by the tests
 // on every configuration including the 10 M-triangle one): the postponed subtree would be lost, so the
 // caller must be able to see it.  srt_bvh_build.cpp reports the tree's depth (SrtSceneInfo::bvh_max_depth);
 // near-first descent with cull-on-pop keeps the occupied depth far below 3 x depth in practice.
-constexpr int kStackSize = 48;
+#ifndef SRT_BVH_STACK
+#define SRT_BVH_STACK 48  // tools/build_alt.sh tiny -DSRT_BVH_STACK=4 builds the library the overflow counter is checked with
+#endif
+constexpr int kStackSize = SRT_BVH_STACK;
 
 // Wide-node step helpers.  Children that pass the slab test are ordered near-to-far with a 5-comparator
 // network on 32-bit keys held in registers: key = bits of max(lower bound, 0) with the two low
@@ -370,6 +373,13 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
         int32_t best_prim = -1;
         uint2 stack[kStackSize];  // (key, ref)
         int sp = 0;
+#ifndef SRT_NO_OVERFLOW_CHECK
+        // canary in the last entry: a push only ever writes it when the stack becomes completely full, which
+        // is the state in which the next postponed subtree would be dropped.  One local store here and one
+        // load after the traversal; the node loop itself carries no check (an atomic inside it cost 45 % on
+        // the C5 scene: profiles/r02_notes.md)
+        stack[kStackSize - 1] = make_uint2(kKeyNone, 0u);
+#endif
         int32_t cur = 0;  // >= 0 inner node; < 0 leaf reference ~(first << 3 | count); kRefDone
         for (;;) {
             // ---- inner nodes: descend until this lane holds a leaf (or has nothing left) -------------
@@ -405,10 +415,6 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
                 key_sort2(key[1], key[3]);
                 key_sort2(key[1], key[2]);
                 // push far-to-near, continue with the nearest
-                if (key[1] != kKeyNone && sp > kStackSize - 3) {  // (rare) not enough room for up to three
-                    const int want = (key[3] != kKeyNone) + (key[2] != kKeyNone) + 1;
-                    if (sp + want > kStackSize) atomicAdd(S.diag, 1ull);
-                }
                 if (key[3] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[3], (uint32_t)ref_select(refs, key[3]));
                 if (key[2] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[2], (uint32_t)ref_select(refs, key[2]));
                 if (key[1] != kKeyNone && sp < kStackSize) stack[sp++] = make_uint2(key[1], (uint32_t)ref_select(refs, key[1]));
@@ -473,6 +479,9 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
             }
             if (cur == kRefDone) break;
         }
+#ifndef SRT_NO_OVERFLOW_CHECK
+        if (stack[kStackSize - 1].x != kKeyNone) atomicAdd(S.diag, 1ull);  // counted, never silent
+#endif
         if (best_rank < 0) return false;
         RayInv inv{xdiv(1.0f, q.kx), xdiv(1.0f, q.ky), xdiv(1.0f, q.kz)};
         // Reachability shortcut.  Every ancestor box of the reference tree is a union that contains the

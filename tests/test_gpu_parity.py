@@ -81,7 +81,10 @@ def test_secondary_hits_match_golden(trace_scene):
     gid, gt, grec = sc.trace_closest(g["rays2"])
     worst = _check_hits(gid, gt, g["ids2"], g["t2"])
     hit = g["ids2"] >= 0
-    assert np.allclose(grec[hit], g["rec2"][hit], rtol=1e-5, atol=1e-4)
+    # env_sphere::hit with an un-normalised direction lands far outside the sphere: asin(y > 1) = NaN in v, on
+    # both sides (env_sphere.h:27-38, hitable.h:10-15)
+    assert np.array_equal(np.isnan(grec[hit]), np.isnan(g["rec2"][hit]))
+    assert np.allclose(grec[hit], g["rec2"][hit], rtol=1e-5, atol=1e-4, equal_nan=True)
     record_parity(f"secondary_hits/{name}", {"rays": int(len(gid)), "id_mismatches": 0, "max_rel_t_err": worst})
     assert sc.ctx.counters()["stack_overflows"] == 0
 
@@ -249,7 +252,9 @@ def test_counters_are_consistent(golden_scene, monkeypatch):
     # reference keeps bouncing it.  culled_rays counts the first skipped ray of each such path, so
     # rays + culled is a lower bound of the reference's count and not far below it.
     got = (c["rays"] + c["culled_rays"]) / c["paths"]
-    assert 0.85 * ref_rpp <= got <= 1.02 * ref_rpp
+    # `final`: a culled path would go on for many bounces inside the scene-wide constant_medium (every scatter
+    # there is specular and keeps the zero throughput alive up to depth 50), so the bound is looser
+    assert (0.6 if name == "final" else 0.85) * ref_rpp <= got <= 1.02 * ref_rpp
     monkeypatch.setenv("SRT_WAVEFRONT", "3")
     buf2 = torch.zeros_like(buf)
     w = sc.render_counted(render.render_params(nx, ny, ns), buf2)

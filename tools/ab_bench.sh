@@ -3,7 +3,7 @@
 # prints one line per config with the kernel time bench.py measured.
 tag=$1; shift
 for cfg in ${SRT_AB_CONFIGS:-spheres cornell}; do
-  env "$@" python bench.py --config $cfg --steps 5 --warmup 3 --no-cpu-baseline > gpurun_out/ab_${tag}_${cfg}.json 2> gpurun_out/ab_${tag}_${cfg}.err
+  env "$@" python bench.py --config $cfg --steps 5 --warmup 3 --no-cpu-baseline --no-per-config > gpurun_out/ab_${tag}_${cfg}.json 2> gpurun_out/ab_${tag}_${cfg}.err
   python - "$tag" "$cfg" <<'PY'
 import json,sys
 tag,cfg=sys.argv[1:3]
