@@ -396,6 +396,15 @@ int srt_sobol_points_u32(uint32_t n, uint32_t* out);
  * order in which SrtSceneDesc.bvh_items must list them.  Multi-threaded (10 M items: a few seconds). */
 int srt_ref_bvh_leaf_order(const float* mins, int64_t n, uint64_t* seed, int32_t* order_out);
 
+/* Diagnostic: the bounding boxes of the reference's bvh_node tree (bvh.h:96-119) over n leaves given in their
+ * in-order sequence, as srt_scene_create keeps them for the reachability replay.  item_boxes: [n][6] (min, max);
+ * nodes_out: 12 x 32-bit words per node in depth-first order — lo[3], left, hi[3], right, mid, 3 x 0 (left / right:
+ * node index or -1; mid: first rank of the right subtree) — room for 2 n nodes (srt_api.cu RefNode).  on_device != 0
+ * runs the per-level kernels srt_scene_create uses for large trees, 0 the host recursion it uses for small ones:
+ * the two must agree bit for bit (tests/test_gpu_features.py).  *count_out = nodes written. */
+int srt_ref_tree_boxes(SrtContext* ctx, const float* item_boxes, int32_t n, int on_device, void* nodes_out,
+                       int32_t* count_out);
+
 #ifdef __cplusplus
 }
 #endif

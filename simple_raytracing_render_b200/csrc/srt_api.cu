@@ -1,16 +1,20 @@
 // srt_api.cu — the C ABI of include/srt_ffi.h on top of the CUDA kernels.  No CPU path: every
 // compute entry point fails with SRT_E_NODEVICE / SRT_E_CUDA when there is no usable GPU.
 #include <algorithm>
+#include <thread>
+#include <atomic>
 #include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <vector>
 
 #include "srt_bvh_build.h"
+#include "srt_lbvh.cuh"
 #include "srt_ffi.h"
 #include "srt_aux_kernels.cuh"
 #include "srt_types.h"
@@ -76,6 +80,9 @@ struct SrtContext {
     size_t l2_persist_max = 0, l2_window_max = 0;
     const void* l2_window_base = nullptr;
     size_t l2_window_bytes = 0;
+    // pinned staging ring of staged_upload (large host -> device copies of srt_scene_create)
+    uint8_t* h_stage[2] = {nullptr, nullptr};
+    cudaEvent_t stage_ev[2] = {nullptr, nullptr};
 };
 
 struct SrtScene {
@@ -304,6 +311,150 @@ int validate(const SrtSceneDesc& d) {
 
 }  // namespace
 
+// fn(lo, hi) over [0, n) in contiguous chunks, on the host threads when the range is worth a fork
+template <class F>
+static void parallel_chunks(long long n, F&& fn, long long kMin = 1 << 16) {
+    unsigned hw = std::max(1u, std::min(32u, std::thread::hardware_concurrency()));
+    long long parts = std::min<long long>(hw, n / kMin);
+    if (parts <= 1) {
+        fn(0ll, n);
+        return;
+    }
+    std::vector<std::thread> th;
+    for (long long t = 0; t < parts; t++) th.emplace_back([&, t] { fn(n * t / parts, n * (t + 1) / parts); });
+    for (auto& x : th) x.join();
+}
+
+// Host -> device copy of a large pageable range: the host threads copy 32 MiB slices into a two-deep pinned ring and
+// each slice goes out as one DMA, so a 10 M-triangle scene uploads at host-memcpy speed instead of the driver's
+// single-threaded pageable staging.  Small ranges (and SRT_STAGED_UPLOAD=0) take cudaMemcpyAsync directly.
+// Either way the source range is consumed when the call returns.
+static cudaError_t staged_upload(SrtContext* c, void* dst, const void* src, size_t bytes) {
+    constexpr size_t kSlice = (size_t)32 << 20;
+    static const bool enabled = [] {
+        const char* e = getenv("SRT_STAGED_UPLOAD");
+        return !e || atoi(e) != 0;
+    }();
+    if (bytes < ((size_t)4 << 20) || !enabled) return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
+    for (int i = 0; i < 2; i++) {
+        if (!c->h_stage[i]) {
+            cudaError_t e = cudaHostAlloc((void**)&c->h_stage[i], kSlice, cudaHostAllocDefault);
+            if (e != cudaSuccess) {
+                c->h_stage[i] = nullptr;
+                (void)cudaGetLastError();
+                return cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, c->stream);
+            }
+        }
+        if (!c->stage_ev[i]) {
+            cudaError_t e = cudaEventCreateWithFlags(&c->stage_ev[i], cudaEventDisableTiming);
+            if (e != cudaSuccess) return e;
+        }
+    }
+    int turn = 0;
+    for (size_t at = 0; at < bytes; at += kSlice, turn ^= 1) {
+        const size_t len = std::min(kSlice, bytes - at);
+        cudaError_t e = cudaEventSynchronize(c->stage_ev[turn]);  // the DMA that last read this slot
+        if (e != cudaSuccess) return e;
+        uint8_t* stage = c->h_stage[turn];
+        const uint8_t* from = (const uint8_t*)src + at;
+        parallel_chunks((long long)len, [&](long long lo, long long hi) { std::memcpy(stage + lo, from + lo, (size_t)(hi - lo)); },
+                        (long long)1 << 20);
+        e = cudaMemcpyAsync((uint8_t*)dst + at, stage, len, cudaMemcpyHostToDevice, c->stream);
+        if (e != cudaSuccess) return e;
+        e = cudaEventRecord(c->stage_ev[turn], c->stream);
+        if (e != cudaSuccess) return e;
+    }
+    return cudaSuccess;
+}
+
+// ---- device-side reference tree (large BVHs) ---------------------------------------------------------------------------
+// The reference bvh_node tree over n leaves in their in-order sequence is a pure function of n: the node at level L,
+// position j (the bits of j, most significant first, say left/right) covers [lo, lo + cnt) with cnt halved floor/ceil on
+// the way down (bvh.h:96-119), and its depth-first index adds 1 for a left step, 1 + nodes(left size) for a right step.
+// A level holds two sizes at most, so nodes() is a two-entry table per level.  One launch per level, deepest first.
+struct RefLevelTable {
+    int size_lo[32];     // smaller subtree size at this level (the other is size_lo + 1)
+    int nodes_lo[32];    // nodes of a subtree of size_lo leaves
+    int nodes_hi[32];    // ... of size_lo + 1 leaves
+};
+
+__global__ void k_ref_tree_level(RefLevelTable tab, int level, int n, const float* __restrict__ item_boxes, RefNode* __restrict__ out) {
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= (1ll << level)) return;
+    int lo = 0, cnt = n, idx = 0;
+    for (int l = 0; l < level; l++) {
+        if (cnt <= 2) return;  // this position has no node: an ancestor is a leaf pair
+        const int nl = cnt / 2;
+        if ((j >> (level - 1 - l)) & 1) {
+            idx += 1 + (nl == tab.size_lo[l + 1] ? tab.nodes_lo[l + 1] : tab.nodes_hi[l + 1]);
+            lo += nl;
+            cnt -= nl;
+        } else {
+            idx += 1;
+            cnt = nl;
+        }
+    }
+    RefNode nd;
+    nd._pad[0] = nd._pad[1] = nd._pad[2] = 0;
+    if (cnt <= 2) {
+        // n == 1: left = right = l[0]; n == 2: left = l[0], right = l[1] (bvh.h:104-110)
+        const float* a = item_boxes + 6 * (size_t)lo;
+        const float* b = item_boxes + 6 * (size_t)(lo + cnt - 1);
+        for (int k = 0; k < 3; k++) {
+            nd.lo[k] = a[k] < b[k] ? a[k] : b[k];                  // ffmin, aabb.h:8
+            nd.hi[k] = a[3 + k] > b[3 + k] ? a[3 + k] : b[3 + k];  // ffmax, aabb.h:9
+        }
+        nd.left = nd.right = -1;
+        nd.mid = lo;
+    } else {
+        const int nl = cnt / 2;
+        const int l = idx + 1, r = idx + 1 + (nl == tab.size_lo[level + 1] ? tab.nodes_lo[level + 1] : tab.nodes_hi[level + 1]);
+        const RefNode &L = out[l], &R = out[r];
+        for (int k = 0; k < 3; k++) {
+            nd.lo[k] = L.lo[k] < R.lo[k] ? L.lo[k] : R.lo[k];
+            nd.hi[k] = L.hi[k] > R.hi[k] ? L.hi[k] : R.hi[k];
+        }
+        nd.left = l;
+        nd.right = r;
+        nd.mid = lo + nl;
+    }
+    out[idx] = nd;
+}
+
+// DPrim records of a large scene straight from the uploaded SrtPrim rows (same fields as make_dprim below)
+__global__ void k_make_dprims(const SrtPrim* __restrict__ prims, int n, const float* __restrict__ spheres,
+                              const float* __restrict__ rects, DPrim* __restrict__ out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    SrtPrim p = prims[i];
+    DPrim o;
+    o.g = make_float4(0.f, 0.f, 0.f, 0.f);
+    o.k = 0.f;
+    o.type = p.type;
+    o.material = p.material;
+    o.flags_aux = p.flags & SRT_PRIM_FLIP;
+    switch (p.type) {
+        case SRT_PRIM_SPHERE:
+        case SRT_PRIM_ENV_SPHERE: {
+            const float* q = spheres + 4 * (size_t)p.index;
+            o.g = make_float4(q[0], q[1], q[2], q[3]);
+            break;
+        }
+        case SRT_PRIM_XY_RECT:
+        case SRT_PRIM_XZ_RECT:
+        case SRT_PRIM_YZ_RECT: {
+            const float* q = rects + 5 * (size_t)p.index;
+            o.g = make_float4(q[0], q[1], q[2], q[3]);
+            o.k = q[4];
+            break;
+        }
+        default:
+            o.flags_aux |= (uint32_t)p.index << 1;
+            break;
+    }
+    out[i] = o;
+}
+
 extern "C" {
 
 const char* srt_last_error(void) { return g_error.c_str(); }
@@ -350,6 +501,10 @@ int srt_context_destroy(SrtContext* ctx) {
     for (int i = 0; i < 2; i++)
         if (ctx->wf_ev[i]) cudaEventDestroy(ctx->wf_ev[i]);
     if (ctx->h_rgb8) cudaFreeHost(ctx->h_rgb8);
+    for (int i = 0; i < 2; i++) {
+        if (ctx->h_stage[i]) cudaFreeHost(ctx->h_stage[i]);
+        if (ctx->stage_ev[i]) cudaEventDestroy(ctx->stage_ev[i]);
+    }
     delete ctx;
     return 0;
 }
@@ -372,6 +527,11 @@ int srt_scene_destroy(SrtScene* s) {
 }
 
 // SRT_SCENE_TIMING=1: per-stage host times of srt_scene_create on stderr
+static int env_int_early_value(const char* n, int fallback) {
+    const char* v = getenv(n);
+    return v && *v ? atoi(v) : fallback;
+}
+
 struct StageTimer {
     bool on;
     std::chrono::steady_clock::time_point t0;
@@ -397,20 +557,148 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     if (rc) return rc;
     CUDA_TRY(cudaSetDevice(ctx->device));
     auto t0 = std::chrono::steady_clock::now();
+    stage.tick("validate");
 
     // ---- acceleration structures -----------------------------------------------------------
+    // Per bvh the three arrays the traversal reads (wide nodes, leaf ranks, leaf geometry) come either from the
+    // host builder (vectors) or from the device builder (device buffers): `Seg` lists keep them in bvh order, the
+    // blob copy below takes each from where it is.
+    struct Seg {
+        const void* src;
+        size_t bytes;
+        bool on_device;
+    };
+    struct TempDev {  // device scratch of this call: freed on every exit path
+        std::vector<void*> ptrs;
+        std::vector<srt_lbvh::DeviceBvh> built;
+        ~TempDev() {
+            for (void* p : ptrs) cudaFree(p);
+            for (auto& b : built) b.release();
+        }
+    } tmpdev;
     std::vector<DBvh> bvhs(d.n_bvhs);
-    std::vector<WideNode4> wide;
-    std::vector<RefNode> refn;
-    std::vector<int32_t> leaf_rank;
-    std::vector<float4> leaf_geom;
+    std::vector<Seg> seg_wide, seg_rank, seg_geom;
+    std::vector<std::vector<WideNode4>> keep_wide(d.n_bvhs);
+    std::vector<std::vector<int32_t>> keep_rank(d.n_bvhs);
+    std::vector<std::vector<float4>> keep_geom(d.n_bvhs);
+    std::vector<std::vector<float>> dev_root_box(d.n_bvhs);  // device-built: root bounds (for the entry record)
+    std::vector<std::vector<RefNode>> keep_ref(d.n_bvhs);
+    std::vector<Seg> seg_ref;
+    size_t n_ref = 0;
+    size_t n_wide = 0, n_rank = 0, n_geom = 0;
     float top_sah = 0.f;
-    int top_items = 0, max_depth = 0;
+    int top_items = 0, max_depth = 0, builder_used = 0;
+    float* d_tri_tmp = nullptr;  // the triangle positions, uploaded early for the device builder
+    const int dev_min = env_int_early_value("SRT_DEVICE_BVH_MIN", 32768);
+    const bool dev_ok = env_int_early_value("SRT_DEVICE_BVH", 1) != 0;
+    double ms_build_dev = 0.0, ms_build_top = 0.0;
     for (int bi = 0; bi < d.n_bvhs; bi++) {
         const SrtBvh& sb = d.bvhs[bi];
         int n = sb.item_count;
+        std::atomic<bool> all_sphere{true}, all_tri{true};
+        parallel_chunks(n, [&](long long lo, long long hi) {
+            bool as = true, at = true;
+            for (long long k = lo; k < hi && (as || at); k++) {
+                const SrtGroup& g = d.groups[d.bvh_items[sb.first_item + k]];
+                bool single = g.prim_count == 1;
+                as = as && single && d.prims[g.first_prim].type == SRT_PRIM_SPHERE;
+                at = at && single && d.prims[g.first_prim].type == SRT_PRIM_TRIANGLE;
+            }
+            if (!as) all_sphere = false;
+            if (!at) all_tri = false;
+        });
+        DBvh& B = bvhs[bi];
+        B.kind = all_sphere.load() ? BVH_KIND_SPHERE : (all_tri.load() ? BVH_KIND_TRIANGLE : BVH_KIND_GENERIC);
+        B.first_item = sb.first_item;
+        B.item_count = n;
+        B.node_base = (int32_t)n_wide;
+        B.ref_base = (int32_t)n_ref;
+        B.leaf_base = (int32_t)n_rank;
+        B.geom_base = (int32_t)n_geom;
+        B._pad = 0;
+        if (dev_ok && n >= dev_min) {
+            // the reference tree on the device: boxes up, one launch per level from the leaves to the root
+            RefLevelTable tab;
+            const int levels = ref_tree_levels(n, tab.size_lo, tab.nodes_lo, tab.nodes_hi);
+            const size_t count = (size_t)tab.nodes_lo[0];
+            float* d_boxes = nullptr;
+            RefNode* d_ref = nullptr;
+            CUDA_TRY(cudaMalloc(&d_boxes, sizeof(float) * 6 * (size_t)n));
+            tmpdev.ptrs.push_back(d_boxes);
+            CUDA_TRY(cudaMalloc(&d_ref, sizeof(RefNode) * count));
+            tmpdev.ptrs.push_back(d_ref);
+            CUDA_TRY(staged_upload(ctx, d_boxes, d.bvh_item_boxes + 6 * (size_t)sb.first_item, sizeof(float) * 6 * (size_t)n));
+            for (int L = levels - 1; L >= 0; L--) {
+                const long long width = 1ll << L;
+                k_ref_tree_level<<<(unsigned)((width + 255) / 256), 256, 0, ctx->stream>>>(tab, L, n, d_boxes, d_ref);
+            }
+            CUDA_TRY(cudaGetLastError());
+            seg_ref.push_back(Seg{d_ref, sizeof(RefNode) * count, true});
+            n_ref += count;
+            stage.tick("reference tree (device)");
+        } else {
+            build_ref_tree(d.bvh_item_boxes + 6 * (size_t)sb.first_item, n, keep_ref[bi]);
+            seg_ref.push_back(Seg{keep_ref[bi].data(), sizeof(RefNode) * keep_ref[bi].size(), false});
+            n_ref += keep_ref[bi].size();
+            stage.tick("build_ref_tree");
+        }
+        if (dev_ok && B.kind == BVH_KIND_TRIANGLE && n >= dev_min) {
+            // ---- device build (srt_lbvh.cuh) --------------------------------------------------------------
+            if (!d_tri_tmp) {
+                CUDA_TRY(cudaMalloc(&d_tri_tmp, sizeof(float) * 9 * (size_t)d.n_tris));
+                tmpdev.ptrs.push_back(d_tri_tmp);
+                CUDA_TRY(staged_upload(ctx, d_tri_tmp, d.tri_pos, sizeof(float) * 9 * (size_t)d.n_tris));
+            }
+            std::unique_ptr<int32_t[]> rows(new int32_t[(size_t)n]);  // first touched by the threads that fill it
+            parallel_chunks(n, [&](long long lo, long long hi) {
+                for (long long k = lo; k < hi; k++)
+                    rows[(size_t)k] = d.prims[d.groups[d.bvh_items[sb.first_item + k]].first_prim].index;
+            });
+            int32_t* d_rows = nullptr;
+            CUDA_TRY(cudaMalloc(&d_rows, sizeof(int32_t) * (size_t)n));
+            tmpdev.ptrs.push_back(d_rows);
+            CUDA_TRY(staged_upload(ctx, d_rows, rows.get(), sizeof(int32_t) * (size_t)n));
+            stage.tick("device build: uploads queued");
+            srt_lbvh::DeviceBvh db;
+            std::string err;
+            if (!srt_lbvh::build(ctx->stream, d_tri_tmp, d_rows, n, db, err)) return fail(SRT_E_CUDA, "%s", err.c_str());
+            tmpdev.built.push_back(db);
+            stage.tick("device build: srt_lbvh::build");
+            if (stage.on)
+                fprintf(stderr, "[srt_lbvh::build] n %d: device %.2f ms, host top SAH over %d clusters %.2f ms\n", n, db.ms_device,
+                        db.n_clusters, db.ms_host_top);
+            ms_build_dev += db.ms_device;
+            ms_build_top += db.ms_host_top;
+            seg_wide.push_back(Seg{db.nodes, sizeof(WideNode4) * (size_t)db.n_nodes, true});
+            seg_rank.push_back(Seg{db.leaf_rank, sizeof(int32_t) * (size_t)n, true});
+            seg_geom.push_back(Seg{db.leaf_geom, sizeof(float4) * 3 * (size_t)n, true});
+            n_wide += (size_t)db.n_nodes;
+            n_rank += (size_t)n;
+            n_geom += 3 * (size_t)n;
+            max_depth = std::max(max_depth, db.max_depth);
+            builder_used = 1;
+            // root bounds = union of the four child boxes of wide node 0
+            WideNode4 rootn;
+            CUDA_TRY(cudaMemcpy(&rootn, db.nodes, sizeof rootn, cudaMemcpyDeviceToHost));
+            std::vector<float>& rb = dev_root_box[bi];
+            rb.assign({3.4e38f, 3.4e38f, 3.4e38f, -3.4e38f, -3.4e38f, -3.4e38f});
+            for (int i = 0; i < 4; i++) {
+                if ((&rootn.ref.x)[i] == (int32_t)0x80000000) continue;
+                rb[0] = std::min(rb[0], (&rootn.lox.x)[i]);
+                rb[1] = std::min(rb[1], (&rootn.loy.x)[i]);
+                rb[2] = std::min(rb[2], (&rootn.loz.x)[i]);
+                rb[3] = std::max(rb[3], (&rootn.hix.x)[i]);
+                rb[4] = std::max(rb[4], (&rootn.hiy.x)[i]);
+                rb[5] = std::max(rb[5], (&rootn.hiz.x)[i]);
+            }
+            if (n > top_items) {
+                top_items = n;
+                top_sah = db.sah_cost;
+            }
+            continue;
+        }
+        // ---- host build (srt_bvh_build.cpp) -----------------------------------------------------------------
         std::vector<float> boxes(6 * (size_t)n);
-        bool all_sphere = true, all_tri = true;
         for (int k = 0; k < n; k++) {
             const SrtGroup& g = d.groups[d.bvh_items[sb.first_item + k]];
             float* b = &boxes[6 * (size_t)k];
@@ -432,45 +720,38 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
                 for (int a = 0; a < 6; a++) b[a] = 0.f;
             }
             pad_box(b);
-            bool single = g.prim_count == 1;
-            all_sphere = all_sphere && single && d.prims[g.first_prim].type == SRT_PRIM_SPHERE;
-            all_tri = all_tri && single && d.prims[g.first_prim].type == SRT_PRIM_TRIANGLE;
         }
         WideBvh wb;
         stage.tick("item boxes");
         build_wide_bvh(boxes.data(), n, wb);
         stage.tick("build_wide_bvh");
-        std::vector<RefNode> rt;
-        build_ref_tree(d.bvh_item_boxes + 6 * (size_t)sb.first_item, n, rt);
-        stage.tick("build_ref_tree");
-        DBvh& B = bvhs[bi];
-        B.kind = all_sphere ? BVH_KIND_SPHERE : (all_tri ? BVH_KIND_TRIANGLE : BVH_KIND_GENERIC);
-        B.first_item = sb.first_item;
-        B.item_count = n;
-        B.node_base = (int32_t)wide.size();
-        B.ref_base = (int32_t)refn.size();
-        B.leaf_base = (int32_t)leaf_rank.size();
-        B.geom_base = (int32_t)leaf_geom.size();
-        B._pad = 0;
-        wide.insert(wide.end(), wb.nodes.begin(), wb.nodes.end());
-        refn.insert(refn.end(), rt.begin(), rt.end());
-        leaf_rank.insert(leaf_rank.end(), wb.order.begin(), wb.order.end());
+        keep_wide[bi].swap(wb.nodes);
+        keep_rank[bi].swap(wb.order);
+        const std::vector<int32_t>& order = keep_rank[bi];
+        std::vector<float4>& geom = keep_geom[bi];
         if (B.kind == BVH_KIND_SPHERE) {
+            geom.reserve((size_t)n);
             for (int s = 0; s < n; s++) {
-                const SrtPrim& p = d.prims[d.groups[d.bvh_items[sb.first_item + wb.order[s]]].first_prim];
+                const SrtPrim& p = d.prims[d.groups[d.bvh_items[sb.first_item + order[s]]].first_prim];
                 const float* q = d.spheres + 4 * (size_t)p.index;
-                leaf_geom.push_back(float4{q[0], q[1], q[2], q[3]});
+                geom.push_back(float4{q[0], q[1], q[2], q[3]});
             }
         } else if (B.kind == BVH_KIND_TRIANGLE) {
-            leaf_geom.reserve(leaf_geom.size() + 3 * (size_t)n);
+            geom.reserve(3 * (size_t)n);
             for (int s = 0; s < n; s++) {
-                const SrtPrim& p = d.prims[d.groups[d.bvh_items[sb.first_item + wb.order[s]]].first_prim];
+                const SrtPrim& p = d.prims[d.groups[d.bvh_items[sb.first_item + order[s]]].first_prim];
                 const float* q = d.tri_pos + 9 * (size_t)p.index;
-                leaf_geom.push_back(float4{q[0], q[1], q[2], 0.f});
-                leaf_geom.push_back(float4{q[3], q[4], q[5], 0.f});
-                leaf_geom.push_back(float4{q[6], q[7], q[8], 0.f});
+                geom.push_back(float4{q[0], q[1], q[2], 0.f});
+                geom.push_back(float4{q[3], q[4], q[5], 0.f});
+                geom.push_back(float4{q[6], q[7], q[8], 0.f});
             }
         }
+        seg_wide.push_back(Seg{keep_wide[bi].data(), sizeof(WideNode4) * keep_wide[bi].size(), false});
+        seg_rank.push_back(Seg{keep_rank[bi].data(), sizeof(int32_t) * keep_rank[bi].size(), false});
+        seg_geom.push_back(Seg{geom.data(), sizeof(float4) * geom.size(), false});
+        n_wide += keep_wide[bi].size();
+        n_rank += keep_rank[bi].size();
+        n_geom += geom.size();
         max_depth = std::max(max_depth, wb.max_depth);
         if (n > top_items) {
             top_items = n;
@@ -511,21 +792,33 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     std::vector<char> in_tri_bvh(d.n_prims, 0);
     for (int bi = 0; bi < d.n_bvhs; bi++) {
         if (bvhs[bi].kind != BVH_KIND_TRIANGLE) continue;
-        for (int k = 0; k < d.bvhs[bi].item_count; k++)
-            in_tri_bvh[d.groups[d.bvh_items[d.bvhs[bi].first_item + k]].first_prim] = 1;
+        parallel_chunks(d.bvhs[bi].item_count, [&](long long lo, long long hi) {
+            for (long long k = lo; k < hi; k++) in_tri_bvh[d.groups[d.bvh_items[d.bvhs[bi].first_item + k]].first_prim] = 1;
+        });
         feat |= F_BVH_TRI;
     }
     for (int bi = 0; bi < d.n_bvhs; bi++) {
         if (bvhs[bi].kind == BVH_KIND_SPHERE) feat |= F_BVH_SPHERE;
         if (bvhs[bi].kind == BVH_KIND_GENERIC) feat |= F_BVH_GENERIC;
     }
-    std::vector<DPrim> dprims(d.n_prims);
-    for (int i = 0; i < d.n_prims; i++) {
-        const SrtPrim& p = d.prims[i];
-        dprims[i] = make_dprim(p.type, p.index, p.material, p.flags);
-        if (p.type == SRT_PRIM_TRIANGLE && !in_tri_bvh[i]) feat |= F_TRI;
-        if (p.type == SRT_PRIM_MOVING_SPHERE) feat |= F_MSPHERE;
-        if (p.type == SRT_PRIM_ENV_SPHERE) feat |= F_ENV;
+    // large scenes: the records are written on the device from the uploaded SrtPrim rows (k_make_dprims), the host
+    // loop only collects the feature bits
+    const bool dprims_on_device = dev_ok && d.n_prims >= dev_min;
+    std::vector<DPrim> dprims(dprims_on_device ? 0 : d.n_prims);
+    {
+        std::atomic<uint32_t> prim_feat{0};
+        parallel_chunks(d.n_prims, [&](long long lo, long long hi) {
+            uint32_t f = 0;
+            for (long long i = lo; i < hi; i++) {
+                const SrtPrim& p = d.prims[i];
+                if (!dprims_on_device) dprims[(size_t)i] = make_dprim(p.type, p.index, p.material, p.flags);
+                if (p.type == SRT_PRIM_TRIANGLE && !in_tri_bvh[(size_t)i]) f |= F_TRI;
+                if (p.type == SRT_PRIM_MOVING_SPHERE) f |= F_MSPHERE;
+                if (p.type == SRT_PRIM_ENV_SPHERE) f |= F_ENV;
+            }
+            prim_feat.fetch_or(f);
+        });
+        feat |= prim_feat.load();
     }
     std::vector<DPrim> dlights(d.n_lights);
     for (int i = 0; i < d.n_lights; i++) {
@@ -581,6 +874,12 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
             o.first_prim = g.first_prim;
             o.prim_count = g.prim_count;
             add_group(g);
+        } else if (!dev_root_box[e.geom_index].empty()) {
+            // device-built bvh: its root box IS the union of the padded item boxes (same padding, srt_lbvh.cuh)
+            const std::vector<float>& rb = dev_root_box[e.geom_index];
+            for (int a = 0; a < 6; a++) b[a] = rb[a];
+            honours_t = false;  // triangle::hit ignores (t0, t1)
+            n_inside = d.bvhs[e.geom_index].item_count;
         } else {
             const SrtBvh& sb = d.bvhs[e.geom_index];
             for (int k = 0; k < sb.item_count; k++) add_group(d.groups[d.bvh_items[sb.first_item + k]]);
@@ -641,31 +940,44 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
         const void* src;
         size_t bytes;
         size_t off;
+        bool on_device;
     };
     std::vector<Piece> pieces;
     Layout lay;
     auto piece = [&](const void* src, size_t bytes, size_t align = 256) -> size_t {
         size_t off = lay.add(bytes, align);
-        if (bytes) pieces.push_back(Piece{src, bytes, off});
+        if (bytes) pieces.push_back(Piece{src, bytes, off, false});
+        return off;
+    };
+    auto seg_pieces = [&](const std::vector<Seg>& segs, size_t total_bytes) -> size_t {
+        size_t off = lay.add(total_bytes, 256), at = off;
+        for (const Seg& g : segs) {
+            if (g.bytes) pieces.push_back(Piece{g.src, g.bytes, at, g.on_device});
+            at += g.bytes;
+        }
         return off;
     };
     static_assert(sizeof(DEntry) == 64 && sizeof(DPrim) == 32 && sizeof(SrtXformOp) == 16 && sizeof(DMaterial) == 48,
                   "record sizes are part of the device layout");
     size_t o_entries = piece(dentries.data(), sizeof(DEntry) * dentries.size());
     size_t o_ops = piece(d.ops, sizeof(SrtXformOp) * (size_t)d.n_ops, 16);
-    size_t o_dprims = piece(dprims.data(), sizeof(DPrim) * dprims.size(), 16);
+    size_t o_dprims = dprims_on_device ? lay.add(sizeof(DPrim) * (size_t)d.n_prims, 16)
+                                       : piece(dprims.data(), sizeof(DPrim) * dprims.size(), 16);
     size_t o_lights = piece(dlights.data(), sizeof(DPrim) * dlights.size(), 16);
     size_t hot_end = (lay.total + 15) & ~(size_t)15;
     size_t o_groups = piece(d.groups, sizeof(SrtGroup) * (size_t)d.n_groups);
     size_t o_items = piece(d.bvh_items, sizeof(int32_t) * (size_t)d.n_bvh_items);
     size_t o_media = piece(d.media, sizeof(SrtMedium) * (size_t)d.n_media);
     size_t o_bvhs = piece(bvhs.data(), sizeof(DBvh) * bvhs.size());
-    size_t o_wide = piece(wide.data(), sizeof(WideNode4) * wide.size());
-    size_t o_ref = piece(refn.data(), sizeof(RefNode) * refn.size());
-    size_t o_rank = piece(leaf_rank.data(), sizeof(int32_t) * leaf_rank.size());
-    size_t o_geom = piece(leaf_geom.data(), sizeof(float4) * leaf_geom.size());
+    size_t o_wide = seg_pieces(seg_wide, sizeof(WideNode4) * n_wide);
+    size_t o_ref = seg_pieces(seg_ref, sizeof(RefNode) * n_ref);
+    size_t o_rank = seg_pieces(seg_rank, sizeof(int32_t) * n_rank);
+    size_t o_geom = seg_pieces(seg_geom, sizeof(float4) * n_geom);
     size_t o_msph = piece(d.msph, sizeof(float) * 9 * (size_t)d.n_msph);
-    size_t o_tpos = piece(d.tri_pos, sizeof(float) * 9 * (size_t)d.n_tris);
+    size_t o_tpos = lay.add(sizeof(float) * 9 * (size_t)d.n_tris, 256);
+    if (d.n_tris)  // already on the device when the device builder ran
+        pieces.push_back(Piece{d_tri_tmp ? (const void*)d_tri_tmp : (const void*)d.tri_pos, sizeof(float) * 9 * (size_t)d.n_tris,
+                               o_tpos, d_tri_tmp != nullptr});
     size_t o_tnrm = piece(d.tri_nrm, sizeof(float) * 9 * (size_t)d.n_tris);
     size_t o_tuv = piece(d.tri_uv, sizeof(float) * 6 * (size_t)d.n_tris);
     size_t o_mats = piece(dmats.data(), sizeof(DMaterial) * dmats.size());
@@ -699,7 +1011,26 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
         }                                                                         \
     } while (0)
     SCENE_TRY(cudaMemsetAsync(s->d_blob, 0, s->blob_bytes, ctx->stream));
-    for (const Piece& p : pieces) SCENE_TRY(cudaMemcpyAsync(s->d_blob + p.off, p.src, p.bytes, cudaMemcpyHostToDevice, ctx->stream));
+    for (const Piece& p : pieces) {
+        if (p.on_device) SCENE_TRY(cudaMemcpyAsync(s->d_blob + p.off, p.src, p.bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+        else SCENE_TRY(staged_upload(ctx, s->d_blob + p.off, p.src, p.bytes));
+    }
+    if (dprims_on_device) {
+        SrtPrim* d_prims_in = nullptr;
+        float *d_sph = nullptr, *d_rect = nullptr;
+        SCENE_TRY(cudaMalloc(&d_prims_in, sizeof(SrtPrim) * (size_t)d.n_prims));
+        tmpdev.ptrs.push_back(d_prims_in);
+        SCENE_TRY(cudaMalloc(&d_sph, sizeof(float) * 4 * (size_t)std::max(d.n_spheres, 1)));
+        tmpdev.ptrs.push_back(d_sph);
+        SCENE_TRY(cudaMalloc(&d_rect, sizeof(float) * 5 * (size_t)std::max(d.n_rects, 1)));
+        tmpdev.ptrs.push_back(d_rect);
+        SCENE_TRY(staged_upload(ctx, d_prims_in, d.prims, sizeof(SrtPrim) * (size_t)d.n_prims));
+        if (d.n_spheres) SCENE_TRY(staged_upload(ctx, d_sph, d.spheres, sizeof(float) * 4 * (size_t)d.n_spheres));
+        if (d.n_rects) SCENE_TRY(staged_upload(ctx, d_rect, d.rects, sizeof(float) * 5 * (size_t)d.n_rects));
+        k_make_dprims<<<(unsigned)((d.n_prims + 255) / 256), 256, 0, ctx->stream>>>(d_prims_in, d.n_prims, d_sph, d_rect,
+                                                                                    (DPrim*)(s->d_blob + o_dprims));
+        SCENE_TRY(cudaGetLastError());
+    }
     std::vector<DImage> imgtab(d.n_images);
     for (int i = 0; i < d.n_images; i++) imgtab[i] = DImage{s->d_blob + o_img[i], d.images[i].nx, d.images[i].ny};
     if (d.n_images) SCENE_TRY(cudaMemcpyAsync(s->d_blob + o_imgtab, imgtab.data(), sizeof(DImage) * imgtab.size(), cudaMemcpyHostToDevice, ctx->stream));
@@ -760,12 +1091,14 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
     s->info.n_entries = d.n_entries;
     s->info.n_bvhs = d.n_bvhs;
     s->info.n_lights = d.n_lights;
-    s->info.bvh_nodes = (int64_t)wide.size();
-    s->info.bvh_node_bytes = (int64_t)(wide.size() * sizeof(WideNode4));
+    s->info.bvh_nodes = (int64_t)n_wide;
+    s->info.bvh_node_bytes = (int64_t)(n_wide * sizeof(WideNode4));
     s->info.device_bytes = (int64_t)s->blob_bytes + (int64_t)d.n_merl * 8 * 3 * 90 * 90 * 180;
     s->info.sah_cost = top_sah;
     s->info.bvh_max_depth = max_depth;
-    s->info.bvh_builder = 0;
+    s->info.bvh_builder = builder_used;
+    (void)ms_build_dev;
+    (void)ms_build_top;
     s->info.build_ms = std::chrono::duration<float, std::milli>(t1 - t0).count();
     *out = s;
     return 0;
@@ -946,6 +1279,38 @@ int srt_ref_bvh_leaf_order(const float* mins, int64_t n, uint64_t* seed, int32_t
     unsigned long long s = *seed;
     ref_bvh_leaf_order(mins, (long long)n, &s, order_out);
     *seed = s;
+    return 0;
+}
+
+int srt_ref_tree_boxes(SrtContext* ctx, const float* item_boxes, int32_t n, int on_device, void* nodes_out, int32_t* count_out) {
+    if (!ctx || !item_boxes || !nodes_out || !count_out || n < 1) return fail(SRT_E_INVALID, "bad argument");
+    if (!on_device) {
+        std::vector<RefNode> t;
+        build_ref_tree(item_boxes, n, t);
+        std::memcpy(nodes_out, t.data(), sizeof(RefNode) * t.size());
+        *count_out = (int32_t)t.size();
+        return 0;
+    }
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    RefLevelTable tab;
+    const int levels = ref_tree_levels(n, tab.size_lo, tab.nodes_lo, tab.nodes_hi);
+    const size_t count = (size_t)tab.nodes_lo[0];
+    float* d_boxes = nullptr;
+    RefNode* d_ref = nullptr;
+    CUDA_TRY(cudaMalloc(&d_boxes, sizeof(float) * 6 * (size_t)n));
+    cudaError_t e = cudaMalloc(&d_ref, sizeof(RefNode) * count);
+    if (e == cudaSuccess) e = staged_upload(ctx, d_boxes, item_boxes, sizeof(float) * 6 * (size_t)n);
+    for (int L = levels - 1; L >= 0 && e == cudaSuccess; L--) {
+        const long long width = 1ll << L;
+        k_ref_tree_level<<<(unsigned)((width + 255) / 256), 256, 0, ctx->stream>>>(tab, L, n, d_boxes, d_ref);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(nodes_out, d_ref, sizeof(RefNode) * count, cudaMemcpyDeviceToHost, ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    cudaFree(d_boxes);
+    cudaFree(d_ref);
+    if (e != cudaSuccess) return fail(SRT_E_CUDA, "srt_ref_tree_boxes: %s", cudaGetErrorString(e));
+    *count_out = (int32_t)count;
     return 0;
 }
 

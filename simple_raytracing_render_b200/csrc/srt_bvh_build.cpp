@@ -10,6 +10,7 @@
 #include <cmath>
 #include <cstring>
 #include <future>
+#include <map>
 #include <thread>
 
 namespace {
@@ -58,6 +59,7 @@ struct Builder {
     std::atomic<int32_t> next_node{0};
     std::atomic<int> live_tasks{0};
     int max_tasks;
+    int max_leaf = kMaxLeaf;
 
     Builder(const float* b, int n, std::vector<int32_t>& ord) : boxes(b), order(ord) {
         nodes.resize(std::max(1, 2 * n));
@@ -215,7 +217,7 @@ struct Builder {
         if (best_axis >= 0) {
             float split_cost = kTraversalCost + kIntersectCost * best_cost / std::max(parent_area, 1e-30f);
             float leaf_cost = kIntersectCost * count;
-            if (count <= kMaxLeaf && leaf_cost <= split_cost) return me;
+            if (count <= max_leaf && leaf_cost <= split_cost) return me;
             const float bscale = scale[best_axis];
             const float lo = cb.lo[best_axis];
             auto it = std::partition(order.begin() + first, order.begin() + first + count, [&](int32_t item) {
@@ -226,7 +228,7 @@ struct Builder {
             mid = (int)(it - order.begin());
         }
         if (mid <= first || mid >= first + count) {
-            if (count <= kMaxLeaf) return me;
+            if (count <= max_leaf) return me;
             // all centroids coincide (or binning degenerated): split by count
             mid = first + count / 2;
         }
@@ -354,46 +356,114 @@ void build_wide_bvh(const float* boxes, int n, WideBvh& out) {
     }
 }
 
+void build_binary_sah(const float* boxes, int n, int max_leaf, std::vector<SahBinNode>& nodes, std::vector<int32_t>& order) {
+    order.resize(n);
+    for (int i = 0; i < n; i++) order[i] = i;
+    Builder b(boxes, n, order);
+    b.max_leaf = std::max(1, max_leaf);
+    b.build(0, n);
+    const int used = b.next_node.load();
+    nodes.resize((size_t)used);
+    for (int k = 0; k < used; k++) {
+        const BinNode& s = b.nodes[(size_t)k];
+        SahBinNode& o = nodes[(size_t)k];
+        for (int a = 0; a < 3; a++) {
+            o.lo[a] = s.box.lo[a];
+            o.hi[a] = s.box.hi[a];
+        }
+        o.left = s.left;
+        o.right = s.right;
+        o.first = s.first;
+        o.count = s.count;
+    }
+}
+
 namespace {
-int32_t ref_build(const float* ib, int lo, int n, std::vector<RefNode>& out) {
-    int32_t me = (int32_t)out.size();
-    out.emplace_back();
-    RefNode nd;
-    std::memset(&nd, 0, sizeof(nd));
-    nd.left = nd.right = -1;
-    nd.mid = lo;
-    if (n <= 2) {
-        // n == 1: left = right = l[0]; n == 2: left = l[0], right = l[1] (bvh.h:104-110)
-        const float* a = ib + 6 * (size_t)lo;
-        const float* b = ib + 6 * (size_t)(lo + n - 1);
+// nodes of the reference subtree over n leaves (one node for n <= 2); memoised, a level holds two sizes at most
+struct NodeCount {
+    std::map<long long, long long> memo;
+    long long fill(long long n) {
+        if (n <= 2) return 1;
+        auto it = memo.find(n);
+        if (it != memo.end()) return it->second;
+        long long v = 1 + fill(n / 2) + fill(n - n / 2);
+        memo[n] = v;
+        return v;
+    }
+    long long operator()(long long n) const { return n <= 2 ? 1 : memo.at(n); }  // after fill(root): read-only
+};
+
+// Node indices are the depth-first numbers, known before the subtree is built (left = me + 1,
+// right = me + 1 + nodes(left)), so the upper levels fork into independent tasks.
+struct RefTree {
+    const float* ib;
+    RefNode* out;
+    NodeCount nodes;
+
+    void build(int lo, int n, int32_t me, int forks) {
+        RefNode nd;
+        std::memset(&nd, 0, sizeof(nd));
+        nd.left = nd.right = -1;
+        nd.mid = lo;
+        if (n <= 2) {
+            // n == 1: left = right = l[0]; n == 2: left = l[0], right = l[1] (bvh.h:104-110)
+            const float* a = ib + 6 * (size_t)lo;
+            const float* b = ib + 6 * (size_t)(lo + n - 1);
+            for (int k = 0; k < 3; k++) {
+                nd.lo[k] = a[k] < b[k] ? a[k] : b[k];               // ffmin, aabb.h:8
+                nd.hi[k] = a[3 + k] > b[3 + k] ? a[3 + k] : b[3 + k];  // ffmax, aabb.h:9
+            }
+            out[me] = nd;
+            return;
+        }
+        const int nl = n / 2;
+        const int32_t l = me + 1, r = me + 1 + (int32_t)nodes(nl);
+        if (forks > 0 && n >= (1 << 15)) {
+            auto other = std::async(std::launch::async, [&] { build(lo, nl, l, forks - 1); });
+            build(lo + nl, n - nl, r, forks - 1);
+            other.get();
+        } else {
+            build(lo, nl, l, 0);
+            build(lo + nl, n - nl, r, 0);
+        }
+        nd.left = l;
+        nd.right = r;
+        nd.mid = lo + nl;
         for (int k = 0; k < 3; k++) {
-            nd.lo[k] = a[k] < b[k] ? a[k] : b[k];               // ffmin, aabb.h:8
-            nd.hi[k] = a[3 + k] > b[3 + k] ? a[3 + k] : b[3 + k];  // ffmax, aabb.h:9
+            float a = out[l].lo[k], b = out[r].lo[k];
+            nd.lo[k] = a < b ? a : b;
+            a = out[l].hi[k];
+            b = out[r].hi[k];
+            nd.hi[k] = a > b ? a : b;
         }
         out[me] = nd;
-        return me;
     }
-    int32_t l = ref_build(ib, lo, n / 2, out);
-    int32_t r = ref_build(ib, lo + n / 2, n - n / 2, out);
-    nd.left = l;
-    nd.right = r;
-    nd.mid = lo + n / 2;
-    for (int k = 0; k < 3; k++) {
-        float a = out[l].lo[k], b = out[r].lo[k];
-        nd.lo[k] = a < b ? a : b;
-        a = out[l].hi[k];
-        b = out[r].hi[k];
-        nd.hi[k] = a > b ? a : b;
-    }
-    out[me] = nd;
-    return me;
-}
+};
 }  // namespace
 
 void build_ref_tree(const float* item_boxes, int n, std::vector<RefNode>& out) {
-    out.clear();
-    out.reserve((size_t)n);
-    ref_build(item_boxes, 0, n, out);
+    RefTree t;
+    t.ib = item_boxes;
+    out.resize((size_t)t.nodes.fill(n));
+    t.out = out.data();
+    unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    int forks = 0;
+    while ((1u << forks) < std::min(hw, 32u)) forks++;
+    t.build(0, n, 0, forks);
+}
+
+int ref_tree_levels(long long n, int size_lo[32], int nodes_lo[32], int nodes_hi[32]) {
+    NodeCount nc;
+    int levels = 0;
+    for (int L = 0; L < 32; L++) {
+        const long long m = n >> L;
+        size_lo[L] = (int)m;
+        nodes_lo[L] = (int)nc.fill(m);
+        nodes_hi[L] = (int)nc.fill(m + 1);
+        // nodes exist at level L when the largest subtree one level up, ceil(n / 2^(L-1)), has more than two leaves
+        if (L == 0 || ((n + (1ll << (L - 1)) - 1) >> (L - 1)) > 2) levels = L + 1;
+    }
+    return levels;
 }
 
 // ---- reference bvh_node order replay (bvh.h:96-119) ----------------------------------------------------------
@@ -405,10 +475,7 @@ struct RefOrder {
     std::atomic<int> live{0};
     int max_tasks;
 
-    static long long node_count(long long n) {  // nodes of the subtree over n leaves
-        if (n <= 2) return 1;
-        return 1 + node_count(n / 2) + node_count(n - n / 2);
-    }
+    NodeCount node_count;
 
     void sort_slice(long long lo, long long n, int ax, std::vector<std::pair<float, int32_t>>& tmp) {
         tmp.resize((size_t)n);
@@ -455,7 +522,7 @@ void ref_bvh_leaf_order(const float* mins, long long n, unsigned long long* seed
     R.mins = mins;
     R.order = order_out;
     R.max_tasks = (int)std::max(1u, std::thread::hardware_concurrency());
-    const long long nodes = RefOrder::node_count(n);
+    const long long nodes = R.node_count.fill(n);
     R.axis.resize((size_t)nodes);
     unsigned long long s = *seed & 0xFFFFFFFFFFFFull;
     for (long long k = 0; k < nodes; k++) {  // mathf.h:14-19; the constructor draws before it recurses

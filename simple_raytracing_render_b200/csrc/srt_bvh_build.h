@@ -26,9 +26,24 @@ struct WideBvh {
 // boxes: [n][6] = min xyz, max xyz (already padded by the caller).  n >= 1.
 void build_wide_bvh(const float* boxes, int n, WideBvh& out);
 
+// The binary binned-SAH tree itself (before the collapse), for callers that join it with other subtrees: the
+// device builder (srt_lbvh.cuh) hands it the boxes of its radix-tree clusters with max_leaf = 1.
+// nodes[0] is the root; a leaf has left < 0 and covers order[first .. first + count).
+struct SahBinNode {
+    float lo[3], hi[3];
+    int32_t left, right;
+    int32_t first, count;
+};
+void build_binary_sah(const float* boxes, int n, int max_leaf, std::vector<SahBinNode>& nodes, std::vector<int32_t>& order);
+
 // item_boxes: [n][6] reference leaf boxes in the reference tree's in-order leaf sequence.
 // out[0] is the root; child indices are relative to out[0].
 void build_ref_tree(const float* item_boxes, int n, std::vector<RefNode>& out);
+
+// The shape of that tree level by level, for the device build of large trees (k_ref_tree_level, srt_api.cu): level L
+// holds subtrees of size_lo[L] or size_lo[L] + 1 leaves, which have nodes_lo[L] / nodes_hi[L] nodes.  Returns the
+// number of levels that hold nodes; the tables are filled one level past that.  n < 2^30.
+int ref_tree_levels(long long n, int size_lo[32], int nodes_lo[32], int nodes_hi[32]);
 
 // The in-order leaf sequence of the reference's `new bvh_node(l, n, t0, t1)` (bvh.h:96-119): at every node, in
 // depth-first order, axis = int(3 * drand48()) from the global 48-bit LCG (mathf.h:12-19), qsort of the node's

@@ -354,6 +354,7 @@ _SIGNATURES = {
     "srt_counters_get": (C.c_int, [C.c_void_p, C.POINTER(SrtCounters)]),
     "srt_sobol_points_u32": (C.c_int, [C.c_uint32, C.c_void_p]),
     "srt_ref_bvh_leaf_order": (C.c_int, [C.c_void_p, C.c_int64, C.POINTER(C.c_uint64), C.c_void_p]),
+    "srt_ref_tree_boxes": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int32, C.c_int, C.c_void_p, C.POINTER(C.c_int32)]),
     "srt_merl_lookup": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p, C.c_int64, C.c_void_p]),
     "srt_measure_fp32_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),
     "srt_measure_l2_peak": (C.c_int, [C.c_void_p, C.POINTER(C.c_double)]),

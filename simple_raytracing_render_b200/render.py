@@ -68,6 +68,16 @@ class Context:
         ffi.check(self.lib, self.lib.srt_measure_l2_peak(self.h, C.byref(v)))
         return float(v.value)
 
+    def ref_tree_boxes(self, item_boxes, on_device: bool):
+        """The reference bvh_node tree over leaves in in-order sequence as 12-word records (srt_ref_tree_boxes)."""
+        import numpy as np
+        boxes = np.ascontiguousarray(item_boxes, dtype=np.float32).reshape(-1, 6)
+        out = np.zeros((2 * len(boxes), 12), dtype=np.int32)  # a tree over n leaves has fewer than 2 n nodes
+        count = C.c_int32(0)
+        ffi.check(self.lib, self.lib.srt_ref_tree_boxes(self.h, boxes.ctypes.data, len(boxes), 1 if on_device else 0,
+                                                        out.ctypes.data, C.byref(count)))
+        return out[:count.value]
+
     def resolve(self, accum_dev, n_pixels: int, n_samples: int, rgb8_out):
         ffi.check(self.lib, self.lib.srt_resolve(self.h, _ptr(accum_dev), int(n_pixels), int(n_samples), _ptr(rgb8_out)))
 

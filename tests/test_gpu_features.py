@@ -204,3 +204,46 @@ def test_orennayar_only_scene(gpu_ctx, feat, scheduler, monkeypatch):
     assert c["stack_overflows"] == 0
     assert abs(x.mean() - r.mean()) <= 0.01 * r.mean()
     assert err <= 1e-3
+
+
+# ---- device-side builds of srt_scene_create (large scenes) -------------------------------------------------------
+@pytest.mark.gpu
+@pytest.mark.parametrize("n", [1, 2, 3, 4, 5, 7, 8, 9, 31, 100, 1023, 1025, 32768, 40001, 999999])
+def test_device_reference_tree_equals_host_recursion(gpu_ctx, n):
+    """k_ref_tree_level (one launch per level, node indices from the level tables) writes the same records as the
+    host recursion that follows bvh.h:96-119 step by step: indices, children, split ranks and the box bits."""
+    rng = np.random.default_rng(1000 + n)
+    lo = rng.uniform(-50, 50, size=(n, 3)).astype(np.float32)
+    boxes = np.concatenate([lo, lo + rng.uniform(0, 3, size=(n, 3)).astype(np.float32)], axis=1)
+    host = gpu_ctx.ref_tree_boxes(boxes, on_device=False)
+    dev = gpu_ctx.ref_tree_boxes(boxes, on_device=True)
+    assert host.shape == dev.shape and host.shape[0] >= 1
+    assert np.array_equal(host, dev)
+    # root box = union of the item boxes
+    root = host[0].view(np.float32)
+    assert np.array_equal(root[0:3], boxes[:, :3].min(axis=0)) and np.array_equal(root[4:7], boxes[:, 3:].max(axis=0))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name", ["teapot", "tessellated"])
+def test_device_scene_build_renders_the_same_image(gpu_ctx, name, monkeypatch):
+    """SRT_DEVICE_BVH=1 (device LBVH + per-cluster SAH, device reference tree, device primitive records) and =0 (host
+    builders) are two search orders over the same primitives: closest hits, hence every pixel, are identical."""
+    import torch
+    world, hlist, cam = get_scene(name)
+    flat = S.flatten(world, hlist, cam)
+    nx, ny, ns = 96, 64, 4
+    imgs, infos = [], []
+    for dev in ("1", "0"):
+        monkeypatch.setenv("SRT_DEVICE_BVH", dev)
+        sc = render.Scene(gpu_ctx, flat)
+        infos.append(sc.info())
+        buf = torch.zeros(nx * ny * 3, dtype=torch.int64, device="cuda")
+        sc.render_fixed(render.render_params(nx, ny, ns), buf)
+        gpu_ctx.synchronize()
+        imgs.append(buf.cpu().numpy().copy())
+        sc.close()
+    assert infos[0]["bvh_builder"] == 1 and infos[1]["bvh_builder"] == 0
+    assert np.abs(imgs[0]).max() > 0
+    assert np.array_equal(imgs[0], imgs[1])
+    assert gpu_ctx.counters()["stack_overflows"] == 0
