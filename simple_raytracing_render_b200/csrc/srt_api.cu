@@ -649,19 +649,23 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
                 tmpdev.ptrs.push_back(d_tri_tmp);
                 CUDA_TRY(staged_upload(ctx, d_tri_tmp, d.tri_pos, sizeof(float) * 9 * (size_t)d.n_tris));
             }
-            std::unique_ptr<int32_t[]> rows(new int32_t[(size_t)n]);  // first touched by the threads that fill it
+            std::unique_ptr<int32_t[]> rows(new int32_t[2 * (size_t)n]);  // first touched by the threads that fill it
+            int32_t* item_prim = rows.get() + n;
             parallel_chunks(n, [&](long long lo, long long hi) {
-                for (long long k = lo; k < hi; k++)
-                    rows[(size_t)k] = d.prims[d.groups[d.bvh_items[sb.first_item + k]].first_prim].index;
+                for (long long k = lo; k < hi; k++) {
+                    const int32_t prim = d.groups[d.bvh_items[sb.first_item + k]].first_prim;
+                    item_prim[(size_t)k] = prim;
+                    rows[(size_t)k] = d.prims[prim].index;
+                }
             });
             int32_t* d_rows = nullptr;
-            CUDA_TRY(cudaMalloc(&d_rows, sizeof(int32_t) * (size_t)n));
+            CUDA_TRY(cudaMalloc(&d_rows, sizeof(int32_t) * 2 * (size_t)n));
             tmpdev.ptrs.push_back(d_rows);
-            CUDA_TRY(staged_upload(ctx, d_rows, rows.get(), sizeof(int32_t) * (size_t)n));
+            CUDA_TRY(staged_upload(ctx, d_rows, rows.get(), sizeof(int32_t) * 2 * (size_t)n));
             stage.tick("device build: uploads queued");
             srt_lbvh::DeviceBvh db;
             std::string err;
-            if (!srt_lbvh::build(ctx->stream, d_tri_tmp, d_rows, n, db, err)) return fail(SRT_E_CUDA, "%s", err.c_str());
+            if (!srt_lbvh::build(ctx->stream, d_tri_tmp, d_rows, d_rows + n, n, db, err)) return fail(SRT_E_CUDA, "%s", err.c_str());
             tmpdev.built.push_back(db);
             stage.tick("device build: srt_lbvh::build");
             if (stage.on)
@@ -738,11 +742,18 @@ int srt_scene_create(SrtContext* ctx, const SrtSceneDesc* desc, SrtScene** out) 
             }
         } else if (B.kind == BVH_KIND_TRIANGLE) {
             geom.reserve(3 * (size_t)n);
+            auto bits = [](int32_t v) {
+                float f;
+                std::memcpy(&f, &v, sizeof f);
+                return f;
+            };
             for (int s = 0; s < n; s++) {
-                const SrtPrim& p = d.prims[d.groups[d.bvh_items[sb.first_item + order[s]]].first_prim];
+                const int32_t prim = d.groups[d.bvh_items[sb.first_item + order[s]]].first_prim;
+                const SrtPrim& p = d.prims[prim];
                 const float* q = d.tri_pos + 9 * (size_t)p.index;
-                geom.push_back(float4{q[0], q[1], q[2], 0.f});
-                geom.push_back(float4{q[3], q[4], q[5], 0.f});
+                // the spare words carry the rank and the primitive id (srt_types.h, DBvh)
+                geom.push_back(float4{q[0], q[1], q[2], bits(order[s])});
+                geom.push_back(float4{q[3], q[4], q[5], bits(prim)});
                 geom.push_back(float4{q[6], q[7], q[8], 0.f});
             }
         }

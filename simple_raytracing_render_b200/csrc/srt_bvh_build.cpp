@@ -76,7 +76,7 @@ struct Builder {
     int32_t alloc() { return next_node.fetch_add(1); }
 
     // how many threads a pass over `count` items is worth (the top levels of the tree only)
-    int chunks_for(int count) const { return count >= (1 << 17) ? std::min(max_tasks, std::max(1, count >> 16)) : 1; }
+    int chunks_for(int count) const { return count >= (1 << 15) ? std::min(max_tasks, std::max(1, count >> 13)) : 1; }
 
     // f(first, count, chunk_index) over [first, first + count) split into chunks_for(count) pieces
     template <class F>
@@ -234,7 +234,7 @@ struct Builder {
         }
         int lc = mid - first, rc = count - lc;
         int32_t l, r;
-        bool spawn = lc > 4096 && rc > 4096 && live_tasks.load() < max_tasks;
+        bool spawn = lc > 512 && rc > 512 && live_tasks.load() < max_tasks;
         if (spawn) {
             live_tasks.fetch_add(1);
             auto fut = std::async(std::launch::async, [&, first, lc] { return build(first, lc); });

@@ -438,7 +438,8 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
                 int packed = ~cur;
                 int first = packed >> 3, cnt = packed & 7;
                 for (int s = first; s < first + cnt; s++) {
-                    int rank = __ldg(&ranks[s]);
+                    int rank = 0;
+                    if (kind != BVH_KIND_TRIANGLE) rank = __ldg(&ranks[s]);
                     float tt;
                     int32_t pp;
                     bool h;
@@ -454,7 +455,8 @@ SRT_DEV bool bvh_hit(const View& W, const DBvh& B, const RayK& q, float t_min, f
                         tl.prim();
                         h = tri_hit(v3(a.x, a.y, a.z), v3(b.x, b.y, b.z), v3(c.x, c.y, c.z), r.o, tdir, is_medium, tt, u,
                                     v);
-                        pp = -2;
+                        rank = __float_as_int(a.w);  // rank and primitive id ride in the spare words of the record
+                        pp = __float_as_int(b.w);
                     } else {
                         SrtGroup g = S.groups[__ldg(&S.bvh_items[B.first_item + rank])];
                         h = group_hit<F>(W, g.first_prim, g.prim_count, q, t_min, t_max, is_medium, tt, pp, tl);

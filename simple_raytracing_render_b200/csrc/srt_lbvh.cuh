@@ -565,15 +565,16 @@ __global__ void k_collapse(Tree T, const int2* __restrict__ q_in, int n_in, int2
 
 // leaf_rank[slot] = item (== the reference in-order rank); leaf_geom[3 slot + k] = vertex k of its triangle
 __global__ void k_leaf_arrays(const float* __restrict__ tri_pos, const int32_t* __restrict__ item_row,
-                              const int32_t* __restrict__ vals, int n, int32_t* __restrict__ leaf_rank,
-                              float4* __restrict__ leaf_geom) {
+                              const int32_t* __restrict__ item_prim, const int32_t* __restrict__ vals, int n,
+                              int32_t* __restrict__ leaf_rank, float4* __restrict__ leaf_geom) {
     int s = blockIdx.x * blockDim.x + threadIdx.x;
     if (s >= n) return;
     int item = vals[s];
     leaf_rank[s] = item;
     const float* t = tri_pos + 9 * (size_t)item_row[item];
-    leaf_geom[3 * (size_t)s + 0] = make_float4(t[0], t[1], t[2], 0.f);
-    leaf_geom[3 * (size_t)s + 1] = make_float4(t[3], t[4], t[5], 0.f);
+    // the spare words carry the rank and the primitive id (srt_types.h, DBvh)
+    leaf_geom[3 * (size_t)s + 0] = make_float4(t[0], t[1], t[2], __int_as_float(item));
+    leaf_geom[3 * (size_t)s + 1] = make_float4(t[3], t[4], t[5], __int_as_float(item_prim[item]));
     leaf_geom[3 * (size_t)s + 2] = make_float4(t[6], t[7], t[8], 0.f);
 }
 
@@ -641,9 +642,10 @@ struct Scratch {  // freed on scope exit; one arena for the whole build (a cudaM
         }                                                                      \
     } while (0)
 
-// d_tri_pos: device [rows][9]; d_item_row: device [n] triangle row of item k (items in reference leaf order).
-inline bool build(cudaStream_t st, const float* d_tri_pos, const int32_t* d_item_row, int n, DeviceBvh& out,
-                  std::string& err) {
+// d_tri_pos: device [rows][9]; d_item_row / d_item_prim: device [n] triangle row and primitive id of item k (items in
+// reference leaf order).
+inline bool build(cudaStream_t st, const float* d_tri_pos, const int32_t* d_item_row, const int32_t* d_item_prim, int n,
+                  DeviceBvh& out, std::string& err) {
     using clk = std::chrono::steady_clock;
     auto t0 = clk::now();
     out = DeviceBvh();
@@ -820,7 +822,7 @@ inline bool build(cudaStream_t st, const float* d_tri_pos, const int32_t* d_item
     LBVH_TRY(cudaMemcpyAsync(&out.sah_cost, d_sah, sizeof(float), cudaMemcpyDeviceToHost, st));
     LBVH_TRY(cudaMalloc(&out.leaf_rank, sizeof(int32_t) * (size_t)n));
     LBVH_TRY(cudaMalloc(&out.leaf_geom, sizeof(float4) * 3 * (size_t)n));
-    k_leaf_arrays<<<gb, T, 0, st>>>(d_tri_pos, d_item_row, vals2, n, out.leaf_rank, out.leaf_geom);
+    k_leaf_arrays<<<gb, T, 0, st>>>(d_tri_pos, d_item_row, d_item_prim, vals2, n, out.leaf_rank, out.leaf_geom);
     LBVH_TRY(cudaStreamSynchronize(st));
     LBVH_TRY(cudaGetLastError());
     auto t3 = clk::now();

@@ -133,7 +133,8 @@ enum { BVH_KIND_GENERIC = 0, BVH_KIND_SPHERE = 1, BVH_KIND_TRIANGLE = 2 };
 //   leaf_rank[leaf_base + s]   : rank of the item in the reference tree's in-order leaf sequence
 //                                (== position in bvh_items; ties on t go to the higher rank)
 //   kind SPHERE   : leaf_geom[geom_base + s]            = (cx, cy, cz, r)
-//   kind TRIANGLE : leaf_geom[geom_base + 3*s .. +2]    = (p0, .), (p1, .), (p2, .)
+//   kind TRIANGLE : leaf_geom[geom_base + 3*s .. +2]    = (p0, rank bits), (p1, primitive id bits), (p2, 0): the
+//                   traversal reads neither leaf_rank nor bvh_items / groups for a triangle leaf
 //   kind GENERIC  : the item's group is groups[bvh_items[first_item + rank]]
 struct DBvh {
     int32_t kind;

@@ -8,6 +8,8 @@ from simple_raytracing_render_b200 import render, scene as S
 name = sys.argv[1]
 mode = sys.argv[2] if len(sys.argv) > 2 else "float"
 scene_name, kw, nx, ny, ns, label, _ = bench.config_of(name)
+ns = int(os.environ.get("AB_NS", ns))  # fewer samples per pixel for a profiler run
+reps = int(os.environ.get("AB_REPS", 4))
 stream = torch.cuda.Stream()
 ctx = render.Context(0, stream.cuda_stream)
 if "peaks" in sys.argv:
@@ -17,7 +19,7 @@ sc = render.Scene(ctx, S.flatten(*bench.build_scene(name)))
 params = render.render_params(nx, ny, ns)
 buf = torch.zeros(nx * ny * 3, dtype=torch.int64 if mode == "fixed" else torch.float32, device="cuda")
 with torch.cuda.stream(stream):
-    for k in range(4):
+    for k in range(reps):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record(stream)
         (sc.render_fixed if mode == "fixed" else sc.render)(params, buf)
