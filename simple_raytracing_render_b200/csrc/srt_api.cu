@@ -67,15 +67,11 @@ struct SrtContext {
     int variant_blocks[SRT_N_VARIANTS] = {};  // occupancy query results, 0 = not queried yet
     int variant_regs[SRT_N_VARIANTS] = {};
     size_t variant_smem[SRT_N_VARIANTS] = {};  // dynamic shared memory the query was made with
-    // wavefront path (srt_wavefront.cuh): slot pool, per-pass live counts, host poll words
+    // wavefront path (srt_wavefront.cuh): the slot pool
     uint8_t* d_wf = nullptr;
     size_t wf_cap = 0;
-    int* d_live = nullptr;
-    int* h_poll = nullptr;  // pinned, 2 words
-    cudaEvent_t wf_ev[2] = {nullptr, nullptr};
     WfVariantInfo wf_info[SRT_N_WF_VARIANTS] = {};
     size_t wf_info_smem[SRT_N_WF_VARIANTS] = {};
-    unsigned long long wf_passes = 0;  // passes enqueued by the last wavefront render
     // persisting-L2 window over the slot pool (run_wavefront)
     size_t l2_persist_max = 0, l2_window_max = 0;
     const void* l2_window_base = nullptr;
@@ -496,10 +492,6 @@ int srt_context_destroy(SrtContext* ctx) {
     cudaFree(ctx->d_accum);
     cudaFree(ctx->d_fixed);
     cudaFree(ctx->d_wf);
-    cudaFree(ctx->d_live);
-    if (ctx->h_poll) cudaFreeHost(ctx->h_poll);
-    for (int i = 0; i < 2; i++)
-        if (ctx->wf_ev[i]) cudaEventDestroy(ctx->wf_ev[i]);
     if (ctx->h_rgb8) cudaFreeHost(ctx->h_rgb8);
     for (int i = 0; i < 2; i++) {
         if (ctx->h_stage[i]) cudaFreeHost(ctx->h_stage[i]);
@@ -1424,8 +1416,6 @@ constexpr uint32_t kWfMask[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_MASK(0), SRT_WF_
 constexpr int kWfCounting[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_COUNTING(0), SRT_WF_VARIANT_COUNTING(1),
                                                 SRT_WF_VARIANT_COUNTING(2), SRT_WF_VARIANT_COUNTING(3),
                                                 SRT_WF_VARIANT_COUNTING(4)};
-constexpr int kWfMaxPasses = 1 << 20;
-constexpr int kWfBatch = 8;  // passes enqueued between two polls of the live count
 
 int pick_wf_variant(const SrtScene* s, bool counting) {
     uint32_t need = s->dev.features & F_ALL_SCENE;
@@ -1441,12 +1431,9 @@ int pick_wf_variant(const SrtScene* s, bool counting) {
     return -1;
 }
 
-// The wavefront form of one render (srt_wavefront.cuh): pass 0 fills the slot pool, then
-// trace + shade passes until a shade pass leaves no slot alive.  Passes are enqueued kWfBatch at a
-// time; after each batch the live count of its last pass is copied to pinned memory, and the host
-// waits for the copy of the PREVIOUS batch only, so the stream never drains while work remains.
-int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, int mode) {
-    const bool persistent = mode >= 2;  // 2: k_wf_persist, 3: k_wf_sorted
+// The wavefront form of one render (srt_wavefront.cuh): ONE launch of the persistent sorted kernel, one CTA
+// per SM, every CTA owning per_thread x threads slots of the pool.
+int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v) {
     SrtContext* c = s->ctx;
     const size_t smem = (kWfMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
     WfLaunch L = {};
@@ -1455,27 +1442,23 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, 
     L.sobol = c->d_sobol;
     L.out = out;
     L.counters = c->d_counters;
-    L.smem_bytes = smem;
     L.stream = c->stream;
     // k_wf_sorted keeps its index queues behind the hot tables: Q_N x kSortCap 16-bit entries at most
     const size_t smem_hot16 = (smem + 15) & ~(size_t)15;
     const size_t smem_max = smem_hot16 + (size_t)srt::Q_N * srt::kSortCap * sizeof(unsigned short);
-    if (c->wf_info[v].trace_blocks_per_sm == 0 || smem > c->wf_info_smem[v]) {
-        L.smem_bytes = smem_max;  // opt-in ceiling for every kernel of the variant
+    if (c->wf_info[v].blocks_per_sm == 0 || smem > c->wf_info_smem[v]) {
+        L.smem_bytes = smem_max;  // opt-in ceiling
         cudaError_t e = kWfVariants[v](L, &c->wf_info[v]);
-        L.smem_bytes = smem;
         if (e != cudaSuccess) return fail(SRT_E_CUDA, "wavefront variant %d: %s", v, cudaGetErrorString(e));
         c->wf_info_smem[v] = smem;
     }
     const WfVariantInfo& info = c->wf_info[v];
     const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 4096)) & ~31;
-    // persistent form: every CTA owns per_thread x threads slots
-    const int p_blocks = std::max(1, info.persist_blocks_per_sm), p_threads = std::max(32, info.persist_threads);
-    int per_thread = std::max(1, slots_per_sm / (p_blocks * p_threads));
-    if (mode == 3) per_thread = std::max(1, std::min(per_thread, srt::kSortCap / p_threads));
-    const int p_grid = c->sm_count * p_blocks;
-    const int n_slots = persistent ? p_grid * per_thread * p_threads : c->sm_count * slots_per_sm;
-    const size_t need = (size_t)n_slots * 144;
+    const int threads = std::max(32, info.threads);
+    const int per_thread = std::max(1, std::min(slots_per_sm / threads, srt::kSortCap / threads));
+    const int grid = c->sm_count;
+    const int n_slots = grid * per_thread * threads;
+    const size_t need = (size_t)n_slots * (size_t)info.slot_bytes;
     if (c->wf_cap < need) {
         CUDA_TRY(cudaStreamSynchronize(c->stream));
         cudaFree(c->d_wf);
@@ -1506,70 +1489,30 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v, 
         c->l2_window_base = c->d_wf;
         c->l2_window_bytes = need;
     }
-    if (!c->d_live) {
-        CUDA_TRY(cudaMalloc(&c->d_live, sizeof(int) * kWfMaxPasses));
-        CUDA_TRY(cudaHostAlloc(&c->h_poll, sizeof(int) * 2, cudaHostAllocDefault));
-        CUDA_TRY(cudaEventCreateWithFlags(&c->wf_ev[0], cudaEventDisableTiming));
-        CUDA_TRY(cudaEventCreateWithFlags(&c->wf_ev[1], cudaEventDisableTiming));
-    }
     srt::WfState st;
-    uint8_t* b = c->d_wf;
-    const size_t col = (size_t)n_slots * 16;
-    st.ray_o = (float4*)(b + 0 * col);
-    st.ray_d = (float4*)(b + 1 * col);
-    st.hit = (float4*)(b + 2 * col);
-    st.thr = (float4*)(b + 3 * col);
-    st.rad = (float4*)(b + 4 * col);
-    st.sum = (float4*)(b + 5 * col);
-    st.item = (int4*)(b + 6 * col);
-    st.rng = (uint4*)(b + 7 * col);
+    st.rec = reinterpret_cast<float4*>(c->d_wf);
     st.n_slots = n_slots;
     L.state = &st;
-    L.live = c->d_live;
-    if (persistent) {  // one launch: shade / trace phases alternate inside the kernel (k_wf_persist)
-        L.stage = mode;
-        L.per_thread = per_thread;
-        if (mode == 3) L.smem_bytes = smem_hot16 + (size_t)srt::Q_N * per_thread * p_threads * sizeof(unsigned short);
-        L.grid = p_grid;
-        c->launches++;
-        cudaError_t pe = kWfVariants[v](L, nullptr);
-        if (pe != cudaSuccess) return fail(SRT_E_CUDA, "k_wf_persist (variant %d): %s", v, cudaGetErrorString(pe));
-        c->wf_passes = 0;
-        return 0;
+    L.per_thread = per_thread;
+    L.smem_bytes = smem_hot16 + (size_t)srt::Q_N * per_thread * threads * sizeof(unsigned short);
+    L.grid = grid;
+    c->launches++;
+    cudaError_t pe = kWfVariants[v](L, nullptr);
+    if (pe != cudaSuccess) return fail(SRT_E_CUDA, "k_wf_sorted (variant %d): %s", v, cudaGetErrorString(pe));
+#ifdef SRT_WFS_PHASE_CLOCKS
+    {  // debug build (tools/build_alt.sh clocks -DSRT_WFS_PHASE_CLOCKS): where thread 0 of the CTAs spent its clocks
+        unsigned long long t[6] = {0, 0, 0, 0, 0, 0};
+        CUDA_TRY(cudaMemcpyAsync(t, c->d_counters + 10, sizeof t, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaMemsetAsync(c->d_counters + 10, 0, sizeof t, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        const double tot = (double)(t[0] + t[1] + t[2]);
+        fprintf(stderr, "[k_wf_sorted phases] regenerate %.1f %%, trace %.1f %%, shade %.1f %%; %.1f iterations per CTA, %.3f Mclk per CTA\n",
+                100.0 * t[0] / tot, 100.0 * t[1] / tot, 100.0 * t[2] / tot, (double)t[3] / grid, tot / grid / 1e6);
+        const double warps = (double)(threads / 32);
+        fprintf(stderr, "[k_wf_sorted phases] warps busy: %.1f %% of the trace phase, %.1f %% of the shade phase\n",
+                100.0 * t[4] / (warps * t[1]), 100.0 * t[5] / (warps * t[2]));
     }
-
-    // every pass this render can need: each pass retires at least one ray per live slot
-    CUDA_TRY(cudaMemsetAsync(c->d_live, 0, sizeof(int) * kWfMaxPasses, c->stream));
-    const int blocks_needed = (n_slots + srt::kWfThreads - 1) / srt::kWfThreads;
-    const int grid_trace = std::min(blocks_needed, c->sm_count * std::max(1, info.trace_blocks_per_sm));
-    const int grid_shade = std::min(blocks_needed, c->sm_count * std::max(1, info.shade_blocks_per_sm));
-    auto launch = [&](int stage, int pass) -> cudaError_t {
-        L.stage = stage;
-        L.pass = pass;
-        L.grid = stage == 0 ? grid_trace : grid_shade;
-        c->launches++;
-        return kWfVariants[v](L, nullptr);
-    };
-    cudaError_t e = launch(1, 0);
-    if (e != cudaSuccess) return fail(SRT_E_CUDA, "k_wf_shade (variant %d): %s", v, cudaGetErrorString(e));
-    int pass = 1, batch = 0;
-    bool done = false;
-    while (!done) {
-        if (pass + kWfBatch >= kWfMaxPasses) return fail(SRT_E_UNSUPPORTED, "wavefront render exceeds %d passes", kWfMaxPasses);
-        for (int k = 0; k < kWfBatch; k++, pass++) {
-            e = launch(0, pass);
-            if (e == cudaSuccess) e = launch(1, pass);
-            if (e != cudaSuccess) return fail(SRT_E_CUDA, "wavefront pass %d (variant %d): %s", pass, v, cudaGetErrorString(e));
-        }
-        CUDA_TRY(cudaMemcpyAsync(c->h_poll + (batch & 1), c->d_live + (pass - 1), sizeof(int), cudaMemcpyDeviceToHost, c->stream));
-        CUDA_TRY(cudaEventRecord(c->wf_ev[batch & 1], c->stream));
-        if (batch >= 1) {
-            CUDA_TRY(cudaEventSynchronize(c->wf_ev[(batch - 1) & 1]));
-            done = c->h_poll[(batch - 1) & 1] == 0;
-        }
-        batch++;
-    }
-    c->wf_passes = (unsigned long long)pass;
+#endif
     return 0;
 }
 
@@ -1601,13 +1544,9 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     bool wavefront = wf_env >= 0 ? wf_env != 0 : ((p->flags & SRT_RENDER_WAVEFRONT) != 0 || auto_wavefront(s, p));
     int wv = wavefront ? pick_wf_variant(s, counting) : -1;
     if (wv < 0) wavefront = false;
-    // wavefront form: 1 two kernels per bounce, 2 persistent kernel, 3 persistent kernel with sorted queues
-    int wf_mode = !wavefront ? 0 : (wf_env >= 1 && wf_env <= 3 ? wf_env : env_int("SRT_WF_MODE", 3));
-    if (wf_mode == 3 && std::min(count, env_int("SRT_CHUNK", 1)) > 1) wf_mode = 2;  // the queues hold one path per item
-    if (wavefront && counting && wf_mode != 3) {  // only the sorted scheduler has an instrumented build
-        wavefront = false;
-        wf_mode = 0;
-    }
+    // the queues of k_wf_sorted hold one path per work item: SRT_CHUNK > 1 renders on the fused kernel
+    if (wavefront && std::min(count, env_int("SRT_CHUNK", 1)) > 1) wavefront = false;
+    const int wf_mode = wavefront ? 3 : 0;  // SrtSceneInfo::render_variant = 100 x mode + variant (3: k_wf_sorted)
     int v = pick_variant(s, counting);
     if (v < 0) return fail(SRT_E_UNSUPPORTED, "no render-kernel variant covers feature mask 0x%x", s->dev.features);
     size_t smem = (kVariantMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
@@ -1699,7 +1638,7 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     // counters[7] is the work counter
     CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
     if (wavefront) {
-        int rc2 = run_wavefront(s, A, out, wv, wf_mode);
+        int rc2 = run_wavefront(s, A, out, wv);
         if (rc2) return rc2;
         return finish();
     }

@@ -624,11 +624,13 @@ SRT_DEV bool entry_bounds_hit(const DEntry* ep, const RayK& q, float t_min, floa
 }
 
 // The geometry below an entry's transform chain (group or bvh), without the medium wrapper.
+// `qw` = make_rayk(world_ray): an entry without a transform chain reuses it (the second set of reciprocals was
+// ~50 instructions per ray and entry)
 template <uint32_t F, bool COUNT>
-SRT_DEV bool entry_geom_hit(const View& W, const DEntry* ep, const DEntry& e, const Ray& world_ray, float t_min,
-                            float t_max, bool is_medium, float& t, int32_t& prim, Tally<COUNT> tl) {
-    Ray lr = entry_local_ray<F>(W, e.first_op, e.op_count, world_ray);
-    RayK q = make_rayk(lr);
+SRT_DEV bool entry_geom_hit(const View& W, const DEntry* ep, const DEntry& e, const Ray& world_ray, const RayK& qw,
+                            float t_min, float t_max, bool is_medium, float& t, int32_t& prim, Tally<COUNT> tl) {
+    RayK q = qw;
+    if ((F & F_XFORM) && e.op_count > 0) q = make_rayk(entry_local_ray<F>(W, e.first_op, e.op_count, world_ray));
     if ((e.flags & DENTRY_CULL) && !is_medium && !entry_bounds_hit(ep, q, t_min, t_max, (e.flags & DENTRY_TCULL) != 0))
         return false;
     if (!(F & (F_BVH_SPHERE | F_BVH_TRI | F_BVH_GENERIC)) || e.geom_kind == SRT_GEOM_GROUP)
@@ -640,13 +642,13 @@ SRT_DEV bool entry_geom_hit(const View& W, const DEntry* ep, const DEntry& e, co
 // constant_medium::hit (constant_medium.h:19-50): two boundary hits, then an exponential
 // free-flight distance.  The dead debug draw at :20 is not reproduced (counter RNG).
 template <uint32_t F, bool COUNT>
-SRT_DEV bool medium_hit(const View& W, const DEntry* ep, const DEntry& e, const Ray& r, float t_min, float t_max,
-                        Philox& rng, float& t, Tally<COUNT> tl) {
+SRT_DEV bool medium_hit(const View& W, const DEntry* ep, const DEntry& e, const Ray& r, const RayK& qw, float t_min,
+                        float t_max, Philox& rng, float& t, Tally<COUNT> tl) {
     float t1, t2;
     int32_t p1, p2;
-    if (!entry_geom_hit<F>(W, ep, e, r, -kFltMax, kFltMax, true, t1, p1, tl)) return false;
+    if (!entry_geom_hit<F>(W, ep, e, r, qw, -kFltMax, kFltMax, true, t1, p1, tl)) return false;
     float t_min2 = (float)((double)t1 + 0.0001);
-    if (!entry_geom_hit<F>(W, ep, e, r, t_min2, kFltMax, true, t2, p2, tl)) return false;
+    if (!entry_geom_hit<F>(W, ep, e, r, qw, t_min2, kFltMax, true, t2, p2, tl)) return false;
     if (t1 < t_min) t1 = t_min;
     if (t2 > t_max) t2 = t_max;
     if (t1 >= t2) return false;
@@ -654,6 +656,7 @@ SRT_DEV bool medium_hit(const View& W, const DEntry* ep, const DEntry& e, const 
     float len = length(r.d);
     float distance_inside = xmul(xsub(t2, t1), len);
     float density = W.S.media[e.medium].density;
+    philox_fresh(rng);  // one free-flight draw = one block (srt_math.cuh)
     float hit_distance = (float)(-(double)xdiv(1.0f, density) * log(rand_d(rng)));
     if (hit_distance < distance_inside) {
         t = xadd(t1, xdiv(hit_distance, len));
@@ -679,7 +682,7 @@ SRT_DEV Hit world_hit(const View& W, const Ray& r, float t_min, float t_max, Phi
         int32_t prim = -1;
         bool got;
         if ((F & F_MEDIA) && e.medium >= 0) {
-            got = medium_hit<F>(W, ep, e, r, t_min, closest, rng, t, tl);
+            got = medium_hit<F>(W, ep, e, r, qw, t_min, closest, rng, t, tl);
             prim = W.S.n_prims + e.medium;
         } else if (e.op_count == 0 && e.geom_kind == SRT_GEOM_GROUP) {
             // fast path: untransformed list of primitives shares the world-frame ray constants
@@ -687,7 +690,7 @@ SRT_DEV Hit world_hit(const View& W, const Ray& r, float t_min, float t_max, Phi
                 continue;
             got = group_hit<F>(W, e.first_prim, e.prim_count, qw, t_min, closest, false, t, prim, tl);
         } else {
-            got = entry_geom_hit<F>(W, ep, e, r, t_min, closest, false, t, prim, tl);
+            got = entry_geom_hit<F>(W, ep, e, r, qw, t_min, closest, false, t, prim, tl);
         }
         if (got) {
             closest = t;

@@ -372,6 +372,7 @@ SRT_DEV ShadeStatus shade_hit(const View& W, Path& P, const Hit& h, int max_dept
     }
     // specular materials: return attenuation * color(specular_ray) (emitted is dropped, :66-70)
     if ((F & F_METAL) && m.type == SRT_MAT_METAL) {  // material.h:248-256
+        philox_fresh(rng);
         V3 reflected = reflect(fm::normalize(r.d), rec.normal);
         V3 dir = fm::madd(random_in_unit_sphere(rng), m.p[3], reflected);
         P.thr = fm::mul(P.thr, v3(m.c[0], m.c[1], m.c[2]));
@@ -399,12 +400,14 @@ SRT_DEV ShadeStatus shade_hit(const View& W, Path& P, const Hit& h, int max_dept
             reflect_prob = schlick(cosine, ref_idx);
         else
             reflect_prob = 1.0f;
+        philox_fresh(rng);
         V3 dir = (rand_f(rng) < reflect_prob) ? reflected : refracted;
         P.r = Ray{rec.p, dir, 0.f};
         P.depth++;
         return SHADE_CONTINUES;
     }
     if ((F & F_MEDIA) && m.type == SRT_MAT_ISOTROPIC) {  // material.h:362-367
+        philox_fresh(rng);
         V3 dir = random_in_unit_sphere(rng);
         P.thr = fm::mul(P.thr, material_color<F>(S, m, rec));
         P.r = Ray{rec.p, dir, 0.f};
@@ -448,7 +451,7 @@ SRT_DEV bool shade_sample_iter(const View& W, SampleCtx& C, Philox& rng, Tally<C
     if (W.S.n_lights > 0) {
         if (++C.iters > kMaxRejectIters) return true;
         if (COUNT) tl.c->reject_iters++;
-        philox_fresh(rng);  // one iteration draws at most four numbers (choice, light pick, two coordinates)
+        philox_fresh(rng);  // one attempt = one block: it draws at most four numbers (choice, light pick, two coordinates)
         if (rand_f(rng) < 0.5f)  // pdf.h:183-189
             C.sdir = light_random<F>(W, C.p, rng);
         else
@@ -458,6 +461,7 @@ SRT_DEV bool shade_sample_iter(const View& W, SampleCtx& C, Philox& rng, Tally<C
         C.pdf_val = 0.5f * pl + 0.5f * pb;  // pdf.h:177-182
         return C.pdf_val != 0.f;
     }
+    philox_fresh(rng);
     C.sdir = bsdf_generate<F>(C.B, C.wo, rng);
     C.pdf_val = bsdf_value<F>(C.B, C.wo, C.sdir);
     return true;

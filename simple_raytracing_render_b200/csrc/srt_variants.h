@@ -59,7 +59,7 @@ typedef cudaError_t (*RenderVariantFn)(const RenderLaunch& L, RenderVariantInfo*
 // fetch that more warps hide; the sphere-BVH kernel spills ~1 KB at 64 registers and is best at 2.
 #define SRT_VARIANT_MINBLOCKS(n) ((n) == 1 ? 2 : 4)
 
-// ---- wavefront kernel pairs (srt_wavefront.cuh), one translation unit per mask -----------------------
+// ---- the sorted wavefront kernel (srt_wavefront.cuh), one translation unit per mask -------------------
 struct WfLaunch {
     const DScene* scene;
     const srt::RenderArgs* args;
@@ -67,10 +67,7 @@ struct WfLaunch {
     const uint32_t* sobol;
     long long* out;  // fixed-point accumulation buffer, 3 per pixel
     unsigned long long* counters;
-    int* live;    // live[pass] = slots left alive by shade pass `pass`
-    int pass;
-    int stage;    // 0: trace, 1: shade, 2: the persistent kernel (both stages as phases), 3: its sorted-queue form
-    int per_thread;  // stage 2: slots per thread
+    int per_thread;  // slots per thread of the CTA
     int grid;
     size_t smem_bytes;
     cudaStream_t stream;
@@ -78,10 +75,8 @@ struct WfLaunch {
 
 struct WfVariantInfo {
     uint32_t features;
-    int trace_blocks_per_sm, shade_blocks_per_sm;
-    int trace_registers, shade_registers;
-    int persist_blocks_per_sm, persist_registers, persist_threads;
-    int sorted_blocks_per_sm, sorted_registers;
+    int blocks_per_sm, registers, threads;
+    int slot_bytes;  // bytes of one slot record (srt_wavefront.cuh: kSlotQuads x 16)
 };
 
 typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
@@ -95,12 +90,10 @@ typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
      : (n) == 2 ? (SRT_VM_MESH)                                \
                 : (SRT_VM_FULL))
 #define SRT_WF_VARIANT_COUNTING(n) ((n) == 4)
-// threads of the one persistent CTA per SM (k_wf_persist / k_wf_sorted).  Measured (profiles/r01_notes.md,
+// threads of the one persistent CTA per SM (k_wf_sorted).  Measured (profiles/r01_notes.md,
 // capture K): the sphere-BVH variant needs 107 registers and is best at 640 threads (96 registers, 20
 // warps); the mesh and full variants spill there and are best at 512 (128 registers).
 #define SRT_WF_VARIANT_PERSIST_THREADS(n) ((n) <= 1 ? 640 : 512)
-#define SRT_WF_VARIANT_TRACE_MINBLOCKS(n) 3
-#define SRT_WF_VARIANT_SHADE_MINBLOCKS(n) 3
 
 cudaError_t srt_wavefront_variant_0(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_1(const WfLaunch&, WfVariantInfo*);

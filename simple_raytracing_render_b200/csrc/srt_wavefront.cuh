@@ -1,64 +1,93 @@
-// srt_wavefront.cuh — the render loop as a two-stage wavefront over a fixed pool of path slots.
+// srt_wavefront.cuh — the render loop as a persistent, sorted wavefront over a fixed pool of path slots.
 //
-// Why (profiles/r01_notes.md, captures A-D): the fused kernel of srt_kernels.cuh is bound by
-// instruction fetch — its hot code (37 KB for the sphere-BVH scene, 95 KB for the Beckmann mesh) is
-// larger than the SM's instruction cache, 60 % of its stall samples are `no_instruction`, while the
-// closest-hit code run on its own (k_trace_closest) sustains 10-27 Grays/s, five times the fused rate.
-// Splitting the bounce into a TRACE kernel (world->hit only) and a SHADE kernel (color()'s material /
-// pdf / light-sampling step, path regeneration and ray generation) gives each stage a hot set that
-// fits the instruction cache, and gives the trace stage full warps: a slot whose path ended is
-// refilled in the same shade pass, so every lane of every warp traces a live ray.
+// Why a wavefront (profiles/r01_notes.md, captures A-G): the fused kernel of srt_kernels.cuh is bound by
+// instruction fetch and divergence — its hot code is larger than the SM's instruction cache and its warps
+// sit at unrelated program counters — while the closest-hit code run on its own sustains five times the
+// fused rate.  Here a bounce is split into a TRACE phase (world->hit only) and a SHADE phase (color()'s
+// material / pdf / light-sampling step), both inside ONE persistent kernel, one CTA per SM; barriers keep
+// all warps of the SM in the same phase, so the instruction cache holds one stage's code at a time.
 //
-// State lives in global memory as 16-byte SoA records, 144 B per slot; the pool is sized to the
-// resident threads of the GPU (a few 100 k slots, tens of MB), so it stays in the 126 MB L2 between
-// the passes and HBM sees none of it.  One iteration = one k_wf_trace + one k_wf_shade launch; the
-// host enqueues iterations in batches and polls the live-slot count of an earlier pass, never
-// draining the stream (srt_api.cu: launch_wavefront).
+// State: one record per path slot in global memory (the pool is sized to stay in L2 and carries a
+// persisting access-policy window, srt_api.cu).  A record is kSlotQuads 16-byte words, array-of-structures:
+// a gather touches 3 consecutive 32-byte sectors of one or two lines instead of one sector in each of
+// seven column arrays (round-1 layout; capture L: the gathers held a quarter of the stall samples).
 //
-// Results are the ones of the fused kernel: same work items, same Philox counters (the buffered
-// outputs of a path's generator are part of the slot), same per-item partial sums.
+//   q0  ray origin .xyz, time                        q3  throughput .xyz, depth
+//   q1  ray direction .xyz, Beckmann pdf stash       q4  radiance so far .xyz, Philox block counter
+//   q2  hit t, primitive, entry, sampling attempts   q5  pixel, Sobol index, -, -
+//
+// The generator state of a path between two consumers of random numbers is its BLOCK COUNTER alone: every
+// consumer (camera ray, one specular scatter, one attempt of the sampling loop, one free-flight draw)
+// starts a new Philox block (srt_math.cuh: philox_fresh), so left-over outputs never cross a phase.
+//
+// Every scheduler starts the same paths with the same Philox counters and accumulates in fixed point, so
+// this kernel's image equals the fused kernel's up to float contraction differences between template
+// instantiations (tests/test_gpu_kernels.py).
 #ifndef SRT_WAVEFRONT_CUH
 #define SRT_WAVEFRONT_CUH
 
 #include "srt_kernels.cuh"
 
-// resident CTAs per SM the two kernels are register-bounded for (srt_variants.h picks per variant)
-#ifndef SRT_WF_TRACE_MINBLOCKS
-#define SRT_WF_TRACE_MINBLOCKS 3
+#ifndef SRT_WFP_THREADS
+#define SRT_WFP_THREADS 512
 #endif
-#ifndef SRT_WF_SHADE_MINBLOCKS
-#define SRT_WF_SHADE_MINBLOCKS 3
+#ifndef SRT_WFP_MINBLOCKS
+#define SRT_WFP_MINBLOCKS 1
+#endif
+#ifndef SRT_WFS_TAIL_GRAIN
+#define SRT_WFS_TAIL_GRAIN 32  // 8 and 16 measured slower (most queues are short, they never leave the tail regime)
+#endif
+#ifndef SRT_WFS_TRACE_NEW_FIRST
+#define SRT_WFS_TRACE_NEW_FIRST 0  // 0: continuing (incoherent, slow) rays first, so the phase ends on short groups
+#endif
+#ifndef SRT_WF_SLOT_QUADS
+#define SRT_WF_SLOT_QUADS 6  // 16-byte words per slot record (6 used; 8 = one 128-byte line per record)
+#endif
+#ifndef SRT_WF_SLOT_CG
+#define SRT_WF_SLOT_CG 0  // 1: slot records bypass L1 (ld.global.cg / st.global.cg); measured 0-2.5 % slower (profiles/r02_notes.md)
+#endif
+#ifndef SRT_WFS_SHADE_ORDER
+#define SRT_WFS_SHADE_ORDER 1  // 1: shade queues in the order Beckmann, diffuse, glass, metal, light, miss; 0: enum order
+#endif
+#ifndef SRT_WFS_RETRY
+#define SRT_WFS_RETRY 0  // 1: a rejected sampling attempt re-queues the slot (measured: C4 -4 %, C2 +4 %, C3 +8 %); 0: the warp loops
 #endif
 
 namespace srt {
 
+constexpr int kSlotQuads = SRT_WF_SLOT_QUADS;
+enum { SQ_O = 0, SQ_D, SQ_HIT, SQ_THR, SQ_RAD, SQ_ITEM };
+
 struct WfState {
-    float4* ray_o;  // o.xyz, time
-    float4* ray_d;  // d.xyz, -
-    float4* hit;    // t, prim (int bits), entry (int bits), -
-    float4* thr;    // throughput.xyz, depth (int bits)
-    float4* rad;    // radiance gathered so far .xyz, -
-    float4* sum;    // radiance sum of the current work item .xyz, flags (int bits: 1 alive, 2 has_item)
-    int4* item;     // pixel, chunk_id, s_next, s_stop
-    uint4* rng;     // (c2 << 3) | have, out[0], out[1], out[2]
-    int n_slots;    // multiple of 32
+    float4* rec;  // [n_slots][kSlotQuads]
+    int n_slots;  // multiple of 32
 };
 
-constexpr int kWfThreads = 256;
-constexpr int kWfAlive = 1, kWfHasItem = 2;
-
-SRT_DEV void wf_load_rng(const WfState& st, int slot, uint32_t seed, uint32_t pixel, uint32_t sample, Philox& p) {
-    uint4 v = st.rng[slot];
-    philox_init(p, seed, pixel, sample);
-    p.c2 = v.x >> 3;
-    p.have = (int)(v.x & 7u);
-    p.out[0] = v.y;
-    p.out[1] = v.z;
-    p.out[2] = v.w;
-    p.out[3] = 0;
+SRT_DEV float4 slot_ld(const float4* p) {
+#if SRT_WF_SLOT_CG
+    return __ldcg(p);
+#else
+    return *p;
+#endif
 }
-SRT_DEV void wf_store_rng(const WfState& st, int slot, const Philox& p) {
-    st.rng[slot] = make_uint4((p.c2 << 3) | (uint32_t)p.have, p.out[0], p.out[1], p.out[2]);
+SRT_DEV void slot_st(float4* p, float4 v) {
+#if SRT_WF_SLOT_CG
+    __stcg(p, v);
+#else
+    *p = v;
+#endif
+}
+SRT_DEV void slot_st1(float* p, float v) {
+#if SRT_WF_SLOT_CG
+    __stcg(p, v);
+#else
+    *p = v;
+#endif
+}
+
+SRT_DEV void wf_rng(Philox& p, uint32_t seed, uint32_t pixel, uint32_t sample, uint32_t block) {
+    philox_init(p, seed, pixel, sample);
+    p.c2 = block;
 }
 
 // Stage the hot tables of the scene into shared memory (F_SMEM_TABLES) and return the view.
@@ -79,381 +108,22 @@ SRT_DEV View wf_view(const DScene& S, float4* smem_hot) {
     return global_view(S);
 }
 
-// ---- TRACE: world->hit(r, 0.001, FLT_MAX, rec) (Raytracing_n.cpp:58) for every live slot -----------
-// `live[pass]` is the number of live slots the shade pass `pass` left behind; a trace / shade pass
-// whose predecessor left none (and is not the first) has nothing to do and returns at once: the host
-// may enqueue a few passes more than needed (it polls with a lag), they cost a launch each.
-template <uint32_t F>
-SRT_DEV void wf_trace_slot(const View& W, const RenderArgs& A, const WfState& st, int slot) {
-    Tally<false> tl{nullptr};
-    const int flags = __float_as_int(st.sum[slot].w);
-    if (!(flags & kWfAlive)) return;
-    float4 o = st.ray_o[slot], d = st.ray_d[slot];
-    Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-    Philox rng;
-    rng.have = 0;
-    if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
-        int4 it = st.item[slot];
-        wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)(it.z - 1), rng);
-    }
-    Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
-    st.hit[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f);
-    if (F & F_MEDIA) wf_store_rng(st, slot, rng);
-}
-
-template <uint32_t F>
-__global__ void __launch_bounds__(kWfThreads, SRT_WF_TRACE_MINBLOCKS)
-    k_wf_trace(DScene S, RenderArgs A, WfState st, const int* __restrict__ live, int pass) {
-    extern __shared__ float4 smem_hot[];
-    if (pass > 0 && live[pass - 1] == 0) return;
-    View W = wf_view<F>(S, smem_hot);
-    const int stride = gridDim.x * blockDim.x;
-    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride)
-        wf_trace_slot<F>(W, A, st, slot);
-}
-
-// ---- SHADE: one level of color() for every live slot, then refill ----------------------------------
-// For a live slot: shade_bounce on the hit the trace pass stored (emitted / scatter / mixture sampling,
-// Raytracing_n.cpp:61-99); a path that ends adds de_nan(radiance) to its work item's sum (:841).
-// For a slot without a live path: close the finished work item (write its sum to the item's own
-// partial slot, as the fused kernel does), take the next item from the global counter (one atomic per
-// warp), and start the next path: Sobol jitter + camera::get_ray (:827-836).
-// counters[7] is the work-item counter; live[pass] receives the number of slots left alive.
-// One slot of the shade pass; warp-collective (the refill takes work items with one ballot and one
-// atomic per warp): every lane of the warp must call it, each with its own slot.  Returns whether
-// the slot holds a live path afterwards.
-template <uint32_t F>
-SRT_DEV bool wf_shade_slot(const DScene& S, const View& W, const RenderArgs& A, const WfState& st,
-                           const uint32_t* __restrict__ sobol, long long* __restrict__ out,
-                           unsigned long long* __restrict__ work_counter, int slot, bool first,
-                           volatile int* exhausted = nullptr) {
-    Tally<false> tl{nullptr};
-    const unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const int n_pixels = A.nx * A.ny;
-    float4 sm = st.sum[slot];
-    int flags = first ? 0 : __float_as_int(sm.w);
-    V3 sum = first ? v3(0.f, 0.f, 0.f) : v3(sm.x, sm.y, sm.z);
-    int4 it = first ? make_int4(0, 0, 0, 0) : st.item[slot];
-    int pixel = it.x, chunk_id = it.y, s_next = it.z, s_stop = it.w;
-    bool alive = (flags & kWfAlive) != 0, has_item = (flags & kWfHasItem) != 0;
-    Philox rng;
-    rng.have = 0;
-    Path P;
-    if (alive) {
-        float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
-        P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-        P.thr = v3(tv.x, tv.y, tv.z);
-        P.depth = __float_as_int(tv.w);
-        P.L = v3(lv.x, lv.y, lv.z);
-        Hit h;
-        h.t = hv.x;
-        h.prim = __float_as_int(hv.y);
-        h.entry = __float_as_int(hv.z);
-        wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)(s_next - 1), rng);
-        if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
-            V3 c = de_nan(P.L);
-            sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
-            alive = false;
-        }
-    }
-    // ---- refill (the regeneration phase of srt_kernels.cuh, per lane and without a threshold) ----
-    if (!alive && has_item && s_next >= s_stop) {
-        item_commit(out, pixel, sum, A.fx_clamp);
-        has_item = false;
-    }
-    const bool need_item = !alive && !has_item;
-    const unsigned m = __ballot_sync(FULL, need_item);
-    // `exhausted` (shared memory, persistent kernel): once the counter has run past the last item
-    // the draining warps stop hammering it
-    if (m && !(exhausted && *exhausted)) {
-        unsigned long long base = 0;
-        if (lane == 0) {
-            base = atomicAdd(work_counter, (unsigned long long)__popc(m));
-            if (exhausted && base >= A.n_items) *exhausted = 1;
-        }
-        base = __shfl_sync(FULL, base, 0);
-        const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
-        if (need_item && item < A.n_items) {
-            decode_item(A, item, pixel, chunk_id, s_next, s_stop);
-            sum = v3(0.f, 0.f, 0.f);
-            has_item = true;
-        }
-    }
-    if (!alive && has_item && s_next < s_stop) {
-        int s = s_next++;
-        P.r = start_path(S.camera, A, sobol, pixel, s, rng);
-        P.thr = v3(1.f, 1.f, 1.f);
-        P.L = v3(0.f, 0.f, 0.f);
-        P.depth = 0;
-        alive = true;
-    }
-    // ---- store ------------------------------------------------------------------------------------
-    flags = (alive ? kWfAlive : 0) | (has_item ? kWfHasItem : 0);
-    st.sum[slot] = make_float4(sum.x, sum.y, sum.z, __int_as_float(flags));
-    st.item[slot] = make_int4(pixel, chunk_id, s_next, s_stop);
-    if (alive) {
-        st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
-        st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
-        st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
-        st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
-        wf_store_rng(st, slot, rng);
-        return true;
-    }
-    return false;
-}
-
-template <uint32_t F>
-__global__ void __launch_bounds__(kWfThreads, SRT_WF_SHADE_MINBLOCKS)
-    k_wf_shade(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
-               unsigned long long* __restrict__ counters, int* __restrict__ live, int pass) {
-    extern __shared__ float4 smem_hot[];
-    if (pass > 0 && live[pass - 1] == 0) return;
-    View W = wf_view<F>(S, smem_hot);
-    const int stride = gridDim.x * blockDim.x;
-    int n_alive = 0;
-    // n_slots is a multiple of 32 and blockDim of 32: the warps of this loop are always full
-    for (int slot = blockIdx.x * blockDim.x + threadIdx.x; slot < st.n_slots; slot += stride)
-        n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, slot, pass == 0) ? 1 : 0;
-    const unsigned total = __reduce_add_sync(0xffffffffu, (unsigned)n_alive);
-    if ((threadIdx.x & 31) == 0 && total) atomicAdd(live + pass, (int)total);
-}
-
-
-// ---- PERSISTENT form: the same two stages as phases of ONE kernel ------------------------------------
-// Every CTA owns a private, contiguous range of the slot pool (slot = base + k * blockDim + thread,
-// k < per_thread: a slot is only ever touched by one thread, coalesced across the warp) and
-// alternates   shade phase -> __syncthreads -> trace phase -> __syncthreads   until a shade phase
-// leaves none of its slots alive.  The barriers are not needed for correctness; they keep every warp
-// of the CTA in the same phase, so the SM's instruction cache holds one stage's code at a time
-// (what the two-kernel form buys), without a launch, a table re-staging and a ramp-up/tail per
-// stage and bounce: profiles/r02_notes.md measured ~14 us of those per launch, 1500 launches per
-// C2 frame.  CTAs take work items from the same global counter, so load balance is dynamic and a
-// CTA's tail is bounded by chunk x depth iterations over its own slots only.
-#ifndef SRT_WFP_THREADS
-#define SRT_WFP_THREADS 512
-#endif
-#ifndef SRT_WFP_LANE_SCHED
-#define SRT_WFP_LANE_SCHED 0  // 1: wf_shade_phase (rejection loop scheduled per lane); measured slower, see notes
-#endif
-#ifndef SRT_WFP_DYNAMIC
-#define SRT_WFP_DYNAMIC 1  // warps take 32-slot groups from a shared-memory cursor instead of a fixed mapping
-#endif
-#ifndef SRT_WFS_PREFETCH
-#define SRT_WFS_PREFETCH 0  // 1: gather the next group's rays while the current group is traced; measured 2-4 % slower (8 more live registers spill)
-#endif
-#ifndef SRT_WFS_TAIL_GRAIN
-#define SRT_WFS_TAIL_GRAIN 32  // 8 and 16 measured slower (most queues are short, they never leave the tail regime)
-#endif
-#ifndef SRT_WFS_TRACE_NEW_FIRST
-#define SRT_WFS_TRACE_NEW_FIRST 0  // 0: continuing (incoherent, slow) rays first, so the phase ends on short groups
-#endif
-#ifndef SRT_WFP_MINBLOCKS
-#define SRT_WFP_MINBLOCKS 1
-#endif
-
-// The shade phase of the persistent kernel, for one warp: wf_shade_slot's work, but scheduled per
-// LANE.  A lane that reaches the `while (pdf_val == 0)` rejection loop of color() (:79-84) keeps its
-// slot and runs ONE iteration per trip of the loop below, while the lanes that are done store their
-// slot and fetch the next one from the CTA's cursor.  In the per-slot form the warp waits for its
-// unluckiest lane: the loop ran at 3 of 32 lanes and held a quarter of the kernel's instructions
-// (profiles/r01_notes.md, capture E).  Same paths, same Philox counters, same sums.
-template <uint32_t F>
-SRT_DEV int wf_shade_phase(const DScene& S, const View& W, const RenderArgs& A, const WfState& st,
-                           const uint32_t* __restrict__ sobol, long long* __restrict__ out,
-                           unsigned long long* __restrict__ work_counter, int cta_base, int n_cta_slots, int* cursor,
-                           volatile int* exhausted, bool first) {
-    Tally<false> tl{nullptr};
-    const unsigned FULL = 0xffffffffu;
-    const int lane = threadIdx.x & 31;
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const int n_pixels = A.nx * A.ny;
-    int n_alive = 0;
-    bool sampling = false, more = true;
-    int slot = 0;
-    V3 sum = v3(0.f, 0.f, 0.f);
-    int pixel = 0, chunk_id = 0, s_next = 0, s_stop = 0;
-    bool has_item = false;
-    Philox rng;
-    rng.have = 0;
-    Path P;
-    SampleCtx C;
-    for (;;) {
-        // ---- 1. lanes without a pending vertex take the next slots of this CTA ------------------------
-        const unsigned free_m = __ballot_sync(FULL, !sampling);
-        bool got = false;
-        if (more && free_m) {
-            int base = 0;
-            if (lane == 0) base = atomicAdd(cursor, __popc(free_m));
-            base = __shfl_sync(FULL, base, 0);
-            const int idx = base + __popc(free_m & lt_mask);
-            got = !sampling && idx < n_cta_slots;
-            slot = got ? cta_base + idx : slot;
-            more = base + __popc(free_m) < n_cta_slots;
-        }
-        if (!__ballot_sync(FULL, got || sampling)) break;
-        bool finishing = false, alive = false;
-        if (got) {
-            float4 sm = st.sum[slot];
-            int flags = first ? 0 : __float_as_int(sm.w);
-            sum = first ? v3(0.f, 0.f, 0.f) : v3(sm.x, sm.y, sm.z);
-            int4 it = first ? make_int4(0, 0, 0, 0) : st.item[slot];
-            pixel = it.x, chunk_id = it.y, s_next = it.z, s_stop = it.w;
-            alive = (flags & kWfAlive) != 0;
-            has_item = (flags & kWfHasItem) != 0;
-            finishing = true;
-            if (alive) {
-                float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
-                P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-                P.thr = v3(tv.x, tv.y, tv.z);
-                P.depth = __float_as_int(tv.w);
-                P.L = v3(lv.x, lv.y, lv.z);
-                Hit h;
-                h.t = hv.x;
-                h.prim = __float_as_int(hv.y);
-                h.entry = __float_as_int(hv.z);
-                wf_load_rng(st, slot, A.seed, (uint32_t)pixel, (uint32_t)(s_next - 1), rng);
-                ShadeStatus ss = shade_hit<F>(W, P, h, A.max_depth, rng, C, tl);
-                if (ss == SHADE_SAMPLE) {
-                    sampling = true;
-                    finishing = false;
-                } else if (ss == SHADE_ENDED) {
-                    V3 c = de_nan(P.L);
-                    sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
-                    alive = false;
-                }
-            }
-        }
-        // ---- 2. one iteration of the rejection loop for every lane that holds a diffuse vertex ----------
-        if (sampling && shade_sample_iter<F>(W, C, rng, tl)) {
-            alive = shade_finish<F>(P, C, tl);
-            if (!alive) {
-                V3 c = de_nan(P.L);
-                sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
-            }
-            sampling = false;
-            finishing = true;
-        }
-        // ---- 3. lanes that are through: close / take a work item, start the next path, store ------------
-        if (finishing && !alive && has_item && s_next >= s_stop) {
-            item_commit(out, pixel, sum, A.fx_clamp);
-            has_item = false;
-        }
-        const bool need_item = finishing && !alive && !has_item;
-        const unsigned m = __ballot_sync(FULL, need_item);
-        if (m && !*exhausted) {
-            unsigned long long base = 0;
-            if (lane == 0) {
-                base = atomicAdd(work_counter, (unsigned long long)__popc(m));
-                if (base >= A.n_items) *exhausted = 1;
-            }
-            base = __shfl_sync(FULL, base, 0);
-            const unsigned long long item = base + (unsigned)__popc(m & lt_mask);
-            if (need_item && item < A.n_items) {
-                decode_item(A, item, pixel, chunk_id, s_next, s_stop);
-                sum = v3(0.f, 0.f, 0.f);
-                has_item = true;
-            }
-        }
-        if (finishing) {
-            if (!alive && has_item && s_next < s_stop) {
-                int s = s_next++;
-                P.r = start_path(S.camera, A, sobol, pixel, s, rng);
-                P.thr = v3(1.f, 1.f, 1.f);
-                P.L = v3(0.f, 0.f, 0.f);
-                P.depth = 0;
-                alive = true;
-            }
-            const int flags = (alive ? kWfAlive : 0) | (has_item ? kWfHasItem : 0);
-            st.sum[slot] = make_float4(sum.x, sum.y, sum.z, __int_as_float(flags));
-            st.item[slot] = make_int4(pixel, chunk_id, s_next, s_stop);
-            if (alive) {
-                st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
-                st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
-                st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
-                st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
-                wf_store_rng(st, slot, rng);
-                n_alive++;
-            }
-        }
-    }
-    return n_alive;
-}
-
-template <uint32_t F>
-__global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
-    k_wf_persist(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
-                 unsigned long long* __restrict__ counters, int per_thread) {
-    extern __shared__ float4 smem_hot[];
-    __shared__ int s_exhausted;
-    __shared__ int s_cursor[2];  // next slot of the shade phase / next 32-slot group of the trace phase
-    if (threadIdx.x == 0) s_exhausted = s_cursor[0] = s_cursor[1] = 0;
-    View W = wf_view<F>(S, smem_hot);
-    __syncthreads();
-    const int n_cta_slots = per_thread * blockDim.x;
-    const int cta_base = blockIdx.x * n_cta_slots;
-    const int lane = threadIdx.x & 31;
-    for (int iter = 0;; iter++) {
-#if SRT_WFP_LANE_SCHED
-        const int n_alive = wf_shade_phase<F>(S, W, A, st, sobol, out, counters + 7, cta_base, n_cta_slots, &s_cursor[0],
-                                              &s_exhausted, iter == 0);
-#else
-        int n_alive = 0;
-#if SRT_WFP_DYNAMIC
-        for (;;) {
-            int g = 0;
-            if (lane == 0) g = atomicAdd(&s_cursor[0], 32);
-            g = __shfl_sync(0xffffffffu, g, 0);
-            if (g >= n_cta_slots) break;
-            n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, cta_base + g + lane, iter == 0, &s_exhausted)
-                           ? 1
-                           : 0;
-        }
-#else
-        for (int k = 0; k < per_thread; k++)
-            n_alive += wf_shade_slot<F>(S, W, A, st, sobol, out, counters + 7, cta_base + k * blockDim.x + threadIdx.x,
-                                        iter == 0, &s_exhausted)
-                           ? 1
-                           : 0;
-#endif
-#endif
-        const int any = __syncthreads_or(n_alive);
-        if (threadIdx.x == 0) s_cursor[0] = 0;  // next read after the barrier below
-        if (!any) break;
-        // trace phase: warps take groups of 32 slots until the CTA's range is through
-#if SRT_WFP_DYNAMIC
-        for (;;) {
-            int g = 0;
-            if (lane == 0) g = atomicAdd(&s_cursor[1], 32);
-            g = __shfl_sync(0xffffffffu, g, 0);
-            if (g >= n_cta_slots) break;
-            wf_trace_slot<F>(W, A, st, cta_base + g + lane);
-        }
-#else
-        for (int k = 0; k < per_thread; k++) wf_trace_slot<F>(W, A, st, cta_base + k * blockDim.x + threadIdx.x);
-#endif
-        __syncthreads();
-        if (threadIdx.x == 0) s_cursor[1] = 0;  // next read after the next barrier
-    }
-}
-
-
-// ---- SORTED persistent form: material-sorted shade queues, generation-sorted trace queues ------------
-// k_wf_persist walks its slots in storage order, so a warp shades whatever mix of materials its 32
-// slots happen to hold (capture E: the shading code ran at 6 of 32 lanes) and traces fresh camera
-// rays next to fifth-bounce rays.  Here the CTA keeps, in shared memory, index queues over its own
-// slots (16-bit indices, `kSortCap` per queue):
+// ---- index queues over the CTA's own slots (16-bit indices in shared memory) -------------------------
 //   * the TRACE phase appends every traced slot to the queue of what it hit — miss, light, diffuse,
 //     Beckmann, metal, glass — and the SHADE phase drains those queues one after the other, 32
 //     entries per warp: all lanes of a warp run the same material's code;
-//   * the SHADE phase appends every continuing path to the `cont` queue and every path it starts to
-//     the `new` queue (lanes that start paths together take consecutive work items: neighbouring
-//     samples of one pixel), and the TRACE phase drains `new` first: coherent camera rays stay together.
-// Appends are one ballot + one shared-memory atomic per warp.  A slot without a path is in no queue:
-// the tail of the frame shrinks with the live set.  Requires one path per work item (chunk == 1).
+//   * the SHADE phase appends every continuing path to `cont`, every ended path's slot to `dead` and
+//     every slot whose sampling attempt was rejected (Raytracing_n.cpp:79-84: pdf_val == 0) to `retry`;
+//   * the REGENERATE pass starts new paths in the dead slots and appends them to `new` (consecutive work
+//     items: neighbouring samples of one pixel), and the TRACE phase drains `cont` and `new` separately:
+//     coherent camera rays stay together.
+// Appends are one match + one shared-memory atomic per warp.  A slot without a path is in no queue: the
+// tail of the frame shrinks with the live set.  Requires one path per work item (chunk == 1).
 constexpr int kSortCap = 8192;  // most slots a CTA may own (the queues live in dynamic shared memory)
-enum { SC_DEAD = 0, SC_MISS, SC_LIGHT, SC_DIFFUSE, SC_BECKMANN, SC_METAL, SC_GLASS, SC_N, TC_NEW = SC_N, TC_CONT, Q_N };
+enum {
+    SC_DEAD = 0, SC_MISS, SC_LIGHT, SC_DIFFUSE, SC_BECKMANN, SC_METAL, SC_GLASS, SC_N,
+    TC_NEW = SC_N, TC_CONT, RT_A, RT_B, Q_N
+};
 
 struct SortQueues {
     unsigned short* idx;  // [Q_N][cap], dynamic shared memory behind the hot tables
@@ -486,9 +156,7 @@ SRT_DEV void q_push_class(SortQueues& Q, bool valid, int q, int local_slot) {
 }
 
 // The next entries of queue q for this warp: 32 at a time, and SRT_WFS_TAIL_GRAIN at a time once fewer than
-// one full round of the CTA's warps is left — a group lasts as long as its slowest lane, and the warps
-// that are through wait at the phase barrier for the last group (capture H: 12.7 % of C3's stall samples),
-// so the last entries are spread over all warps in short groups.  Returns false when the queue is drained.
+// one full round of the CTA's warps is left.  Returns false when the queue is drained.
 SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid, int& pos) {
     const int lane = threadIdx.x & 31;
     const int n = Q.count[q];
@@ -525,6 +193,66 @@ SRT_DEV int wf_hit_class(const View& W, const Hit& h) {
     return SC_DIFFUSE;
 }
 
+// One level of color() for one slot of the shade phase with AT MOST ONE attempt of the sampling loop
+// (Raytracing_n.cpp:79-84).  In the fused kernel a warp repeats the loop until its unluckiest lane has a
+// direction of non-zero density: with one rejection in eight the second and third trips run at 4 and 1 of
+// 32 lanes and cost as much as the first (capture L: a fifth of the kernel's instructions ran at 6-12
+// lanes).  Here a rejected attempt returns SHADE_SAMPLE: the caller stores the block counter, the Beckmann
+// stash and the attempt count, and re-queues the slot; the next shade phase re-derives the vertex from the
+// stored hit (shade_hit draws no random numbers before the loop) and makes the next attempt with the next
+// Philox block — the numbers the fused kernel's loop draws, so the path is the same.
+template <uint32_t F, bool COUNT>
+SRT_DEV ShadeStatus shade_attempt(const View& W, Path& P, const Hit& h, int max_depth, Philox& rng, float& stash, int& attempts,
+                                  Tally<COUNT> tl) {
+    SampleCtx C;
+    ShadeStatus st = shade_hit<F>(W, P, h, max_depth, rng, C, tl);
+    if (st != SHADE_SAMPLE) return st;
+#if SRT_WFS_RETRY
+    if (attempts > 0) C.B.stash = stash;
+    C.iters = attempts;
+    if (!shade_sample_iter<F>(W, C, rng, tl)) {
+        stash = C.B.stash;
+        attempts = C.iters;
+        return SHADE_SAMPLE;
+    }
+#else
+    while (!shade_sample_iter<F>(W, C, rng, tl)) {
+    }
+#endif
+    return shade_finish<F>(P, C, tl) ? SHADE_CONTINUES : SHADE_ENDED;
+}
+
+// SRT_WFS_PHASE_CLOCKS: thread 0 of every CTA adds the clock64 ticks it spends in each phase (incl. the wait
+// at the closing barrier) to counters[10..13] (regenerate, trace, shade, iterations): a debug build for
+// profiles/, not the shipped kernel.
+#ifdef SRT_WFS_PHASE_CLOCKS
+#define SRT_PHASE_TICK(i)                                   \
+    do {                                                    \
+        if (threadIdx.x == 0) {                             \
+            const long long now_ = clock64();               \
+            phase_ticks[i] += (unsigned long long)(now_ - phase_t0); \
+            phase_t0 = now_;                                \
+        }                                                   \
+    } while (0)
+// busy clocks of THIS warp inside a phase (first take to last group done): sum over warps / (warps x phase
+// clocks) = how full the SM is kept, i.e. what the closing barrier of the phase costs
+#define SRT_WARP_BUSY_BEGIN() const long long busy_t0_ = clock64()
+#define SRT_WARP_BUSY_END(i)                                                       \
+    do {                                                                           \
+        if (lane == 0) warp_busy[i] += (unsigned long long)(clock64() - busy_t0_); \
+    } while (0)
+#else
+#define SRT_WARP_BUSY_BEGIN() \
+    do {                      \
+    } while (0)
+#define SRT_WARP_BUSY_END(i) \
+    do {                     \
+    } while (0)
+#define SRT_PHASE_TICK(i) \
+    do {                  \
+    } while (0)
+#endif
+
 template <uint32_t F, bool COUNT>
 __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     k_wf_sorted(DScene S, RenderArgs A, WfState st, const uint32_t* __restrict__ sobol, long long* __restrict__ out,
@@ -536,12 +264,17 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     View W = wf_view<F>(S, smem_hot);
     const int lane = threadIdx.x & 31;
     const int cap = per_thread * blockDim.x;  // <= kSortCap (srt_api.cu)
-    const int cta_base = blockIdx.x * cap;
+    float4* const pool = st.rec + (size_t)blockIdx.x * cap * kSlotQuads;  // this CTA's records
     unsigned long long* work_counter = counters + 7;
     // COUNT: the instrumented build of THIS kernel (srt_render_counted): same schedule, same paths, plus the
     // per-thread tallies of SrtCounters (the shipping kernel's own visit / test counters)
     Counters cnt = {0, 0, 0, 0, 0, 0, 0, 0};
     Tally<COUNT> tl{&cnt};
+#ifdef SRT_WFS_PHASE_CLOCKS
+    unsigned long long phase_ticks[4] = {0, 0, 0, 0};
+    unsigned long long warp_busy[3] = {0, 0, 0};
+    long long phase_t0 = clock64();
+#endif
     if (threadIdx.x < Q_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
     if (threadIdx.x == 0) {
         Q.exhausted = 0;
@@ -552,7 +285,10 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     for (int i = threadIdx.x; i < cap; i += blockDim.x) Q.idx[SC_DEAD * cap + i] = (unsigned short)i;
     __syncthreads();
     if (threadIdx.x == 0) Q.count[SC_DEAD] = cap;  // every slot starts without a path
-    for (;;) {
+    for (int iter = 0;; iter++) {
+        // retry queues alternate: the shade phase of this iteration drains rt_drain (filled by the previous
+        // one) and fills rt_fill
+        const int rt_fill = RT_A + (iter & 1), rt_drain = RT_A + ((iter & 1) ^ 1);
         // ---- REGENERATE: every slot whose path ended in the last shade phase (queue SC_DEAD) starts the
         // next path, Raytracing_n.cpp:827-836.  The CTA takes ALL the work items it needs with one atomic
         // on the global counter; queue position i gets item base + i, so the new camera rays of the CTA
@@ -562,6 +298,7 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         // between the two barriers below, so every thread of the CTA sees the same value here.
         const int exhausted_before = Q.exhausted;
         __syncthreads();
+        SRT_PHASE_TICK(2);  // the shade phase ends at this barrier
         if (!exhausted_before) {
             if (threadIdx.x == 0) {
                 const int n = Q.count[SC_DEAD];
@@ -585,19 +322,18 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                     if (pos - lane >= avail) break;  // the rest of the queue gets no item: those slots stay empty
                     const bool start = valid && pos < avail;
                     if (start) {
-                        const int slot = cta_base + ls;
+                        float4* rec = pool + (size_t)ls * kSlotQuads;
                         const unsigned long long item = base + (unsigned)pos;
                         const int pixel = (int)(item / (unsigned)A.n_chunks);
                         const int s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
                         Philox rng;
                         const Ray r = start_path(S.camera, A, sobol, pixel, s, rng);
                         if (COUNT) cnt.paths++;
-                        st.item[slot] = make_int4(pixel, s, 0, 0);
-                        st.ray_o[slot] = make_float4(r.o.x, r.o.y, r.o.z, r.time);
-                        st.ray_d[slot] = make_float4(r.d.x, r.d.y, r.d.z, 0.f);
-                        st.thr[slot] = make_float4(1.f, 1.f, 1.f, __int_as_float(0));
-                        st.rad[slot] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        wf_store_rng(st, slot, rng);
+                        slot_st(rec + SQ_O, make_float4(r.o.x, r.o.y, r.o.z, r.time));
+                        slot_st(rec + SQ_D, make_float4(r.d.x, r.d.y, r.d.z, 0.f));
+                        slot_st(rec + SQ_THR, make_float4(1.f, 1.f, 1.f, __int_as_float(0)));
+                        slot_st(rec + SQ_RAD, make_float4(0.f, 0.f, 0.f, __uint_as_float(rng.c2)));
+                        slot_st(rec + SQ_ITEM, make_float4(__int_as_float(pixel), __int_as_float(s), 0.f, 0.f));
                     }
                     q_push(Q, TC_NEW, start, ls);
                 }
@@ -605,76 +341,65 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         }
         __syncthreads();
         if (threadIdx.x < SC_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;  // all shade queues are consumed
-        const int live = Q.count[TC_NEW] + Q.count[TC_CONT];
+        if (threadIdx.x == rt_fill) Q.count[rt_fill] = Q.cursor[rt_fill] = 0;      // drained by the last shade phase
+        const int live = Q.count[TC_NEW] + Q.count[TC_CONT] + Q.count[rt_drain];
         __syncthreads();
+        SRT_PHASE_TICK(0);
         if (live == 0) break;
         // ---- TRACE: world->hit for every live slot; queue by what was hit ------------------------------
-        // The ray of the NEXT group is fetched (a gather over the L2-resident pool) before the current
-        // group is traced, so its latency is covered by the traversal (capture L: the first uses of the
-        // gathered ray held 8 % of the stall samples).
+        SRT_WARP_BUSY_BEGIN();
         for (int ci = 0; ci < 2; ci++) {
             const int c = (SRT_WFS_TRACE_NEW_FIRST ? ci == 0 : ci == 1) ? TC_NEW : TC_CONT;
             if (Q.count[c] == 0) continue;
-            int ls, pos, ls_next = 0;
-            bool valid, valid_next = false;
-            float4 o = make_float4(0.f, 0.f, 0.f, 0.f), d = o, o_next = o, d_next = o;
-            bool have = q_take(Q, c, ls, valid, pos);
-            if (have && valid) {
-                o = st.ray_o[cta_base + ls];
-                d = st.ray_d[cta_base + ls];
-            }
-            while (have) {
-                const bool have_next = SRT_WFS_PREFETCH ? q_take(Q, c, ls_next, valid_next, pos) : false;
-                if (have_next && valid_next) {
-                    o_next = st.ray_o[cta_base + ls_next];
-                    d_next = st.ray_d[cta_base + ls_next];
-                }
-                const int slot = cta_base + ls;
+            int ls, pos;
+            bool valid;
+            while (q_take(Q, c, ls, valid, pos)) {
+                float4* rec = pool + (size_t)ls * kSlotQuads;
                 int cls = SC_MISS;
                 if (valid) {
+                    const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D);
                     Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
                     Philox rng;
                     rng.have = 0;
                     if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
-                        int4 it = st.item[slot];
-                        wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)it.y, rng);
+                        const float4 lv = slot_ld(rec + SQ_RAD), it = slot_ld(rec + SQ_ITEM);
+                        wf_rng(rng, A.seed, __float_as_uint(it.x), __float_as_uint(it.y), __float_as_uint(lv.w));
                     }
                     if (COUNT) cnt.rays++;
                     Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
-                    st.hit[slot] = make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f);
-                    if (F & F_MEDIA) wf_store_rng(st, slot, rng);
+                    slot_st(rec + SQ_HIT, make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), __int_as_float(0)));
+                    if (F & F_MEDIA) slot_st1(reinterpret_cast<float*>(rec + SQ_RAD) + 3, __uint_as_float(rng.c2));
                     cls = wf_hit_class<F>(W, h);
                 }
                 q_push_class(Q, valid, cls, ls);
-                if (SRT_WFS_PREFETCH) {
-                    have = have_next;
-                    ls = ls_next;
-                    valid = valid_next;
-                    o = o_next;
-                    d = d_next;
-                } else {
-                    have = q_take(Q, c, ls, valid, pos);
-                    if (have && valid) {
-                        o = st.ray_o[cta_base + ls];
-                        d = st.ray_d[cta_base + ls];
-                    }
-                }
             }
         }
+        SRT_WARP_BUSY_END(0);
         __syncthreads();
-        if (threadIdx.x >= TC_NEW && threadIdx.x < Q_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
+        if (threadIdx.x == TC_NEW || threadIdx.x == TC_CONT) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
         __syncthreads();
-        // ---- SHADE: one level of color() per queued slot, material by material -------------------------
-        for (int c = SC_MISS; c < SC_N; c++) {
+        SRT_PHASE_TICK(1);
+        // ---- SHADE: one level of color() per queued slot, material by material.  The expensive classes
+        // first (SRT_WFS_SHADE_ORDER), so that the phase ends on the short groups (miss, light) and the warps
+        // reach its closing barrier close together; slots whose last sampling attempt was rejected first ----
+        {
+        SRT_WARP_BUSY_BEGIN();
+        for (int ci = 0; ci < SC_N; ci++) {
+#if SRT_WFS_SHADE_ORDER
+            constexpr int kOrder[SC_N] = {0, SC_BECKMANN, SC_DIFFUSE, SC_GLASS, SC_METAL, SC_LIGHT, SC_MISS};
+            const int c = ci == 0 ? rt_drain : kOrder[ci];
+#else
+            const int c = ci == 0 ? rt_drain : ci;  // ci == 0 would be SC_DEAD, which the regenerate pass owns
+#endif
             if (Q.count[c] == 0) continue;  // nothing of this material: no trip to the cursor
             int ls, pos;
             bool valid;
             while (q_take(Q, c, ls, valid, pos)) {
-                const int slot = cta_base + ls;
-                bool alive = false;
+                float4* rec = pool + (size_t)ls * kSlotQuads;
+                int dest = SC_DEAD;
                 if (valid) {
-                    float4 o = st.ray_o[slot], d = st.ray_d[slot], hv = st.hit[slot], tv = st.thr[slot], lv = st.rad[slot];
-                    int4 it = st.item[slot];
+                    const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D), hv = slot_ld(rec + SQ_HIT),
+                                 tv = slot_ld(rec + SQ_THR), lv = slot_ld(rec + SQ_RAD), it = slot_ld(rec + SQ_ITEM);
                     Path P;
                     P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
                     P.thr = v3(tv.x, tv.y, tv.z);
@@ -684,23 +409,35 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                     h.t = hv.x;
                     h.prim = __float_as_int(hv.y);
                     h.entry = __float_as_int(hv.z);
+                    const int pixel = __float_as_int(it.x);
                     Philox rng;
-                    wf_load_rng(st, slot, A.seed, (uint32_t)it.x, (uint32_t)it.y, rng);
-                    alive = shade_bounce<F>(W, P, h, A.max_depth, rng, tl);
-                    if (alive) {
-                        st.ray_o[slot] = make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time);
-                        st.ray_d[slot] = make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f);
-                        st.thr[slot] = make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth));
-                        st.rad[slot] = make_float4(P.L.x, P.L.y, P.L.z, 0.f);
-                        wf_store_rng(st, slot, rng);
+                    wf_rng(rng, A.seed, (uint32_t)pixel, __float_as_uint(it.y), __float_as_uint(lv.w));
+                    float stash = d.w;
+                    int attempts = __float_as_int(hv.w);
+                    const ShadeStatus ss = shade_attempt<F>(W, P, h, A.max_depth, rng, stash, attempts, tl);
+                    if (ss == SHADE_CONTINUES) {
+                        slot_st(rec + SQ_O, make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time));
+                        slot_st(rec + SQ_D, make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f));
+                        slot_st(rec + SQ_THR, make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth)));
+                        slot_st(rec + SQ_RAD, make_float4(P.L.x, P.L.y, P.L.z, __uint_as_float(rng.c2)));
+                        dest = TC_CONT;
+                    } else if (ss == SHADE_SAMPLE) {  // rejected attempt: same vertex again in the next shade phase
+                        slot_st1(reinterpret_cast<float*>(rec + SQ_D) + 3, stash);
+                        slot_st1(reinterpret_cast<float*>(rec + SQ_HIT) + 3, __int_as_float(attempts));
+                        slot_st1(reinterpret_cast<float*>(rec + SQ_RAD) + 3, __uint_as_float(rng.c2));
+                        dest = rt_fill;
                     } else {
-                        item_commit(out, it.x, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
+                        item_commit(out, pixel, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
                     }
                 }
-                q_push(Q, TC_CONT, alive, ls);
-                q_push(Q, SC_DEAD, valid && !alive, ls);
+                q_push_class(Q, valid, dest, ls);
             }
         }
+        SRT_WARP_BUSY_END(1);
+        }
+#ifdef SRT_WFS_PHASE_CLOCKS
+        if (threadIdx.x == 0) phase_ticks[3]++;
+#endif
     }
     if (COUNT) {
         atomicAdd(&counters[0], cnt.paths);
@@ -711,6 +448,14 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         atomicAdd(&counters[5], cnt.reject_iters);
         atomicAdd(&counters[6], cnt.culled_rays);
     }
+#ifdef SRT_WFS_PHASE_CLOCKS
+    if (threadIdx.x == 0)
+        for (int i = 0; i < 4; i++) atomicAdd(&counters[10 + i], phase_ticks[i]);
+    if (lane == 0) {
+        atomicAdd(&counters[14], warp_busy[0]);
+        atomicAdd(&counters[15], warp_busy[1]);
+    }
+#endif
 }
 
 }  // namespace srt

@@ -104,15 +104,16 @@ def test_variant_selection_and_agreement(gpu_ctx):
 
 @pytest.mark.parametrize("name", ["cornell", "spheres", "teapot", "soldier", "tessellated"])
 def test_wavefront_scheduler_matches_fused_kernel(gpu_ctx, name):
-    """srt_wavefront.cuh (1: two kernels per bounce, 2: persistent kernel, 3: persistent kernel with sorted
-    queues) against srt_kernels.cuh: same work items, same Philox counters, order-independent fixed-point
-    accumulation -> the same image up to how the compiler contracts float expressions in the different
-    instantiations of the shading code (a handful of pixels may differ where a sample sits on a branch)."""
+    """srt_wavefront.cuh (the persistent kernel with sorted queues, which re-queues rejected sampling attempts)
+    against srt_kernels.cuh (the fused kernel, which loops over them): same work items, same Philox block per
+    consumer, order-independent fixed-point accumulation -> the same image up to how the compiler contracts
+    float expressions in the different instantiations of the shading code (a handful of pixels may differ
+    where a sample sits on a branch)."""
     import torch
     sc = render.Scene.from_objects(gpu_ctx, *get_scene(name))
     nx, ny, ns = 96, 64, 16
     imgs = {}
-    for wf in ("0", "1", "2", "3"):
+    for wf in ("0", "3"):
         os.environ["SRT_WAVEFRONT"] = wf
         buf = torch.zeros(nx * ny * 3, dtype=torch.float32, device="cuda")
         sc.render(render.render_params(nx, ny, ns, flags=0), buf)
@@ -121,7 +122,7 @@ def test_wavefront_scheduler_matches_fused_kernel(gpu_ctx, name):
     os.environ.pop("SRT_WAVEFRONT", None)
     a = imgs["0"][0]
     assert imgs["0"][1] < 100
-    for wf in ("1", "2", "3"):
+    for wf in ("3",):
         b = imgs[wf][0]
         assert imgs[wf][1] // 100 == int(wf)
         close = np.isclose(a, b, rtol=1e-3, atol=1e-4)
