@@ -1453,7 +1453,7 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v) 
         c->wf_info_smem[v] = smem;
     }
     const WfVariantInfo& info = c->wf_info[v];
-    const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 4096)) & ~31;
+    const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 6144)) & ~31;
     const int threads = std::max(32, info.threads);
     const int per_thread = std::max(1, std::min(slots_per_sm / threads, srt::kSortCap / threads));
     const int grid = c->sm_count;

@@ -12,9 +12,8 @@
 // a gather touches 3 consecutive 32-byte sectors of one or two lines instead of one sector in each of
 // seven column arrays (round-1 layout; capture L: the gathers held a quarter of the stall samples).
 //
-//   q0  ray origin .xyz, time                        q3  throughput .xyz, depth
-//   q1  ray direction .xyz, Beckmann pdf stash       q4  radiance so far .xyz, Philox block counter
-//   q2  hit t, primitive, entry, sampling attempts   q5  pixel, Sobol index, -, -
+//   q0  ray origin .xyz, time      q2  hit t, primitive, entry, -      q4  radiance so far .xyz, Philox block counter
+//   q1  ray direction .xyz, -      q3  throughput .xyz, depth          q5  pixel, Sobol index, -, -
 //
 // The generator state of a path between two consumers of random numbers is its BLOCK COUNTER alone: every
 // consumer (camera ray, one specular scatter, one attempt of the sampling loop, one free-flight draw)
@@ -45,12 +44,6 @@
 #endif
 #ifndef SRT_WF_SLOT_CG
 #define SRT_WF_SLOT_CG 0  // 1: slot records bypass L1 (ld.global.cg / st.global.cg); measured 0-2.5 % slower (profiles/r02_notes.md)
-#endif
-#ifndef SRT_WFS_SHADE_ORDER
-#define SRT_WFS_SHADE_ORDER 1  // 1: shade queues in the order Beckmann, diffuse, glass, metal, light, miss; 0: enum order
-#endif
-#ifndef SRT_WFS_RETRY
-#define SRT_WFS_RETRY 0  // 1: a rejected sampling attempt re-queues the slot (measured: C4 -4 %, C2 +4 %, C3 +8 %); 0: the warp loops
 #endif
 
 namespace srt {
@@ -112,17 +105,26 @@ SRT_DEV View wf_view(const DScene& S, float4* smem_hot) {
 //   * the TRACE phase appends every traced slot to the queue of what it hit — miss, light, diffuse,
 //     Beckmann, metal, glass — and the SHADE phase drains those queues one after the other, 32
 //     entries per warp: all lanes of a warp run the same material's code;
-//   * the SHADE phase appends every continuing path to `cont`, every ended path's slot to `dead` and
-//     every slot whose sampling attempt was rejected (Raytracing_n.cpp:79-84: pdf_val == 0) to `retry`;
+//   * the SHADE phase appends every continuing path to `cont` and every ended path's slot to `dead`;
 //   * the REGENERATE pass starts new paths in the dead slots and appends them to `new` (consecutive work
 //     items: neighbouring samples of one pixel), and the TRACE phase drains `cont` and `new` separately:
 //     coherent camera rays stay together.
 // Appends are one match + one shared-memory atomic per warp.  A slot without a path is in no queue: the
 // tail of the frame shrinks with the live set.  Requires one path per work item (chunk == 1).
+//
+// The `cont` queue alternates between two queues by iteration: the shade phase fills the one the NEXT trace
+// phase drains, so the drained one is reset without a barrier of its own.
+//
+// Measured and rejected (profiles/r02_notes.md): letting the warps that are through with the trace phase start
+// shading full groups while the others still trace (the warps of a CTA are busy for only 78-91 % of the trace
+// phase; the rest is the wait at its closing barrier) — 7-13 % SLOWER on every configuration, with or without
+// polling: the two stages' code and data then share the SM's caches again, which is what the phases avoid.
+// Re-queueing a slot whose sampling attempt was rejected (pdf_val == 0, Raytracing_n.cpp:79-84) instead of
+// looping in the warp: -4 % on C4, +4 % on C2, +8 % on C3.
 constexpr int kSortCap = 8192;  // most slots a CTA may own (the queues live in dynamic shared memory)
 enum {
     SC_DEAD = 0, SC_MISS, SC_LIGHT, SC_DIFFUSE, SC_BECKMANN, SC_METAL, SC_GLASS, SC_N,
-    TC_NEW = SC_N, TC_CONT, RT_A, RT_B, Q_N
+    TC_NEW = SC_N, TC_CONT_A, TC_CONT_B, Q_N
 };
 
 struct SortQueues {
@@ -156,7 +158,8 @@ SRT_DEV void q_push_class(SortQueues& Q, bool valid, int q, int local_slot) {
 }
 
 // The next entries of queue q for this warp: 32 at a time, and SRT_WFS_TAIL_GRAIN at a time once fewer than
-// one full round of the CTA's warps is left.  Returns false when the queue is drained.
+// one full round of the CTA's warps is left.  Returns false when the queue is drained.  Only for queues that
+// nobody appends to at the same time.
 SRT_DEV bool q_take(SortQueues& Q, int q, int& local_slot, bool& valid, int& pos) {
     const int lane = threadIdx.x & 31;
     const int n = Q.count[q];
@@ -193,46 +196,53 @@ SRT_DEV int wf_hit_class(const View& W, const Hit& h) {
     return SC_DIFFUSE;
 }
 
-// One level of color() for one slot of the shade phase with AT MOST ONE attempt of the sampling loop
-// (Raytracing_n.cpp:79-84).  In the fused kernel a warp repeats the loop until its unluckiest lane has a
-// direction of non-zero density: with one rejection in eight the second and third trips run at 4 and 1 of
-// 32 lanes and cost as much as the first (capture L: a fifth of the kernel's instructions ran at 6-12
-// lanes).  Here a rejected attempt returns SHADE_SAMPLE: the caller stores the block counter, the Beckmann
-// stash and the attempt count, and re-queues the slot; the next shade phase re-derives the vertex from the
-// stored hit (shade_hit draws no random numbers before the loop) and makes the next attempt with the next
-// Philox block — the numbers the fused kernel's loop draws, so the path is the same.
+// One group of the shade phase: one level of color() (Raytracing_n.cpp:55-106) for the slot of every valid
+// lane, then the slot goes to the `cont` queue the NEXT trace phase drains, or to `dead`.
 template <uint32_t F, bool COUNT>
-SRT_DEV ShadeStatus shade_attempt(const View& W, Path& P, const Hit& h, int max_depth, Philox& rng, float& stash, int& attempts,
-                                  Tally<COUNT> tl) {
-    SampleCtx C;
-    ShadeStatus st = shade_hit<F>(W, P, h, max_depth, rng, C, tl);
-    if (st != SHADE_SAMPLE) return st;
-#if SRT_WFS_RETRY
-    if (attempts > 0) C.B.stash = stash;
-    C.iters = attempts;
-    if (!shade_sample_iter<F>(W, C, rng, tl)) {
-        stash = C.B.stash;
-        attempts = C.iters;
-        return SHADE_SAMPLE;
+SRT_DEV void wf_shade_group(const View& W, const RenderArgs& A, SortQueues& Q, float4* pool, long long* __restrict__ out,
+                            int ls, bool valid, int q_cont, Tally<COUNT> tl) {
+    float4* rec = pool + (size_t)ls * kSlotQuads;
+    int dest = SC_DEAD;
+    if (valid) {
+        const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D), hv = slot_ld(rec + SQ_HIT), tv = slot_ld(rec + SQ_THR),
+                     lv = slot_ld(rec + SQ_RAD), it = slot_ld(rec + SQ_ITEM);
+        Path P;
+        P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+        P.thr = v3(tv.x, tv.y, tv.z);
+        P.depth = __float_as_int(tv.w);
+        P.L = v3(lv.x, lv.y, lv.z);
+        Hit h;
+        h.t = hv.x;
+        h.prim = __float_as_int(hv.y);
+        h.entry = __float_as_int(hv.z);
+        const int pixel = __float_as_int(it.x);
+        Philox rng;
+        wf_rng(rng, A.seed, (uint32_t)pixel, __float_as_uint(it.y), __float_as_uint(lv.w));
+        if (shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
+            slot_st(rec + SQ_O, make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time));
+            slot_st(rec + SQ_D, make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f));
+            slot_st(rec + SQ_THR, make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth)));
+            slot_st(rec + SQ_RAD, make_float4(P.L.x, P.L.y, P.L.z, __uint_as_float(rng.c2)));
+            dest = q_cont;
+        } else {
+            item_commit(out, pixel, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
+        }
     }
-#else
-    while (!shade_sample_iter<F>(W, C, rng, tl)) {
-    }
-#endif
-    return shade_finish<F>(P, C, tl) ? SHADE_CONTINUES : SHADE_ENDED;
+    q_push_class(Q, valid, dest, ls);
 }
 
 // SRT_WFS_PHASE_CLOCKS: thread 0 of every CTA adds the clock64 ticks it spends in each phase (incl. the wait
-// at the closing barrier) to counters[10..13] (regenerate, trace, shade, iterations): a debug build for
+// at the closing barrier) to counters[10..13] (regenerate, trace, shade, iterations), and every warp the
+// clocks between its first take and its last group of a phase to counters[14..15]: a debug build for
 // profiles/, not the shipped kernel.
 #ifdef SRT_WFS_PHASE_CLOCKS
-#define SRT_PHASE_TICK(i)                                   \
-    do {                                                    \
-        if (threadIdx.x == 0) {                             \
-            const long long now_ = clock64();               \
+#define SRT_PHASE_TICK(i)                                            \
+    do {                                                             \
+        if (threadIdx.x == 0) {                                      \
+            const long long now_ = clock64();                        \
             phase_ticks[i] += (unsigned long long)(now_ - phase_t0); \
-            phase_t0 = now_;                                \
-        }                                                   \
+            phase_t0 = now_;                                         \
+        }                                                            \
     } while (0)
 // busy clocks of THIS warp inside a phase (first take to last group done): sum over warps / (warps x phase
 // clocks) = how full the SM is kept, i.e. what the closing barrier of the phase costs
@@ -242,14 +252,14 @@ SRT_DEV ShadeStatus shade_attempt(const View& W, Path& P, const Hit& h, int max_
         if (lane == 0) warp_busy[i] += (unsigned long long)(clock64() - busy_t0_); \
     } while (0)
 #else
+#define SRT_PHASE_TICK(i) \
+    do {                  \
+    } while (0)
 #define SRT_WARP_BUSY_BEGIN() \
     do {                      \
     } while (0)
 #define SRT_WARP_BUSY_END(i) \
     do {                     \
-    } while (0)
-#define SRT_PHASE_TICK(i) \
-    do {                  \
     } while (0)
 #endif
 
@@ -285,10 +295,12 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     for (int i = threadIdx.x; i < cap; i += blockDim.x) Q.idx[SC_DEAD * cap + i] = (unsigned short)i;
     __syncthreads();
     if (threadIdx.x == 0) Q.count[SC_DEAD] = cap;  // every slot starts without a path
+    // shade queues, the expensive classes first, so that the phase ends on the short groups (miss, light)
+    // and the warps reach its closing barrier close together
+    constexpr int kShadeOrder[SC_N - 1] = {SC_BECKMANN, SC_DIFFUSE, SC_GLASS, SC_METAL, SC_LIGHT, SC_MISS};
     for (int iter = 0;; iter++) {
-        // retry queues alternate: the shade phase of this iteration drains rt_drain (filled by the previous
-        // one) and fills rt_fill
-        const int rt_fill = RT_A + (iter & 1), rt_drain = RT_A + ((iter & 1) ^ 1);
+        // `cont` queues alternate: this iteration's trace phase drains tc_cur, its shade phase fills tc_next
+        const int tc_cur = TC_CONT_A + (iter & 1), tc_next = TC_CONT_A + ((iter & 1) ^ 1);
         // ---- REGENERATE: every slot whose path ended in the last shade phase (queue SC_DEAD) starts the
         // next path, Raytracing_n.cpp:827-836.  The CTA takes ALL the work items it needs with one atomic
         // on the global counter; queue position i gets item base + i, so the new camera rays of the CTA
@@ -341,99 +353,56 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
         }
         __syncthreads();
         if (threadIdx.x < SC_N) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;  // all shade queues are consumed
-        if (threadIdx.x == rt_fill) Q.count[rt_fill] = Q.cursor[rt_fill] = 0;      // drained by the last shade phase
-        const int live = Q.count[TC_NEW] + Q.count[TC_CONT] + Q.count[rt_drain];
+        const int live = Q.count[TC_NEW] + Q.count[tc_cur];
         __syncthreads();
         SRT_PHASE_TICK(0);
         if (live == 0) break;
         // ---- TRACE: world->hit for every live slot; queue by what was hit ------------------------------
-        SRT_WARP_BUSY_BEGIN();
-        for (int ci = 0; ci < 2; ci++) {
-            const int c = (SRT_WFS_TRACE_NEW_FIRST ? ci == 0 : ci == 1) ? TC_NEW : TC_CONT;
-            if (Q.count[c] == 0) continue;
-            int ls, pos;
-            bool valid;
-            while (q_take(Q, c, ls, valid, pos)) {
-                float4* rec = pool + (size_t)ls * kSlotQuads;
-                int cls = SC_MISS;
-                if (valid) {
-                    const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D);
-                    Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-                    Philox rng;
-                    rng.have = 0;
-                    if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
-                        const float4 lv = slot_ld(rec + SQ_RAD), it = slot_ld(rec + SQ_ITEM);
-                        wf_rng(rng, A.seed, __float_as_uint(it.x), __float_as_uint(it.y), __float_as_uint(lv.w));
-                    }
-                    if (COUNT) cnt.rays++;
-                    Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
-                    slot_st(rec + SQ_HIT, make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), __int_as_float(0)));
-                    if (F & F_MEDIA) slot_st1(reinterpret_cast<float*>(rec + SQ_RAD) + 3, __uint_as_float(rng.c2));
-                    cls = wf_hit_class<F>(W, h);
-                }
-                q_push_class(Q, valid, cls, ls);
-            }
-        }
-        SRT_WARP_BUSY_END(0);
-        __syncthreads();
-        if (threadIdx.x == TC_NEW || threadIdx.x == TC_CONT) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
-        __syncthreads();
-        SRT_PHASE_TICK(1);
-        // ---- SHADE: one level of color() per queued slot, material by material.  The expensive classes
-        // first (SRT_WFS_SHADE_ORDER), so that the phase ends on the short groups (miss, light) and the warps
-        // reach its closing barrier close together; slots whose last sampling attempt was rejected first ----
         {
-        SRT_WARP_BUSY_BEGIN();
-        for (int ci = 0; ci < SC_N; ci++) {
-#if SRT_WFS_SHADE_ORDER
-            constexpr int kOrder[SC_N] = {0, SC_BECKMANN, SC_DIFFUSE, SC_GLASS, SC_METAL, SC_LIGHT, SC_MISS};
-            const int c = ci == 0 ? rt_drain : kOrder[ci];
-#else
-            const int c = ci == 0 ? rt_drain : ci;  // ci == 0 would be SC_DEAD, which the regenerate pass owns
-#endif
-            if (Q.count[c] == 0) continue;  // nothing of this material: no trip to the cursor
-            int ls, pos;
-            bool valid;
-            while (q_take(Q, c, ls, valid, pos)) {
-                float4* rec = pool + (size_t)ls * kSlotQuads;
-                int dest = SC_DEAD;
-                if (valid) {
-                    const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D), hv = slot_ld(rec + SQ_HIT),
-                                 tv = slot_ld(rec + SQ_THR), lv = slot_ld(rec + SQ_RAD), it = slot_ld(rec + SQ_ITEM);
-                    Path P;
-                    P.r = Ray{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-                    P.thr = v3(tv.x, tv.y, tv.z);
-                    P.depth = __float_as_int(tv.w);
-                    P.L = v3(lv.x, lv.y, lv.z);
-                    Hit h;
-                    h.t = hv.x;
-                    h.prim = __float_as_int(hv.y);
-                    h.entry = __float_as_int(hv.z);
-                    const int pixel = __float_as_int(it.x);
-                    Philox rng;
-                    wf_rng(rng, A.seed, (uint32_t)pixel, __float_as_uint(it.y), __float_as_uint(lv.w));
-                    float stash = d.w;
-                    int attempts = __float_as_int(hv.w);
-                    const ShadeStatus ss = shade_attempt<F>(W, P, h, A.max_depth, rng, stash, attempts, tl);
-                    if (ss == SHADE_CONTINUES) {
-                        slot_st(rec + SQ_O, make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time));
-                        slot_st(rec + SQ_D, make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f));
-                        slot_st(rec + SQ_THR, make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth)));
-                        slot_st(rec + SQ_RAD, make_float4(P.L.x, P.L.y, P.L.z, __uint_as_float(rng.c2)));
-                        dest = TC_CONT;
-                    } else if (ss == SHADE_SAMPLE) {  // rejected attempt: same vertex again in the next shade phase
-                        slot_st1(reinterpret_cast<float*>(rec + SQ_D) + 3, stash);
-                        slot_st1(reinterpret_cast<float*>(rec + SQ_HIT) + 3, __int_as_float(attempts));
-                        slot_st1(reinterpret_cast<float*>(rec + SQ_RAD) + 3, __uint_as_float(rng.c2));
-                        dest = rt_fill;
-                    } else {
-                        item_commit(out, pixel, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
+            SRT_WARP_BUSY_BEGIN();
+            for (int ci = 0; ci < 2; ci++) {
+                const int c = (SRT_WFS_TRACE_NEW_FIRST ? ci == 0 : ci == 1) ? TC_NEW : tc_cur;
+                if (Q.count[c] == 0) continue;
+                int ls, pos;
+                bool valid;
+                while (q_take(Q, c, ls, valid, pos)) {
+                    float4* rec = pool + (size_t)ls * kSlotQuads;
+                    int cls = SC_MISS;
+                    if (valid) {
+                        const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D);
+                        Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+                        Philox rng;
+                        rng.have = 0;
+                        if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
+                            const float4 lv = slot_ld(rec + SQ_RAD), it = slot_ld(rec + SQ_ITEM);
+                            wf_rng(rng, A.seed, __float_as_uint(it.x), __float_as_uint(it.y), __float_as_uint(lv.w));
+                        }
+                        if (COUNT) cnt.rays++;
+                        Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
+                        slot_st(rec + SQ_HIT, make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f));
+                        if (F & F_MEDIA) slot_st1(reinterpret_cast<float*>(rec + SQ_RAD) + 3, __uint_as_float(rng.c2));
+                        cls = wf_hit_class<F>(W, h);
                     }
+                    q_push_class(Q, valid, cls, ls);
                 }
-                q_push_class(Q, valid, dest, ls);
             }
+            SRT_WARP_BUSY_END(0);
         }
-        SRT_WARP_BUSY_END(1);
+        __syncthreads();
+        // the trace queues are drained; nobody appends to them before the next iteration
+        if (threadIdx.x == TC_NEW || threadIdx.x == tc_cur) Q.count[threadIdx.x] = Q.cursor[threadIdx.x] = 0;
+        SRT_PHASE_TICK(1);
+        // ---- SHADE: one level of color() per queued slot, material by material ----------------------------
+        {
+            SRT_WARP_BUSY_BEGIN();
+            for (int ci = 0; ci < SC_N - 1; ci++) {
+                const int c = kShadeOrder[ci];
+                if (Q.count[c] == 0) continue;  // nothing of this material: no trip to the cursor
+                int ls, pos;
+                bool valid;
+                while (q_take(Q, c, ls, valid, pos)) wf_shade_group<F>(W, A, Q, pool, out, ls, valid, tc_next, tl);
+            }
+            SRT_WARP_BUSY_END(1);
         }
 #ifdef SRT_WFS_PHASE_CLOCKS
         if (threadIdx.x == 0) phase_ticks[3]++;
