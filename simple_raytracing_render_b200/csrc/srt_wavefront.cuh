@@ -120,7 +120,11 @@ SRT_DEV View wf_view(const DScene& S, float4* smem_hot) {
 // phase; the rest is the wait at its closing barrier) — 7-13 % SLOWER on every configuration, with or without
 // polling: the two stages' code and data then share the SM's caches again, which is what the phases avoid.
 // Re-queueing a slot whose sampling attempt was rejected (pdf_val == 0, Raytracing_n.cpp:79-84) instead of
-// looping in the warp: -4 % on C4, +4 % on C2, +8 % on C3.
+// looping in the warp: -4 % on C4, +4 % on C2, +8 % on C3.  Filling the tail of the trace phase with the work of
+// the next regenerate pass (the pass leaves 1/8 of the slots empty; a warp that finds the trace queues drained
+// starts 32 new paths there and traces their camera rays at once, same code as the warps still tracing): the
+// warps are then busy for 82-94 % of the phase, but the frame is 0-4 % slower — the emptier pool costs more
+// than the shorter wait gives back.
 constexpr int kSortCap = 8192;  // most slots a CTA may own (the queues live in dynamic shared memory)
 enum {
     SC_DEAD = 0, SC_MISS, SC_LIGHT, SC_DIFFUSE, SC_BECKMANN, SC_METAL, SC_GLASS, SC_N,
