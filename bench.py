@@ -51,9 +51,9 @@ FP32_LANES = 148 * 128 * 2
 CONFIGS = {
     "cornell": ("cornell", {}, "C1 Cornell box 512x512 @ 16 spp", 20),
     "spheres": ("spheres", {}, "C2 random spheres (bvh_node) 1200x800 @ 64 spp", 16),
-    "teapot": ("teapot", {}, "C3 Utah teapot 640k triangles (bvh_node), Beckmann, sky sphere 1024x1024 @ 256 spp", 48),
-    "soldier": ("soldier", {}, "C4-like textured Beckmann mesh + env map + MERL-material floor + glass "
-                               "1920x1080 @ 1024 spp", 48),
+    "teapot": ("teapot", {}, "C3 Utah teapot 640k triangles (bvh_node), Beckmann, sky_2.png sky sphere 1024x1024 @ 256 spp", 48),
+    "soldier": ("soldier", {}, "C4 soldier_scene: Soilder.FBX mesh[0] (3 971 triangles, Beckmann + albedo image) + sky4.jpg env "
+                               "map + MERL-material floor (synthetic table) + glass 1920x1080 @ 1024 spp", 48),
     "tessellated": ("tessellated", {"n_side": 512}, "C5-like tessellated terrain (524 288 triangles) + constant_medium "
                                                     "3840x2160 @ 256 spp", 48),
     "tessellated_10m": ("tessellated", {"n_side": 2237}, "C5 tessellated terrain (10 008 338 triangles) + "
@@ -71,6 +71,11 @@ def config_of(name):
     if name == "tessellated" and os.environ.get("SRT_TESS_NSIDE"):
         kw["n_side"] = int(os.environ["SRT_TESS_NSIDE"])
         label = f"C5 tessellated terrain (2 x {kw['n_side']}^2 triangles) + constant_medium 3840x2160 @ 256 spp"
+    if name == "soldier" and not scenes.real_assets():
+        label = ("C4-like textured Beckmann mesh + env map + MERL-material floor + glass 1920x1080 @ 1024 spp "
+                 "(stand-in assets: assets_cache/ is empty)")
+    if name == "teapot" and not scenes.real_assets():
+        label += " (synthetic sky image: assets_cache/ is empty)"
     nx, ny, ns = scenes.CONFIG_SIZES[scene_name]
     return scene_name, kw, nx, ny, ns, label, prim_bytes
 

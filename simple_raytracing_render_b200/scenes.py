@@ -7,7 +7,8 @@ scene out of REAL reference objects.
 C1 cornell_box_classic   512x512 @ 16     rect walls + 2 rotated boxes + diffuse_light, hitable_pdf light
 C2 random_spheres        1200x800 @ 64    ~490 lambertian / metal / dielectric spheres in one bvh_node
 C3 teapot_beckmann       1024x1024 @ 256  640 000-triangle teapot (teapot.h), Beckmann, sky sphere
-C4 soldier_like          1920x1080 @ 1024 mesh + sky4-like env map + floor with brdfmaterial (MERL)
+C4 soldier_scene         1920x1080 @ 1024 Soilder.FBX mesh + sky4.jpg env map + floor with brdfmaterial (MERL);
+                                          soldier_like: the same layout on stand-in assets when the cache is missing
 C5 tessellated_medium    3840x2160 @ 256  10 M triangles + constant_medium
 """
 from __future__ import annotations
@@ -18,6 +19,7 @@ import os
 
 import numpy as np
 
+from . import assets
 from . import scene as S
 from .scene import (beckmann, box, brdfmaterial, bvh_node, camera, checker_texture, constant_medium, constant_texture, dielectric,
                     diffuse_light, env_sphere, flip_normals, hitable_list, image_texture, lambertian, metal, moving_sphere,
@@ -30,6 +32,7 @@ CONFIG_SIZES = {
     "teapot": (1024, 1024, 256),
     "soldier": (1920, 1080, 1024),
     "tessellated": (3840, 2160, 256),
+    "soldier_wood": (1920, 1080, 1024),  # soldier_scene literally (Oren-Nayar wood floor): parity only
     # parity-only scenes (no BASELINE.json config): every reference class C1-C5 leave out
     "final": (500, 500, 64),
     "zoo": (480, 320, 64),
@@ -119,7 +122,9 @@ def teapot_beckmann(aspect: float = 1.0, divs: int = 100, seed: int = 1):
     gold = beckmann(constant_texture(vec3(0.945, 0.75, 0.336)), 0.01, 0.05)
     brown = lambertian(constant_texture(vec3(0.426, 0.3, 0.254)))
     light = diffuse_light(constant_texture(vec3(40, 40, 40)))
-    sky = diffuse_light(image_texture(synthetic_sky()))
+    # contents/environment_map/sky_2.png (2000 x 1000), decoded by the reference's stb_image (tools/make_assets.py)
+    sky_img = assets.load_cached("sky_2.npy") if assets.have_cached("sky_2.npy") else synthetic_sky()
+    sky = diffuse_light(image_texture(sky_img))
     lst = [
         flip_normals(xz_rect(3, 153, 217, 343, 800, light)),
         xz_rect(0, 555, 0, 555, 0, brown),
@@ -226,6 +231,60 @@ def soldier_like(aspect: float = 16.0 / 9.0, detail: int = 12, seed: int = 1):
     hlist = hitable_list([flip_normals(xz_rect(203, 353, 17, 167, 800, None))], 1)
     cam = camera(lookfrom, vec3(300, 278, 200), vec3(0, 1, 0), 40.0, aspect, 10.0, 1000.0, 0.0, 1.0)
     return world, hlist, cam
+
+
+SOLDIER_ASSETS = ("soldier_mesh.npz", "sky4.npy", "soldier_albedo.npy", "wood_albedo.npy")
+
+
+def real_assets() -> bool:
+    """True when tools/make_assets.py has filled assets_cache/: the mesh / image scenes then use the reference's own
+    blobs (Soilder.FBX, sky4.jpg, sky_2.png, the albedo PNGs); otherwise deterministic stand-ins of the same kind."""
+    return assets.have_cached(*SOLDIER_ASSETS, "sky_2.npy")
+
+
+def soldier_scene(aspect: float = 16.0 / 9.0, floor: str = "merl", seed: int = 1):
+    """C4: soldier_scene (Raytracing_n.cpp:585-657) on the reference's own assets — mesh[0] of Soilder.FBX
+    (FlipWindingOrder, scale 8: model.h:26-57, geometry.h:61-77) with beckmann(image_texture(NPC_YuanChengBing_A.png),
+    0.9, 0.85) in a bvh_node under rotate_y 180 / translate, the sky4.jpg sky sphere around the camera, the glass
+    slab, the sampled flipped xz_rect light, thin-lens camera with aperture 10.
+    floor = "merl": the floor box carries the MERL measured-BRDF material (brdfmaterial) BASELINE.json:configs[3]
+    names — the MERL binaries are not in the reference tree, so the table is synthetic in the MERL layout;
+    floor = "wood": the scene function literally — orennayar(image_texture(Wood_Wenge albedo), 0.5), :620."""
+    S.set_seed(seed)
+    lookfrom = vec3(300, 500, -800)
+    light_1 = diffuse_light(constant_texture(vec3(35, 35, 35)))
+    if floor == "wood":
+        floor_mat = orennayar(image_texture(assets.load_cached("wood_albedo.npy")), 0.5)
+    else:
+        floor_mat = brdfmaterial(synthetic_merl_table(), vec3(0.7, 0.7, 0.72))
+    glass = dielectric(1.4)
+    sky = diffuse_light(image_texture(assets.load_cached("sky4.npy")))
+    skin = beckmann(image_texture(assets.load_cached("soldier_albedo.npy")), 0.9, 0.85)
+    mesh = np.load(assets.cache_path("soldier_mesh.npz"))
+    pos = (mesh["pos"] * np.float32(8.0)).astype(np.float32)  # geometry.h:66: p * scale, in float
+    lst = [
+        flip_normals(xz_rect(203, 353, 17, 167, 800, light_1)),
+        box(vec3(0, -0.1, 0), vec3(600, 0.1, 600), floor_mat),
+        box(vec3(0, -1, 0), vec3(600, 1, 600), glass),
+        flip_normals(sphere(lookfrom, 10000, sky)),
+        translate(rotate_y(triangle_soup(pos, skin, uv=mesh["uv"], nrm=mesh["nrm"]), 180), vec3(250, 0, 300)),
+    ]
+    world = hitable_list(lst, len(lst))
+    hlist = hitable_list([flip_normals(xz_rect(203, 353, 17, 167, 800, None))], 1)
+    cam = camera(lookfrom, vec3(300, 278, 200), vec3(0, 1, 0), 40.0, aspect, 10.0, 1000.0, 0.0, 1.0)
+    return world, hlist, cam
+
+
+def soldier(aspect: float = 16.0 / 9.0, **kw):
+    """C4 on the reference's assets when they are cached, on the stand-ins otherwise (real_assets())."""
+    if assets.have_cached(*SOLDIER_ASSETS):
+        return soldier_scene(aspect, **kw)
+    kw.pop("floor", None)
+    return soldier_like(aspect, **kw)
+
+
+def soldier_wood(aspect: float = 16.0 / 9.0, **kw):
+    return soldier_scene(aspect, floor="wood", **kw)
 
 
 def terrain_triangles(n_side: int) -> np.ndarray:
@@ -452,7 +511,7 @@ def medium_probe(boundary_kind: str = "sphere", density: float = 0.7):
 
 def by_name(name: str, **kw):
     fn = {"cornell": cornell_box_classic, "spheres": random_spheres, "teapot": teapot_beckmann,
-          "soldier": soldier_like, "tessellated": tessellated_medium, "final": book_final, "zoo": feature_zoo,
+          "soldier": soldier, "soldier_wood": soldier_wood, "tessellated": tessellated_medium, "final": book_final, "zoo": feature_zoo,
           "zoo_env": zoo_env}.get(name)
     if fn is None:
         raise KeyError(name)

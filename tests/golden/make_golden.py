@@ -173,7 +173,8 @@ if __name__ == "__main__":
         sys.exit(0)
     if only:
         cfg = {"cornell": (64, 64, 2, 4096, 48, 48), "spheres": (96, 64, 2, 16384, 48, 32), "teapot": (96, 96, 1, 4096, 40, 40),
-               "soldier": (96, 54, 2, 4096, 48, 27), "tessellated": (96, 54, 2, 4096, 48, 27),
+               "soldier": (96, 54, 2, 4096, 48, 27), "soldier_wood": (96, 54, 2, 4096, 48, 27),
+               "tessellated": (96, 54, 2, 4096, 48, 27),
                "final": (96, 96, 2, 65536, 24, 24, True), "zoo": (96, 64, 2, 4096, 48, 32, True),
                "zoo_env": (96, 64, 2, 4096, 48, 32, True)}
         for name in only:
@@ -185,6 +186,7 @@ if __name__ == "__main__":
     scene_vectors("spheres", 96, 64, 2, 16384, 48, 32)
     scene_vectors("teapot", 96, 96, 1, 4096, 40, 40)
     scene_vectors("soldier", 96, 54, 2, 4096, 48, 27)
+    scene_vectors("soldier_wood", 96, 54, 2, 4096, 48, 27)
     scene_vectors("tessellated", 96, 54, 2, 4096, 48, 27)
     scene_vectors("final", 96, 96, 2, 65536, 24, 24, True)
     scene_vectors("zoo", 96, 64, 2, 4096, 48, 32, True)

@@ -7,7 +7,7 @@ from simple_raytracing_render_b200 import ffi, scene as S, scenes
 
 
 @pytest.mark.parametrize("name,kw", [("cornell", {}), ("spheres", {}), ("teapot", {"divs": 12}),
-                                     ("soldier", {"detail": 4}), ("tessellated", {"n_side": 16}),
+                                     ("soldier", {}), ("tessellated", {"n_side": 16}),
                                      ("final", {}), ("zoo", {}), ("zoo_env", {})])
 def test_python_and_cpp_flatteners_agree(oracle, name, kw):
     world, hlist, cam = scenes.by_name(name, **kw)

@@ -83,7 +83,9 @@ def test_golden_scene_vectors_match_live_reference(oracle):
     """The committed closest-hit vectors are what the reference computes today."""
     from simple_raytracing_render_b200 import scenes
     from conftest import get_ref_scene, trace_name
-    for name in ("cornell", "spheres", "teapot", "soldier", "tessellated", "final", "zoo", "zoo_env"):
+    for name in ("cornell", "spheres", "teapot", "soldier", "soldier_wood", "tessellated", "final", "zoo", "zoo_env"):
+        if name in ("teapot", "soldier", "soldier_wood") and not scenes.real_assets():
+            continue  # their goldens use the reference's own asset blobs (tools/make_assets.py)
         g = np.load(os.path.join(GOLDEN, f"{name}.npz"))
         rs = get_ref_scene(oracle, trace_name(name))
         n = 2000
