@@ -163,7 +163,17 @@ inline void CRender::Run() {
         finishedPixel = nx * ny;
         isfinished = true;
     }
-    if (rc == 0 && filePath) {
+    // `.pnm` / `.p6`: binary PPM (3 bytes per pixel instead of ~12 characters); anything else, e.g. the `.ppm` the
+    // reference writes, is its own P3 text format
+    const std::string path_s = filePath ? filePath : "";
+    const bool binary = path_s.size() >= 4 && (path_s.compare(path_s.size() - 4, 4, ".pnm") == 0 ||
+                                               path_s.compare(path_s.size() - 3, 3, ".p6") == 0);
+    if (rc == 0 && filePath && binary) {
+        outfile.open(filePath, std::ios_base::out | std::ios_base::binary);
+        outfile << "P6\n" << nx << " " << ny << "\n255\n";
+        outfile.write(reinterpret_cast<const char*>(rgb.data()), (std::streamsize)rgb.size());
+        outfile.close();
+    } else if (rc == 0 && filePath) {
         outfile.open(filePath, std::ios_base::out);
         outfile << "P3\n" << nx << " " << ny << "\n255\n";  // Raytracing_n.cpp:886
         std::string text;

@@ -12,6 +12,7 @@ without a GPU.
 from __future__ import annotations
 
 import ctypes as C
+import os
 import time
 from typing import Optional
 
@@ -217,6 +218,46 @@ def write_ppm_p3(path: str, rgb8: np.ndarray, nx: int, ny: int):
         fh.write("\n")
 
 
+def write_ppm_p6(path: str, rgb8: np.ndarray, nx: int, ny: int):
+    """Binary PPM: the same pixels as the P3 dump (Raytracing_n.cpp:873-876) in 3 bytes per pixel instead of
+    ~12 characters."""
+    rgb8 = np.ascontiguousarray(np.asarray(rgb8, np.uint8).reshape(-1))
+    if rgb8.size != nx * ny * 3:
+        raise ValueError("image size does not match nx * ny * 3")
+    with open(path, "wb") as fh:
+        fh.write(f"P6\n{nx} {ny}\n255\n".encode())
+        fh.write(rgb8.tobytes())
+
+
+def write_png(path: str, rgb8: np.ndarray, nx: int, ny: int):
+    """8-bit RGB PNG (one IDAT, filter type 0 on every row, zlib level 6)."""
+    import struct
+    import zlib
+    rows = np.ascontiguousarray(np.asarray(rgb8, np.uint8).reshape(ny, nx * 3))
+    raw = np.concatenate([np.zeros((ny, 1), np.uint8), rows], axis=1).tobytes()
+
+    def chunk(tag: bytes, data: bytes) -> bytes:
+        return struct.pack(">I", len(data)) + tag + data + struct.pack(">I", zlib.crc32(tag + data) & 0xFFFFFFFF)
+
+    with open(path, "wb") as fh:
+        fh.write(b"\x89PNG\r\n\x1a\n")
+        fh.write(chunk(b"IHDR", struct.pack(">IIBBBBB", nx, ny, 8, 2, 0, 0, 0)))
+        fh.write(chunk(b"IDAT", zlib.compress(raw, 6)))
+        fh.write(chunk(b"IEND", b""))
+
+
+def write_image(path: str, rgb8: np.ndarray, nx: int, ny: int):
+    """By extension: .png -> PNG, .pnm / .p6 -> binary PPM, anything else (the reference writes `.ppm`) -> the
+    reference's own P3 text format."""
+    ext = os.path.splitext(path)[1].lower()
+    if ext == ".png":
+        write_png(path, rgb8, nx, ny)
+    elif ext in (".pnm", ".p6"):
+        write_ppm_p6(path, rgb8, nx, ny)
+    else:
+        write_ppm_p3(path, rgb8, nx, ny)
+
+
 class CRender:
     """Render.h:16-51.  `Run()` renders the registered scene on the GPU and writes the P3 file the
     reference's main() writes; `thread_count` only sized the reference's CPU pool and is ignored."""
@@ -248,7 +289,7 @@ class CRender:
             ctx.close()
         self.colors = rgb8
         if self.filePath:
-            write_ppm_p3(self.filePath, rgb8, self.nx, self.ny)
+            write_image(self.filePath, rgb8, self.nx, self.ny)  # P3 text for `.ppm`, as main() writes it
         self.finishedPixel, self.isfinished = self.nx * self.ny, True
         self.elapsed_ms = int((time.time() - t0) * 1000)
         print(f"{self.elapsed_ms}ms")  # Raytracing_n.cpp:944-946
