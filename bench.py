@@ -210,9 +210,11 @@ def algorithmic_work(counters, n_pixels, prim_bytes):
     return state + geometry, fl, state
 
 
-def measured_traffic(config, kernel):
+def measured_traffic(config, kernel, spp):
     """dram__bytes_read.sum + dram__bytes_write.sum of ONE single-GPU launch of the dominant kernel, from the
-    committed ncu --set full capture of this configuration (profiles/traffic.json, tools/ncu_traffic.py)."""
+    committed ncu --set full capture of this configuration (profiles/traffic.json, tools/ncu_traffic.py).  A capture
+    taken at fewer samples per pixel (`captured_spp`: short replays for the long frames) is scaled to the frame's
+    spp: this kernel's DRAM traffic is proportional to the paths it runs."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
     try:
         with open(path) as f:
@@ -221,12 +223,15 @@ def measured_traffic(config, kernel):
         return None
     if not rec or rec.get("kernel") != kernel:
         return None
-    return rec.get("dram_bytes_per_launch")
+    b = rec.get("dram_bytes_per_launch")
+    if b is not None and rec.get("captured_spp"):
+        b = b * spp / float(rec["captured_spp"])
+    return b
 
 
-def make_roofline(name, cnt, n_pixels, prim_bytes, kernel_s, kernel_name, shard_frac, hw):
+def make_roofline(name, cnt, n_pixels, prim_bytes, kernel_s, kernel_name, shard_frac, hw, spp):
     abytes, aflops, state_bytes = algorithmic_work(cnt, n_pixels, prim_bytes)
-    traffic = measured_traffic(name, kernel_name)
+    traffic = measured_traffic(name, kernel_name, spp)
     if traffic is not None and shard_frac < 1.0:
         traffic = traffic * shard_frac  # a rank renders shard_frac of the frame's samples: traffic of ITS launch
     fp32 = {"achieved": aflops / kernel_s / 1e12, "peak": hw["fp32_tflops"], "unit": "TFLOP/s",
@@ -462,7 +467,7 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
             "e2e": {"value": paths_per_step / e2e_s, "unit": "paths/s", "ms_per_step": e2e_s * 1e3, "steps": e2e_steps,
                     "h2d_bytes_per_step": int(info["device_bytes"]), "d2h_bytes_per_step": int(n_pixels * 3),
                     "parts_ms": {k: v / e2e_steps for k, v in parts.items()}},
-            "roofline": make_roofline(name, cnt, n_pixels, prim_bytes, kernel_ms * 1e-3, kernel_name, shard_frac, rt.hw),
+            "roofline": make_roofline(name, cnt, n_pixels, prim_bytes, kernel_ms * 1e-3, kernel_name, shard_frac, rt.hw, ns),
             "counters": {k: cnt[k] for k in ("paths", "rays", "culled_rays", "probe_rays", "node_visits", "prim_tests",
                                              "reject_iters")},
             "counters_from": "instrumented build of " + kernel_name + " (srt_render_counted), rank 0's shard",
