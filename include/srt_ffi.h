@@ -236,6 +236,12 @@ typedef struct SrtSceneDesc {
 #define SRT_RENDER_WAVEFRONT 2u    /* ask for the persistent sorted wavefront instead of the per-thread
                                       path loop; without the flag the backend picks it for scenes with an
                                       acceleration structure from 2^20 paths per call up.  Same image either way. */
+#define SRT_RENDER_CORRECTED 4u    /* corrected-transport mode, explicitly OUTSIDE parity with the reference:
+                                      cosine-weighted hemisphere sampling about the face-forward normal instead of
+                                      pdf.h:10-18 / :47-56, next-event estimation with a traced shadow ray and
+                                      balance-heuristic MIS instead of the `while (pdf_val == 0)` loop of
+                                      Raytracing_n.cpp:75-84, the microfacet BRDF value and the MERL value
+                                      (discarded at material.h:231-232) actually applied */
 
 typedef struct SrtRenderParams {
     int32_t nx, ny;      /* Raytracing_n.cpp:39-40 */

@@ -1380,13 +1380,13 @@ int check_params(const SrtRenderParams* p) {
 
 const RenderVariantFn kVariants[SRT_N_VARIANTS] = {srt_render_variant_0, srt_render_variant_1, srt_render_variant_2,
                                                     srt_render_variant_3, srt_render_variant_4, srt_render_variant_5,
-                                                    srt_render_variant_6};
+                                                    srt_render_variant_6, srt_render_variant_7};
 constexpr uint32_t kVariantMask[SRT_N_VARIANTS] = {SRT_VARIANT_MASK(0), SRT_VARIANT_MASK(1), SRT_VARIANT_MASK(2),
                                                    SRT_VARIANT_MASK(3), SRT_VARIANT_MASK(4), SRT_VARIANT_MASK(5),
-                                                   SRT_VARIANT_MASK(6)};
+                                                   SRT_VARIANT_MASK(6), SRT_VARIANT_MASK(7)};
 constexpr int kVariantCounting[SRT_N_VARIANTS] = {SRT_VARIANT_COUNTING(0), SRT_VARIANT_COUNTING(1), SRT_VARIANT_COUNTING(2),
                                                   SRT_VARIANT_COUNTING(3), SRT_VARIANT_COUNTING(4), SRT_VARIANT_COUNTING(5),
-                                                  SRT_VARIANT_COUNTING(6)};
+                                                  SRT_VARIANT_COUNTING(6), SRT_VARIANT_COUNTING(7)};
 constexpr size_t kMaxHotSmem = 64 * 1024;  // above this the hot tables stay in global memory
 
 int env_int(const char* name, int fallback) {
@@ -1395,8 +1395,8 @@ int env_int(const char* name, int fallback) {
 }
 
 // The smallest compiled variant whose mask covers the scene (first match in list order).
-int pick_variant(const SrtScene* s, bool counting) {
-    uint32_t need = s->dev.features & F_ALL_SCENE;
+int pick_variant(const SrtScene* s, bool counting, bool corrected = false) {
+    uint32_t need = (s->dev.features & F_ALL_SCENE) | (corrected ? (uint32_t)F_CORRECTED : 0u);
     bool smem_ok = s->dev.hot_bytes <= kMaxHotSmem && !env_int("SRT_NO_SMEM", 0);
     int forced = env_int("SRT_VARIANT", -1);
     for (int v = 0; v < SRT_N_VARIANTS; v++) {
@@ -1404,21 +1404,22 @@ int pick_variant(const SrtScene* s, bool counting) {
         if (kVariantCounting[v] != (counting ? 1 : 0)) continue;
         if ((kVariantMask[v] & F_SMEM_TABLES) && !smem_ok) continue;
         if ((kVariantMask[v] & need) != need) continue;
+        if (((kVariantMask[v] & F_CORRECTED) != 0) != corrected) continue;
         return v;
     }
     return -1;
 }
 
 const WfVariantFn kWfVariants[SRT_N_WF_VARIANTS] = {srt_wavefront_variant_0, srt_wavefront_variant_1, srt_wavefront_variant_2,
-                                                     srt_wavefront_variant_3, srt_wavefront_variant_4};
+                                                     srt_wavefront_variant_3, srt_wavefront_variant_4, srt_wavefront_variant_5};
 constexpr uint32_t kWfMask[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_MASK(0), SRT_WF_VARIANT_MASK(1), SRT_WF_VARIANT_MASK(2),
-                                                 SRT_WF_VARIANT_MASK(3), SRT_WF_VARIANT_MASK(4)};
+                                                 SRT_WF_VARIANT_MASK(3), SRT_WF_VARIANT_MASK(4), SRT_WF_VARIANT_MASK(5)};
 constexpr int kWfCounting[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_COUNTING(0), SRT_WF_VARIANT_COUNTING(1),
                                                 SRT_WF_VARIANT_COUNTING(2), SRT_WF_VARIANT_COUNTING(3),
-                                                SRT_WF_VARIANT_COUNTING(4)};
+                                                SRT_WF_VARIANT_COUNTING(4), SRT_WF_VARIANT_COUNTING(5)};
 
-int pick_wf_variant(const SrtScene* s, bool counting) {
-    uint32_t need = s->dev.features & F_ALL_SCENE;
+int pick_wf_variant(const SrtScene* s, bool counting, bool corrected = false) {
+    uint32_t need = (s->dev.features & F_ALL_SCENE) | (corrected ? (uint32_t)F_CORRECTED : 0u);
     bool smem_ok = s->dev.hot_bytes <= kMaxHotSmem && !env_int("SRT_NO_SMEM", 0);
     int forced = counting ? -1 : env_int("SRT_WF_VARIANT", -1);
     for (int v = 0; v < SRT_N_WF_VARIANTS; v++) {
@@ -1426,6 +1427,7 @@ int pick_wf_variant(const SrtScene* s, bool counting) {
         if (kWfCounting[v] != (counting ? 1 : 0)) continue;
         if ((kWfMask[v] & F_SMEM_TABLES) && !smem_ok) continue;
         if ((kWfMask[v] & need) != need) continue;
+        if (((kWfMask[v] & F_CORRECTED) != 0) != corrected) continue;
         return v;
     }
     return -1;
@@ -1542,12 +1544,20 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     int wf_env = env_int("SRT_WAVEFRONT", -1);
     // a counted replay runs on the instrumented build of the scheduler the plain call would pick
     bool wavefront = wf_env >= 0 ? wf_env != 0 : ((p->flags & SRT_RENDER_WAVEFRONT) != 0 || auto_wavefront(s, p));
-    int wv = wavefront ? pick_wf_variant(s, counting) : -1;
+    // corrected-transport mode has no instrumented build: a counted replay of it is refused below
+    const bool corrected = (p->flags & SRT_RENDER_CORRECTED) != 0;
+    if (corrected && counting) return fail(SRT_E_UNSUPPORTED, "srt_render_counted: no instrumented build of the corrected-transport mode");
+    // the estimator needs a real density for every shape it samples: env_sphere::pdf_value is the constant 1
+    // (env_sphere.h:48-50) and shapes without pdf_value / random return 0 / (1,0,0) (hitable.h:31-32)
+    if (corrected && (s->dev.features & (F_LIGHT_ENV | F_LIGHT_NONE)))
+        return fail(SRT_E_UNSUPPORTED, "corrected-transport mode: the light list holds a shape without a sampling density "
+                                       "(env_sphere, or a class without pdf_value / random)");
+    int wv = wavefront ? pick_wf_variant(s, counting, corrected) : -1;
     if (wv < 0) wavefront = false;
     // the queues of k_wf_sorted hold one path per work item: SRT_CHUNK > 1 renders on the fused kernel
     if (wavefront && std::min(count, env_int("SRT_CHUNK", 1)) > 1) wavefront = false;
     const int wf_mode = wavefront ? 3 : 0;  // SrtSceneInfo::render_variant = 100 x mode + variant (3: k_wf_sorted)
-    int v = pick_variant(s, counting);
+    int v = pick_variant(s, counting, corrected);
     if (v < 0) return fail(SRT_E_UNSUPPORTED, "no render-kernel variant covers feature mask 0x%x", s->dev.features);
     size_t smem = (kVariantMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
 

@@ -126,7 +126,13 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
     V3 sum = v3(0.f, 0.f, 0.f);
     Path P;
     P.depth = 0;
+    P.emit_w = 1.f;
     Philox rng;
+    // corrected-transport mode (F_CORRECTED): the shadow ray of the last vertex, traced by the NEXT trip of the
+    // bounce loop through the same world_hit call as every other ray (one copy of the closest-hit code)
+    Nee nee;
+    nee.valid = false;
+    bool main_dead = false;
     // warp-uniform range of items
     unsigned long long w_cur = 0, w_end = 0;
     bool exhausted = false;
@@ -176,6 +182,7 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
                 P.thr = v3(1.f, 1.f, 1.f);
                 P.L = v3(0.f, 0.f, 0.f);
                 P.depth = 0;
+                P.emit_w = 1.f;
                 alive = true;
                 if (COUNT) {
                     paths++;
@@ -196,19 +203,36 @@ __global__ void __launch_bounds__(kRenderThreads, SRT_MINBLOCKS)
         }
         // ---- one ray + one bounce for every live path ---------------------------------------------
         Hit h;
+        const bool shadow = (F & F_CORRECTED) && nee.valid;  // this trip traces the pending shadow ray instead
+        const Ray tr = shadow ? Ray{nee.o, nee.dir, nee.time} : P.r;
         if (run && alive) {
             if (COUNT) cnt.rays++;
-            h = world_hit<F>(W, P.r, 0.001f, kFltMax, rng, tl);
+            h = world_hit<F>(W, tr, 0.001f, kFltMax, rng, tl);
         }
         if (A.cta_sync >= 2) __syncthreads();
         if (run && alive) {
             if (COUNT && cnt.dbg)
                 printf("[dbg] depth %d hit prim %d entry %d t %g thr=(%g %g %g) L=(%g %g %g)\n", P.depth, h.prim, h.entry, h.t,
                        P.thr.x, P.thr.y, P.thr.z, P.L.x, P.L.y, P.L.z);
-            if (!shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
+            bool ended;
+            if (F & F_CORRECTED) {
+                if (shadow) {  // next-event estimation: the emitter's radiance if an emitter is what the ray reaches
+                    V3 e = emitted_at<F>(W, tr, h);
+                    P.L = v3(fmaf(nee.weight.x, e.x, P.L.x), fmaf(nee.weight.y, e.y, P.L.y), fmaf(nee.weight.z, e.z, P.L.z));
+                    nee.valid = false;
+                    ended = main_dead;
+                } else {
+                    main_dead = !shade_bounce_corrected<F>(W, P, h, A.max_depth, rng, nee, tl);
+                    ended = main_dead && !nee.valid;
+                }
+            } else {
+                ended = !shade_bounce<F>(W, P, h, A.max_depth, rng, tl);
+            }
+            if (ended) {
                 V3 c = de_nan(P.L);  // col += de_nan(color(...)), Raytracing_n.cpp:841
                 sum = v3(sum.x + c.x, sum.y + c.y, sum.z + c.z);
                 alive = false;
+                main_dead = false;
             }
         }
     }

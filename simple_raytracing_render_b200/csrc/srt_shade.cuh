@@ -156,7 +156,9 @@ SRT_DEV V3 onb_local_fast(const Onb& b, V3 a) {
 }
 
 // ---- light list: hitable_list::random / pdf_value over hlist (hitable_list.h:54-67) ----------------
-template <uint32_t F>
+// CORR (corrected-transport mode): the triangle is sampled uniformly — triangle::random draws v = drand48() * (1 - u),
+// which crowds the points towards p1 (density 1 / (1 - u), triangle.h:89-94) while pdf_value assumes 1 / area.
+template <uint32_t F, bool CORR = false>
 SRT_DEV V3 light_random(const View& W, V3 o, Philox& rng) {
     const DScene& S = W.S;
     int index = 0;
@@ -183,6 +185,11 @@ SRT_DEV V3 light_random(const View& W, V3 o, Philox& rng) {
         const float* p = S.tri_pos + 9 * (size_t)(pr.flags_aux >> 1);
         float u = rand_f(rng);
         float v = rand_f(rng) * (1.f - u);
+        if (CORR) {  // uniform: b1 = 1 - sqrt(u1) on p1, b2 = u2 sqrt(u1) on p2
+            const float su = sqrtf(u);
+            v = v / fmaxf(1.f - u, 1e-20f) * su;
+            u = 1.f - su;
+        }
         V3 pt = fm::madd(v3(p), 1.f - u - v, fm::madd(v3(p + 3), u, fm::scale(v3(p + 6), v)));
         return fm::sub(pt, o);
     }
@@ -193,7 +200,9 @@ SRT_DEV V3 light_random(const View& W, V3 o, Philox& rng) {
 // shape re-intersects the ray (o, v) with (0.001, FLT_MAX) — these ARE hit tests of the reference
 // shapes and use the exact routines, so that srt_light_pdf reproduces the reference's zero / non-zero
 // pattern bit for bit; the density arithmetic after the hit is in fast float.
-template <uint32_t F, bool COUNT>
+// CORR (corrected-transport mode): triangle::hit reports t as a DISTANCE (triangle.h:128), so distance^2 is t^2; the
+// reference multiplies it by |v|^2 once more (triangle.h:80), which is only right for unit directions.
+template <uint32_t F, bool COUNT, bool CORR = false>
 SRT_DEV float light_pdf_value(const View& W, V3 o, V3 v, Tally<COUNT> tl) {
     const DScene& S = W.S;
     float weight = 1.0f / (float)S.n_lights;
@@ -241,7 +250,7 @@ SRT_DEV float light_pdf_value(const View& W, V3 o, V3 v, Tally<COUNT> tl) {
                 float sin102 = xsqrt(xsub(1.f, xmul(cos102, cos102)));
                 float h = xmul(l02, sin102);
                 float area = (float)(0.5 * (double)l01 * (double)h);
-                float distance_square = xmul(xmul(t, t), q.a);
+                float distance_square = CORR ? xmul(t, t) : xmul(xmul(t, t), q.a);
                 float cosine = xdiv(fabsf(dot(v, nrm)), xsqrt(q.a));
                 pdf = xdiv(distance_square, xmul(cosine, area));
             }
@@ -316,6 +325,7 @@ struct Path {
     V3 thr;  // product of attenuation * scattering_pdf / pdf_val so far
     V3 L;    // radiance gathered so far
     int depth;
+    float emit_w;  // corrected-transport mode only: MIS weight of the emission the current ray may find
 };
 
 // One level of color() (Raytracing_n.cpp:55-106) for a path whose ray has just been traced to `h`,
@@ -504,6 +514,196 @@ SRT_DEV bool shade_bounce(const View& W, Path& P, const Hit& h, int max_depth, P
     while (!shade_sample_iter<F>(W, C, rng, tl)) {
     }
     return shade_finish<F>(P, C, tl);
+}
+
+// ---- corrected-transport mode (F_CORRECTED, SRT_RENDER_CORRECTED) -----------------------------
+// Explicitly OUTSIDE parity with the reference: what its estimator gets wrong is put right, its scene semantics
+// (closest hit, one-sided emission, depth cap, specular branches, the light list as the set of sampled shapes)
+// stay.  Per non-specular vertex:
+//   * next-event estimation: one direction to a point of a light shape (hitable_list::random, the reference's own
+//     area / cone samplers, which are correct), its mixture density p_l (hitable_list::pdf_value), and a SHADOW RAY
+//     the scheduler traces (closest hit along it: the emitter's radiance if an emitter is what it reaches first);
+//   * BSDF sampling about the face-forward normal: a true cosine-weighted direction (pdf.h:10-18 scales x and y by 2
+//     and pdf.h:47-56 flips the lobe INTO the surface) for lambertian / Oren-Nayar / MERL, the Beckmann normal
+//     distribution for beckmann;
+//   * the BSDF VALUE applied: rho/pi, the Oren-Nayar term, D G / (4 cos cos) with the albedo as specular colour, and
+//     the MERL table value the reference looks up and discards (material.h:231-232);
+//   * balance-heuristic MIS between the two: the shadow ray carries p_l / (p_l + p_b), the continuation ray carries
+//     p_b / (p_b + p_l) for the emission it may find (Path::emit_w; 1 after a camera or specular vertex).
+// One Philox block per consumer, as everywhere: one for the light sample, one for the BSDF sample.
+struct Nee {
+    bool valid;
+    V3 o;       // the vertex
+    float time;
+    V3 dir;     // unnormalised direction from the vertex to the sampled light point
+    V3 weight;  // throughput * f * cos * w_mis / p_l: multiplies the emitted radiance the shadow ray finds
+};
+
+struct LocalFrame {
+    Onb b;  // b.w = face-forward shading normal
+    SRT_DEV V3 to_local(V3 d) const { return v3(fm::dot(d, b.u), fm::dot(d, b.v), fm::dot(d, b.w)); }
+    SRT_DEV V3 to_world(V3 a) const { return onb_local_fast(b, a); }
+};
+
+// Beckmann normal distribution sampling (the full distribution, not the visible normals: the reference's
+// visible-normal sampler leans on its Erf, which ADDS exp(-x^2), common.h:44-46, and therefore does not match any
+// density).  pbrt-v3 BeckmannDistribution::Sample_wh, sampleVisibleArea = false.
+SRT_DEV V3 beckmann_sample_wh(float ax, float ay, float u1, float u2) {
+    float logSample = logf(fmaxf(1.f - u1, 1e-30f));
+    float tan2Theta, phi;
+    if (ax == ay) {
+        tan2Theta = -ax * ax * logSample;
+        phi = u2 * fm::kTwoPi;
+    } else {
+        phi = atanf(ay / ax * tanf(fm::kTwoPi * u2 + 0.5f * 3.14159265f));
+        if (u2 > 0.5f) phi += 3.14159265f;
+        float sp, cp;
+        __sincosf(phi, &sp, &cp);
+        tan2Theta = -logSample / (cp * cp / (ax * ax) + sp * sp / (ay * ay));
+    }
+    float cosTheta = rsqrtf(1.f + tan2Theta);
+    float sinTheta = sqrtf(fmaxf(0.f, 1.f - cosTheta * cosTheta));
+    float sp, cp;
+    __sincosf(phi, &sp, &cp);
+    return v3(sinTheta * cp, sinTheta * sp, cosTheta);
+}
+
+// f(wo, wi) * cos(theta_i) and the solid-angle density of the sampler, both in the local frame (z = face-forward
+// normal; wo points AWAY from the surface).  Zero outside the upper hemisphere.
+template <uint32_t F>
+SRT_DEV void corrected_eval(const DScene& S, const DMaterial& m, V3 albedo, V3 wo, V3 wi, V3& fcos, float& pdf) {
+    fcos = v3(0.f, 0.f, 0.f);
+    pdf = 0.f;
+    if (!(wi.z > 0.f) || !(wo.z > 0.f)) return;
+    if ((F & F_BECKMANN) && m.type == SRT_MAT_BECKMANN) {
+        const float ax = fmaxf(m.p[0], 1e-3f), ay = fmaxf(m.p[1], 1e-3f);
+        V3 wh = fm::normalize(fm::add(wo, wi));
+        float d = BeckmannD(wh, ax, ay);
+        float g = BeckmannG(wo, wi, ax, ay);
+        float k = d * g / (4.f * wo.z);  // D G / (4 cos_o cos_i) * cos_i
+        fcos = fm::scale(albedo, k);
+        pdf = d * fabsf(wh.z) / (4.f * fmaxf(fm::dot(wo, wh), 1e-8f));
+        return;
+    }
+    pdf = wi.z * fm::kInvPi;
+    if ((F & F_ORENNAYAR) && m.type == SRT_MAT_ORENNAYAR) {  // pdf.h:64-101's term, in this frame
+        float sinI = SinTheta(wi), sinO = SinTheta(wo), maxCos = 0.f;
+        if (sinI > 1e-4f && sinO > 1e-4f) maxCos = fmaxf(0.f, CosPhi(wi) * CosPhi(wo) + SinPhi(wi) * SinPhi(wo));
+        float sinAlpha, tanBeta;
+        if (wi.z > wo.z) {
+            sinAlpha = sinO;
+            tanBeta = sinI / wi.z;
+        } else {
+            sinAlpha = sinI;
+            tanBeta = sinO / wo.z;
+        }
+        fcos = fm::scale(albedo, wi.z * (m.p[0] + m.p[1] * maxCos * sinAlpha * tanBeta) * fm::kInvPi);
+        return;
+    }
+    if (m.type == SRT_MAT_BRDF) {  // the measured value, brdf.h:190-214 (fp64, as the reference evaluates it)
+        double rgb[3];
+        merl_lookup(S.merl[(int)m.p[3]], acos((double)fminf(wi.z, 1.f)), atan2((double)wi.y, (double)wi.x),
+                    acos((double)fminf(wo.z, 1.f)), atan2((double)wo.y, (double)wo.x), rgb);
+        fcos = v3(fmaxf((float)rgb[0], 0.f) * wi.z, fmaxf((float)rgb[1], 0.f) * wi.z, fmaxf((float)rgb[2], 0.f) * wi.z);
+        return;
+    }
+    fcos = fm::scale(albedo, wi.z * fm::kInvPi);  // lambertian
+}
+
+template <uint32_t F>
+SRT_DEV V3 corrected_sample(const DMaterial& m, V3 wo, Philox& rng) {
+    float u1 = rand_pcg_like(rng), u2 = rand_pcg_like(rng);
+    if ((F & F_BECKMANN) && m.type == SRT_MAT_BECKMANN) {
+        V3 wh = beckmann_sample_wh(fmaxf(m.p[0], 1e-3f), fmaxf(m.p[1], 1e-3f), u1, u2);
+        return fm::sub(fm::scale(wh, 2.f * fm::dot(wo, wh)), wo);  // reflect wo about wh
+    }
+    float r = sqrtf(u1), sn, cs;
+    __sincosf(fm::kTwoPi * u2, &sn, &cs);
+    return v3(r * cs, r * sn, sqrtf(fmaxf(0.f, 1.f - u1)));
+}
+
+// The emitted radiance a ray finds at its closest hit `h` (diffuse_light::emitted, material.h:348-354: front face
+// only), zero for a miss or a non-emitter.
+template <uint32_t F>
+SRT_DEV V3 emitted_at(const View& W, const Ray& r, const Hit& h) {
+    const DScene& S = W.S;
+    if (h.prim < 0 || ((F & F_MEDIA) && h.prim >= S.n_prims)) return v3(0.f, 0.f, 0.f);
+    const int mat_index = load_prim(W.dprims + h.prim).material;
+    if (mat_index < 0) return v3(0.f, 0.f, 0.f);
+    DMaterial m = load_material(S.materials + mat_index);
+    if (m.type != SRT_MAT_DIFFUSE_LIGHT) return v3(0.f, 0.f, 0.f);
+    HitRecord rec = material_needs_uv<F>(m) ? make_record<F, true>(W, r, h) : make_record<F, false>(W, r, h);
+    if (!(fm::dot(rec.normal, r.d) < 0.f)) return v3(0.f, 0.f, 0.f);
+    return material_color<F>(S, m, rec);
+}
+
+// One level of the corrected estimator.  P.emit_w weights the emission found at THIS hit.  Returns true when the
+// path continues (P.r is the next ray); `nee` is the shadow ray of this vertex (valid or not) either way.
+template <uint32_t F, bool COUNT>
+SRT_DEV bool shade_bounce_corrected(const View& W, Path& P, const Hit& h, int max_depth, Philox& rng, Nee& nee, Tally<COUNT> tl) {
+    const DScene& S = W.S;
+    nee.valid = false;
+    nee.o = nee.dir = nee.weight = v3(0.f, 0.f, 0.f);
+    nee.time = P.r.time;
+    if (h.prim < 0) return false;
+    int mat_index;
+    if ((F & F_MEDIA) && h.prim >= S.n_prims)
+        mat_index = S.media[h.prim - S.n_prims].phase_material;
+    else
+        mat_index = load_prim(W.dprims + h.prim).material;
+    if (mat_index < 0) return false;
+    DMaterial m = load_material(S.materials + mat_index);
+    HitRecord rec = material_needs_uv<F>(m) ? make_record<F, true>(W, P.r, h) : make_record<F, false>(W, P.r, h);
+    const Ray r = P.r;
+    if (m.type == SRT_MAT_DIFFUSE_LIGHT) {
+        if (fm::dot(rec.normal, r.d) < 0.f) {
+            V3 e = fm::scale(material_color<F>(S, m, rec), P.emit_w);
+            P.L = v3(fmaf(P.thr.x, e.x, P.L.x), fmaf(P.thr.y, e.y, P.L.y), fmaf(P.thr.z, e.z, P.L.z));
+        }
+        return false;
+    }
+    if (!(P.depth < max_depth)) return false;
+    if (((F & F_METAL) && m.type == SRT_MAT_METAL) || ((F & F_DIELECTRIC) && m.type == SRT_MAT_DIELECTRIC) ||
+        ((F & F_MEDIA) && m.type == SRT_MAT_ISOTROPIC)) {
+        SampleCtx C;  // the specular branches are the reference's (shade_hit): nothing to correct
+        ShadeStatus st = shade_hit<F>(W, P, h, max_depth, rng, C, tl);
+        P.emit_w = 1.f;
+        return st == SHADE_CONTINUES;
+    }
+    // ---- a non-specular vertex -----------------------------------------------------------------------------
+    const V3 albedo = m.type == SRT_MAT_BRDF ? v3(1.f, 1.f, 1.f) : material_color<F>(S, m, rec);
+    LocalFrame fr;
+    fr.b = onb_fast(fm::dot(rec.normal, r.d) < 0.f ? rec.normal : fm::neg(rec.normal));
+    const V3 wo = fr.to_local(fm::neg(fm::normalize(r.d)));
+    if (S.n_lights > 0) {  // next-event estimation
+        philox_fresh(rng);
+        V3 ldir = light_random<F, true>(W, rec.p, rng);
+        float pl = light_pdf_value<F, COUNT, true>(W, rec.p, ldir, tl);
+        V3 wl = fr.to_local(fm::normalize(ldir));
+        V3 fcos;
+        float pb;
+        corrected_eval<F>(S, m, albedo, wo, wl, fcos, pb);
+        if (pl > 0.f && isfinite(pl) && (fcos.x > 0.f || fcos.y > 0.f || fcos.z > 0.f)) {
+            nee.valid = true;
+            nee.o = rec.p;
+            nee.dir = ldir;
+            nee.weight = fm::mul(P.thr, fm::scale(fcos, 1.f / (pl + pb)));  // f cos / p_l * p_l / (p_l + p_b)
+        }
+    }
+    philox_fresh(rng);
+    V3 wi = corrected_sample<F>(m, wo, rng);
+    V3 fcos;
+    float pb;
+    corrected_eval<F>(S, m, albedo, wo, wi, fcos, pb);
+    if (!(pb > 0.f) || !isfinite(pb)) return false;
+    P.thr = fm::mul(P.thr, fm::scale(fcos, 1.f / pb));
+    if (P.thr.x == 0.f && P.thr.y == 0.f && P.thr.z == 0.f) return false;
+    V3 dir = fr.to_world(wi);
+    float pl2 = S.n_lights > 0 ? light_pdf_value<F, COUNT, true>(W, rec.p, dir, tl) : 0.f;
+    P.emit_w = (pl2 > 0.f && isfinite(pl2)) ? pb / (pb + pl2) : 1.f;
+    P.r = Ray{rec.p, dir, r.time};
+    P.depth++;
+    return true;
 }
 
 // camera::get_ray (camera.h:51-59).  Exact arithmetic: these rays are what srt_trace_closest is

@@ -56,6 +56,7 @@ enum : uint32_t {
     F_LIGHT_ENV = 1u << 17,
     F_LIGHT_NONE = 1u << 18,  // a light-list element without pdf_value / random (hitable.h:31-32)
     F_SMEM_TABLES = 1u << 24, // launch option, not a scene property: hot tables staged in smem
+    F_CORRECTED = 1u << 25,   // launch option: corrected-transport mode (SRT_RENDER_CORRECTED, srt_shade.cuh)
     F_ALL_SCENE = (1u << 19) - 1u
 };
 

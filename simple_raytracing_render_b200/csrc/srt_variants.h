@@ -43,7 +43,8 @@ typedef cudaError_t (*RenderVariantFn)(const RenderLaunch& L, RenderVariantInfo*
 #define SRT_VM_FULL F_ALL_SCENE
 
 // variant n -> (mask, counting)
-#define SRT_N_VARIANTS 7
+// variant 7: corrected-transport mode (SRT_RENDER_CORRECTED, srt_shade.cuh), all features, tables in global memory
+#define SRT_N_VARIANTS 8
 #define SRT_VARIANT_MASK(n)                                  \
     ((n) == 0   ? (SRT_VM_LIST | F_SMEM_TABLES)              \
      : (n) == 1 ? (SRT_VM_SPHERES | F_SMEM_TABLES)           \
@@ -51,13 +52,14 @@ typedef cudaError_t (*RenderVariantFn)(const RenderLaunch& L, RenderVariantInfo*
      : (n) == 3 ? (SRT_VM_FULL | F_SMEM_TABLES)              \
      : (n) == 4 ? (SRT_VM_MESH)                              \
      : (n) == 5 ? (SRT_VM_FULL)                              \
-                : (SRT_VM_FULL))
+     : (n) == 6 ? (SRT_VM_FULL)                              \
+                : (SRT_VM_FULL | F_CORRECTED))
 #define SRT_VARIANT_COUNTING(n) ((n) == 6)
 // Resident CTAs per SM the register allocator is bounded for (__launch_bounds__).  Measured on B200
 // (profiles/r01_notes.md, capture C): the list and mesh kernels gain 30-40 % from 4 CTAs (64
 // registers, < 200 bytes of spills) because their stalls are fixed-latency waits and instruction
 // fetch that more warps hide; the sphere-BVH kernel spills ~1 KB at 64 registers and is best at 2.
-#define SRT_VARIANT_MINBLOCKS(n) ((n) == 1 ? 2 : 4)
+#define SRT_VARIANT_MINBLOCKS(n) ((n) == 1 || (n) == 7 ? 2 : 4)
 
 // ---- the sorted wavefront kernel (srt_wavefront.cuh), one translation unit per mask -------------------
 struct WfLaunch {
@@ -83,11 +85,13 @@ typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
 
 // variant 4 is the COUNTING build of k_wf_sorted (all features, tables in global memory): srt_render_counted
 // replays a launch on it, so that the work counters come from the scheduler that was timed
-#define SRT_N_WF_VARIANTS 5
+// variant 5: corrected-transport mode, all features
+#define SRT_N_WF_VARIANTS 6
 #define SRT_WF_VARIANT_MASK(n)                                 \
     ((n) == 0   ? (SRT_VM_LIST | F_SMEM_TABLES)                \
      : (n) == 1 ? (SRT_VM_SPHERES | F_SMEM_TABLES)             \
      : (n) == 2 ? (SRT_VM_MESH)                                \
+     : (n) == 5 ? (SRT_VM_FULL | F_CORRECTED)                  \
                 : (SRT_VM_FULL))
 #define SRT_WF_VARIANT_COUNTING(n) ((n) == 4)
 // threads of the one persistent CTA per SM (k_wf_sorted).  Measured (profiles/r01_notes.md,
@@ -100,6 +104,7 @@ cudaError_t srt_wavefront_variant_1(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_2(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_3(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_4(const WfLaunch&, WfVariantInfo*);
+cudaError_t srt_wavefront_variant_5(const WfLaunch&, WfVariantInfo*);
 
 cudaError_t srt_render_variant_0(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_1(const RenderLaunch&, RenderVariantInfo*);
@@ -108,5 +113,6 @@ cudaError_t srt_render_variant_3(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_4(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_5(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_6(const RenderLaunch&, RenderVariantInfo*);
+cudaError_t srt_render_variant_7(const RenderLaunch&, RenderVariantInfo*);
 
 #endif

@@ -49,7 +49,19 @@
 namespace srt {
 
 constexpr int kSlotQuads = SRT_WF_SLOT_QUADS;
-enum { SQ_O = 0, SQ_D, SQ_HIT, SQ_THR, SQ_RAD, SQ_ITEM };
+// corrected-transport mode (F_CORRECTED, srt_shade.cuh) keeps the shadow ray of the last vertex in the record:
+//   q1.w  MIS weight of the emission the main ray may find      q5.z  flags: kNeePending | kMainDead
+//   q6    shadow-ray direction .xyz    q7  its weight .xyz       q8    its closest hit t, primitive, entry
+// The trace phase traces both rays of a slot through the same world_hit call; the NEXT shade phase adds the
+// emitter's radiance the shadow ray found, then shades the main hit.  A path whose BSDF sample failed but
+// whose shadow ray is pending stays queued (kMainDead) for one more iteration.
+constexpr int kSlotQuadsCorrected = 9;
+template <uint32_t F>
+struct SlotQuads {
+    static constexpr int value = (F & F_CORRECTED) ? kSlotQuadsCorrected : kSlotQuads;
+};
+enum { SQ_O = 0, SQ_D, SQ_HIT, SQ_THR, SQ_RAD, SQ_ITEM, SQ_SDIR, SQ_SW, SQ_SHIT };
+enum { kNeePending = 1, kMainDead = 2 };
 
 struct WfState {
     float4* rec;  // [n_slots][kSlotQuads]
@@ -206,7 +218,7 @@ SRT_DEV int wf_hit_class(const View& W, const Hit& h) {
 template <uint32_t F, bool COUNT>
 SRT_DEV void wf_shade_group(const View& W, const RenderArgs& A, SortQueues& Q, float4* pool, long long* __restrict__ out,
                             int ls, bool valid, int q_cont, Tally<COUNT> tl) {
-    float4* rec = pool + (size_t)ls * kSlotQuads;
+    float4* rec = pool + (size_t)ls * SlotQuads<F>::value;
     int dest = SC_DEAD;
     if (valid) {
         const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D), hv = slot_ld(rec + SQ_HIT), tv = slot_ld(rec + SQ_THR),
@@ -216,6 +228,7 @@ SRT_DEV void wf_shade_group(const View& W, const RenderArgs& A, SortQueues& Q, f
         P.thr = v3(tv.x, tv.y, tv.z);
         P.depth = __float_as_int(tv.w);
         P.L = v3(lv.x, lv.y, lv.z);
+        P.emit_w = d.w;
         Hit h;
         h.t = hv.x;
         h.prim = __float_as_int(hv.y);
@@ -223,11 +236,39 @@ SRT_DEV void wf_shade_group(const View& W, const RenderArgs& A, SortQueues& Q, f
         const int pixel = __float_as_int(it.x);
         Philox rng;
         wf_rng(rng, A.seed, (uint32_t)pixel, __float_as_uint(it.y), __float_as_uint(lv.w));
-        if (shade_bounce<F>(W, P, h, A.max_depth, rng, tl)) {
+        bool cont;
+        int flags = 0;
+        Nee nee;
+        nee.valid = false;
+        if (F & F_CORRECTED) {
+            const int old_flags = __float_as_int(it.z);
+            if (old_flags & kNeePending) {  // what the shadow ray of the previous vertex reached
+                const float4 sd = slot_ld(rec + SQ_SDIR), sw = slot_ld(rec + SQ_SW), sh = slot_ld(rec + SQ_SHIT);
+                Hit hs;
+                hs.t = sh.x;
+                hs.prim = __float_as_int(sh.y);
+                hs.entry = __float_as_int(sh.z);
+                const V3 e = emitted_at<F>(W, Ray{P.r.o, v3(sd.x, sd.y, sd.z), P.r.time}, hs);
+                P.L = v3(fmaf(sw.x, e.x, P.L.x), fmaf(sw.y, e.y, P.L.y), fmaf(sw.z, e.z, P.L.z));
+            }
+            cont = !(old_flags & kMainDead) && shade_bounce_corrected<F>(W, P, h, A.max_depth, rng, nee, tl);
+            flags = (nee.valid ? kNeePending : 0) | (cont ? 0 : kMainDead);
+            if (!cont && nee.valid) P.r.o = nee.o;  // the shadow ray starts at the vertex
+        } else {
+            cont = shade_bounce<F>(W, P, h, A.max_depth, rng, tl);
+        }
+        if (cont || nee.valid) {
             slot_st(rec + SQ_O, make_float4(P.r.o.x, P.r.o.y, P.r.o.z, P.r.time));
-            slot_st(rec + SQ_D, make_float4(P.r.d.x, P.r.d.y, P.r.d.z, 0.f));
+            slot_st(rec + SQ_D, make_float4(P.r.d.x, P.r.d.y, P.r.d.z, P.emit_w));
             slot_st(rec + SQ_THR, make_float4(P.thr.x, P.thr.y, P.thr.z, __int_as_float(P.depth)));
             slot_st(rec + SQ_RAD, make_float4(P.L.x, P.L.y, P.L.z, __uint_as_float(rng.c2)));
+            if (F & F_CORRECTED) {
+                slot_st(rec + SQ_ITEM, make_float4(it.x, it.y, __int_as_float(flags), 0.f));
+                if (nee.valid) {
+                    slot_st(rec + SQ_SDIR, make_float4(nee.dir.x, nee.dir.y, nee.dir.z, 0.f));
+                    slot_st(rec + SQ_SW, make_float4(nee.weight.x, nee.weight.y, nee.weight.z, 0.f));
+                }
+            }
             dest = q_cont;
         } else {
             item_commit(out, pixel, de_nan(P.L), A.fx_clamp);  // col += de_nan(color(...)), :841
@@ -279,7 +320,8 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
     View W = wf_view<F>(S, smem_hot);
     const int lane = threadIdx.x & 31;
     const int cap = per_thread * blockDim.x;  // <= kSortCap (srt_api.cu)
-    float4* const pool = st.rec + (size_t)blockIdx.x * cap * kSlotQuads;  // this CTA's records
+    constexpr int NQ = SlotQuads<F>::value;
+    float4* const pool = st.rec + (size_t)blockIdx.x * cap * NQ;  // this CTA's records
     unsigned long long* work_counter = counters + 7;
     // COUNT: the instrumented build of THIS kernel (srt_render_counted): same schedule, same paths, plus the
     // per-thread tallies of SrtCounters (the shipping kernel's own visit / test counters)
@@ -339,7 +381,7 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                     if (pos - lane >= avail) break;  // the rest of the queue gets no item: those slots stay empty
                     const bool start = valid && pos < avail;
                     if (start) {
-                        float4* rec = pool + (size_t)ls * kSlotQuads;
+                        float4* rec = pool + (size_t)ls * NQ;
                         const unsigned long long item = base + (unsigned)pos;
                         const int pixel = (int)(item / (unsigned)A.n_chunks);
                         const int s = A.s_begin + (int)(item - (unsigned long long)pixel * (unsigned)A.n_chunks);
@@ -347,7 +389,7 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                         const Ray r = start_path(S.camera, A, sobol, pixel, s, rng);
                         if (COUNT) cnt.paths++;
                         slot_st(rec + SQ_O, make_float4(r.o.x, r.o.y, r.o.z, r.time));
-                        slot_st(rec + SQ_D, make_float4(r.d.x, r.d.y, r.d.z, 0.f));
+                        slot_st(rec + SQ_D, make_float4(r.d.x, r.d.y, r.d.z, 1.f));
                         slot_st(rec + SQ_THR, make_float4(1.f, 1.f, 1.f, __int_as_float(0)));
                         slot_st(rec + SQ_RAD, make_float4(0.f, 0.f, 0.f, __uint_as_float(rng.c2)));
                         slot_st(rec + SQ_ITEM, make_float4(__int_as_float(pixel), __int_as_float(s), 0.f, 0.f));
@@ -371,23 +413,38 @@ __global__ void __launch_bounds__(SRT_WFP_THREADS, SRT_WFP_MINBLOCKS)
                 int ls, pos;
                 bool valid;
                 while (q_take(Q, c, ls, valid, pos)) {
-                    float4* rec = pool + (size_t)ls * kSlotQuads;
+                    float4* rec = pool + (size_t)ls * NQ;
                     int cls = SC_MISS;
+                    float4 o = make_float4(0.f, 0.f, 0.f, 0.f), d = o;
+                    int flags = 0;
+                    Philox rng;
+                    rng.have = 0;
                     if (valid) {
-                        const float4 o = slot_ld(rec + SQ_O), d = slot_ld(rec + SQ_D);
-                        Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
-                        Philox rng;
-                        rng.have = 0;
-                        if (F & F_MEDIA) {  // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
+                        o = slot_ld(rec + SQ_O);
+                        d = slot_ld(rec + SQ_D);
+                        if (F & (F_MEDIA | F_CORRECTED)) {
                             const float4 lv = slot_ld(rec + SQ_RAD), it = slot_ld(rec + SQ_ITEM);
-                            wf_rng(rng, A.seed, __float_as_uint(it.x), __float_as_uint(it.y), __float_as_uint(lv.w));
+                            // constant_medium::hit draws its free-flight distance (constant_medium.h:33)
+                            if (F & F_MEDIA) wf_rng(rng, A.seed, __float_as_uint(it.x), __float_as_uint(it.y), __float_as_uint(lv.w));
+                            if (F & F_CORRECTED) flags = __float_as_int(it.z);
                         }
-                        if (COUNT) cnt.rays++;
-                        Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
-                        slot_st(rec + SQ_HIT, make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f));
-                        if (F & F_MEDIA) slot_st1(reinterpret_cast<float*>(rec + SQ_RAD) + 3, __uint_as_float(rng.c2));
-                        cls = wf_hit_class<F>(W, h);
                     }
+                    // the main ray, then (corrected-transport mode) the shadow ray of the slot's last vertex: one
+                    // world_hit call site for both
+                    for (int k = 0; k < ((F & F_CORRECTED) ? 2 : 1); k++) {
+                        const bool act = valid && (k == 0 ? !(flags & kMainDead) : (flags & kNeePending) != 0);
+                        if ((F & F_CORRECTED) && !__any_sync(0xffffffffu, act)) continue;
+                        if (act) {
+                            if (k == 1) d = slot_ld(rec + SQ_SDIR);
+                            Ray r{v3(o.x, o.y, o.z), v3(d.x, d.y, d.z), o.w};
+                            if (COUNT) cnt.rays++;
+                            Hit h = world_hit<F>(W, r, 0.001f, kFltMax, rng, tl);
+                            slot_st(rec + (k == 0 ? SQ_HIT : SQ_SHIT),
+                                    make_float4(h.t, __int_as_float(h.prim), __int_as_float(h.entry), 0.f));
+                            if (k == 0) cls = wf_hit_class<F>(W, h);
+                        }
+                    }
+                    if ((F & F_MEDIA) && valid) slot_st1(reinterpret_cast<float*>(rec + SQ_RAD) + 3, __uint_as_float(rng.c2));
                     q_push_class(Q, valid, cls, ls);
                 }
             }

@@ -29,7 +29,7 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         e = cudaFuncSetAttribute((const void*)sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
         if (e != cudaSuccess) return e;
         info->threads = SRT_WFP_THREADS;
-        info->slot_bytes = srt::kSlotQuads * 16;
+        info->slot_bytes = srt::SlotQuads<kMask>::value * 16;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->blocks_per_sm, sorted, SRT_WFP_THREADS, L.smem_bytes);
         if (e != cudaSuccess) return e;
         e = cudaFuncGetAttributes(&fa, sorted);

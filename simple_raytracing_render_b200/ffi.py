@@ -34,6 +34,7 @@ TEX_CONSTANT, TEX_CHECKER, TEX_NOISE, TEX_IMAGE = range(4)
 
 COMPAT_PIXEL_MOD_NY = 1
 RENDER_WAVEFRONT = 2
+RENDER_CORRECTED = 4  # corrected-transport mode (outside parity; include/srt_ffi.h)
 
 MERL_DOUBLES = 3 * 90 * 90 * 180
 

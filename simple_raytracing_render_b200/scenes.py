@@ -137,6 +137,15 @@ def teapot_beckmann(aspect: float = 1.0, divs: int = 100, seed: int = 1):
     return world, hlist, cam
 
 
+def constant_merl_table(albedo: float = 0.5) -> np.ndarray:
+    """A MERL-layout table whose looked-up value (brdf.h:190-214, channel scales 1/1500, 1.15/1500, 1.66/1500) is
+    albedo / pi for every angle: a brdfmaterial with it IS a lambertian of that albedo wherever the table value is
+    applied (corrected-transport mode)."""
+    n = 90 * 90 * 180
+    f = albedo / np.pi
+    return np.concatenate([np.full(n, f * 1500.0), np.full(n, f * 1500.0 / 1.15), np.full(n, f * 1500.0 / 1.66)]).astype(np.float64)
+
+
 def synthetic_merl_table() -> np.ndarray:
     """Stand-in for contents/brdfs/aluminium.binary (absent from the reference tree,
     .MISSING_LARGE_BLOBS): a smooth metallic lobe in the MERL layout of brdf.h:171-184 —
@@ -507,6 +516,70 @@ def medium_probe(boundary_kind: str = "sphere", density: float = 0.7):
     world = hitable_list([constant_medium(b, density, constant_texture(vec3(1, 1, 1)))], 1)
     cam = camera(vec3(0, 0, -5), vec3(0, 0, 0), vec3(0, 1, 0), 40.0, 1.0, 0.0, 10.0, 0.0, 0.0)
     return world, hitable_list([], 0), cam
+
+
+def furnace(aspect: float = 1.0, sampled: bool = True, albedo: float = 0.5):
+    """White furnace for the corrected-transport mode (SRT_RENDER_CORRECTED): a closed box of six one-sided emitters
+    of radiance 1 around a lambertian sphere.  Every direction from the (convex) sphere sees radiance 1, so the
+    sphere's pixels converge to exactly `albedo` and every other pixel to 1 — with the floor and ceiling in the
+    light list (next-event estimation + MIS) and without (BSDF sampling alone)."""
+    one = diffuse_light(constant_texture(vec3(1, 1, 1)))
+    a = 10.0
+    lst = [
+        flip_normals(yz_rect(-a, a, -a, a, a, one)), yz_rect(-a, a, -a, a, -a, one),
+        flip_normals(xz_rect(-a, a, -a, a, a, one)), xz_rect(-a, a, -a, a, -a, one),
+        flip_normals(xy_rect(-a, a, -a, a, a, one)), xy_rect(-a, a, -a, a, -a, one),
+        sphere(vec3(0, 0, 0), 2.0, lambertian(constant_texture(vec3(albedo, albedo, albedo)))),
+    ]
+    world = hitable_list(lst, len(lst))
+    lights = [flip_normals(xz_rect(-a, a, -a, a, a, None)), xz_rect(-a, a, -a, a, -a, None)] if sampled else []
+    cam = camera(vec3(0, 0, -8), vec3(0, 0, 0), vec3(0, 1, 0), 40.0, aspect, 0.0, 8.0, 0.0, 0.0)
+    return world, hitable_list(lights, len(lights)), cam
+
+
+def corrected_probe(aspect: float = 1.0, sampled: bool = True, seed: int = 1, lights=("rect", "sphere", "tri"),
+                    materials=("merl", "oren", "beckmann", "glass"), merl_table=None):
+    """A Cornell-like room for the corrected-transport mode with every non-specular material — lambertian walls,
+    an Oren-Nayar sphere, a Beckmann sphere, a floor with the MERL measured-BRDF material — a glass sphere, and
+    three kinds of light shape (rect, sphere, triangle).  `sampled`: the lights are in the light list (next-event
+    estimation + MIS) or not (BSDF sampling alone); both estimate the same image."""
+    S.set_seed(seed)
+    red = lambertian(constant_texture(vec3(0.65, 0.05, 0.05)))
+    white = lambertian(constant_texture(vec3(0.73, 0.73, 0.73)))
+    green = lambertian(constant_texture(vec3(0.12, 0.45, 0.15)))
+    light = diffuse_light(constant_texture(vec3(12, 12, 12)))
+    glow = diffuse_light(constant_texture(vec3(6, 5, 3)))
+    floor = white
+    if "merl" in materials:
+        floor = brdfmaterial(synthetic_merl_table() if merl_table is None else merl_table, vec3(0.7, 0.7, 0.7))
+    elif "floor50" in materials:
+        floor = lambertian(constant_texture(vec3(0.5, 0.5, 0.5)))
+    oren = orennayar(constant_texture(vec3(0.3, 0.45, 0.8)), 40.0) if "oren" in materials else white
+    gold = beckmann(constant_texture(vec3(0.945, 0.75, 0.336)), 0.3, 0.15) if "beckmann" in materials else white
+    glass = dielectric(1.5) if "glass" in materials else white
+    t0, t1, t2 = vec3(40, 300, 554), vec3(120, 450, 554), vec3(200, 300, 554)  # normal -z: faces the room
+    lst = [
+        flip_normals(yz_rect(0, 555, 0, 555, 555, green)), yz_rect(0, 555, 0, 555, 0, red),
+        flip_normals(xz_rect(0, 555, 0, 555, 555, white)), xz_rect(0, 555, 0, 555, 0, floor),
+        flip_normals(xy_rect(0, 555, 0, 555, 555, white)),
+        sphere(vec3(150, 90, 190), 90, oren),
+        sphere(vec3(390, 110, 350), 110, gold),
+        sphere(vec3(270, 60, 100), 60, glass),
+    ]
+    shapes = []
+    if "rect" in lights:
+        lst.append(flip_normals(xz_rect(163, 393, 177, 382, 554, light)))
+        shapes.append(flip_normals(xz_rect(163, 393, 177, 382, 554, None)))
+    if "sphere" in lights:
+        lst.append(sphere(vec3(400, 60, 150), 25, glow))
+        shapes.append(sphere(vec3(400, 60, 150), 25, None))
+    if "tri" in lights:
+        lst.append(triangle(t0, t1, t2, glow))
+        shapes.append(triangle(t0, t1, t2, None))
+    world = hitable_list(lst, len(lst))
+    lights = shapes if sampled else []
+    cam = camera(vec3(278, 278, -800), vec3(278, 278, 0), vec3(0, 1, 0), 40.0, aspect, 0.0, 10.0, 0.0, 0.0)
+    return world, hitable_list(lights, len(lights)), cam
 
 
 def by_name(name: str, **kw):
