@@ -1411,18 +1411,23 @@ int pick_variant(const SrtScene* s, bool counting, bool corrected = false) {
 }
 
 const WfVariantFn kWfVariants[SRT_N_WF_VARIANTS] = {srt_wavefront_variant_0, srt_wavefront_variant_1, srt_wavefront_variant_2,
-                                                     srt_wavefront_variant_3, srt_wavefront_variant_4, srt_wavefront_variant_5};
+                                                     srt_wavefront_variant_3, srt_wavefront_variant_4, srt_wavefront_variant_5,
+                                                     srt_wavefront_variant_6, srt_wavefront_variant_7};
 constexpr uint32_t kWfMask[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_MASK(0), SRT_WF_VARIANT_MASK(1), SRT_WF_VARIANT_MASK(2),
-                                                 SRT_WF_VARIANT_MASK(3), SRT_WF_VARIANT_MASK(4), SRT_WF_VARIANT_MASK(5)};
+                                                 SRT_WF_VARIANT_MASK(3), SRT_WF_VARIANT_MASK(4), SRT_WF_VARIANT_MASK(5),
+                                                 SRT_WF_VARIANT_MASK(6), SRT_WF_VARIANT_MASK(7)};
 constexpr int kWfCounting[SRT_N_WF_VARIANTS] = {SRT_WF_VARIANT_COUNTING(0), SRT_WF_VARIANT_COUNTING(1),
                                                 SRT_WF_VARIANT_COUNTING(2), SRT_WF_VARIANT_COUNTING(3),
-                                                SRT_WF_VARIANT_COUNTING(4), SRT_WF_VARIANT_COUNTING(5)};
+                                                SRT_WF_VARIANT_COUNTING(4), SRT_WF_VARIANT_COUNTING(5),
+                                                SRT_WF_VARIANT_COUNTING(6), SRT_WF_VARIANT_COUNTING(7)};
+constexpr int kWfOrder[SRT_N_WF_VARIANTS] = SRT_WF_VARIANT_ORDER;
 
 int pick_wf_variant(const SrtScene* s, bool counting, bool corrected = false) {
     uint32_t need = (s->dev.features & F_ALL_SCENE) | (corrected ? (uint32_t)F_CORRECTED : 0u);
     bool smem_ok = s->dev.hot_bytes <= kMaxHotSmem && !env_int("SRT_NO_SMEM", 0);
     int forced = counting ? -1 : env_int("SRT_WF_VARIANT", -1);
-    for (int v = 0; v < SRT_N_WF_VARIANTS; v++) {
+    for (int k = 0; k < SRT_N_WF_VARIANTS; k++) {
+        const int v = kWfOrder[k];
         if (forced >= 0 && v != forced) continue;
         if (kWfCounting[v] != (counting ? 1 : 0)) continue;
         if ((kWfMask[v] & F_SMEM_TABLES) && !smem_ok) continue;

@@ -86,18 +86,29 @@ typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
 // variant 4 is the COUNTING build of k_wf_sorted (all features, tables in global memory): srt_render_counted
 // replays a launch on it, so that the work counters come from the scheduler that was timed
 // variant 5: corrected-transport mode, all features
-#define SRT_N_WF_VARIANTS 6
+// variants 6, 7: the two mesh classes cut to what a triangle-mesh scene actually instantiates — one bvh kind (the
+// traversal's kind dispatch folds away), no loose triangles, sphere bvh, Oren-Nayar, checker or sphere / triangle
+// lights: a textured microfacet mesh in a list of rects / boxes / spheres (C3, C4), and a mesh with a
+// constant_medium (C5).  Less code per phase and fewer registers (srt_api.cu tries them before 2 and 3).
+#define SRT_VM_TRIMESH (SRT_VM_LIST | F_BVH_TRI | F_BECKMANN | F_TEX_IMAGE)
+#define SRT_VM_TRIVOLUME (SRT_VM_LIST | F_BVH_TRI | F_MEDIA)
+#define SRT_N_WF_VARIANTS 8
 #define SRT_WF_VARIANT_MASK(n)                                 \
     ((n) == 0   ? (SRT_VM_LIST | F_SMEM_TABLES)                \
      : (n) == 1 ? (SRT_VM_SPHERES | F_SMEM_TABLES)             \
      : (n) == 2 ? (SRT_VM_MESH)                                \
      : (n) == 5 ? (SRT_VM_FULL | F_CORRECTED)                  \
+     : (n) == 6 ? (SRT_VM_TRIMESH)                             \
+     : (n) == 7 ? (SRT_VM_TRIVOLUME)                           \
                 : (SRT_VM_FULL))
+// the order in which pick_wf_variant tries them: the smallest covering mask first
+#define SRT_WF_VARIANT_ORDER {0, 1, 6, 2, 7, 3, 4, 5}
 #define SRT_WF_VARIANT_COUNTING(n) ((n) == 4)
 // threads of the one persistent CTA per SM (k_wf_sorted).  Measured (profiles/r01_notes.md,
 // capture K): the sphere-BVH variant needs 107 registers and is best at 640 threads (96 registers, 20
-// warps); the mesh and full variants spill there and are best at 512 (128 registers).
-#define SRT_WF_VARIANT_PERSIST_THREADS(n) ((n) <= 1 ? 640 : 512)
+// warps); the mesh and full variants spill there and are best at 512 (128 registers); the two lean mesh
+// variants (6, 7) fit 96 registers with 32-96 bytes of spills and gain 1-3 % from the four extra warps.
+#define SRT_WF_VARIANT_PERSIST_THREADS(n) ((n) <= 1 || (n) >= 6 ? 640 : 512)
 
 cudaError_t srt_wavefront_variant_0(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_1(const WfLaunch&, WfVariantInfo*);
@@ -105,6 +116,8 @@ cudaError_t srt_wavefront_variant_2(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_3(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_4(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_5(const WfLaunch&, WfVariantInfo*);
+cudaError_t srt_wavefront_variant_6(const WfLaunch&, WfVariantInfo*);
+cudaError_t srt_wavefront_variant_7(const WfLaunch&, WfVariantInfo*);
 
 cudaError_t srt_render_variant_0(const RenderLaunch&, RenderVariantInfo*);
 cudaError_t srt_render_variant_1(const RenderLaunch&, RenderVariantInfo*);

@@ -14,7 +14,7 @@ nvcc $FLAGS "$@" -c $C/srt_bvh_build.cpp -o $B/srt_bvh_build.o & pids+=($!)
 for v in 0 1 2 3 4 5 6 7; do
   nvcc $FLAGS "$@" -DSRT_VARIANT=$v -c $C/srt_render_variant.cu -o $B/v$v.o & pids+=($!)
 done
-for v in 0 1 2 3 4 5; do
+for v in 0 1 2 3 4 5 6 7; do
   nvcc $FLAGS "$@" -DSRT_WF_VARIANT=$v -c $C/srt_wavefront_variant.cu -o $B/w$v.o & pids+=($!)
 done
 for p in "${pids[@]}"; do wait $p; done
