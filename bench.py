@@ -11,7 +11,8 @@ the reference's resolve (mean -> sqrt -> 8-bit, Raytracing_n.cpp:848-862).  `val
 is the same metric through the C-ABI calls that take HOST buffers (srt_scene_create from the host
 scene description, render, 8-bit image into pinned host memory), copies inside the timed region.
 With N > 1 (torchrun) the Sobol index range [0, ns) is split across ranks and the int64 fixed-point
-accumulation buffers are summed with ONE NCCL reduce.
+accumulation buffers are summed exactly with one NCCL reduce-scatter, resolved per tile, and the 8-bit tiles
+gathered.
 
 The ONE JSON line describes the headline workload (BASELINE.json:configs[1], C2 random spheres) and
 carries `per_config`: the same measurement (value, e2e, cpu_baseline, kernel, roofline, counters) for
@@ -363,17 +364,25 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
         f"{info['n_prims']} prims, {info['device_bytes'] / 1e6:.1f} MB")
     s0, s1 = multigpu.sample_shard(ns, rt.rank, rt.world)
     params = render.render_params(nx, ny, ns, s0, s1, seed=SEED)
-    fixed = torch.zeros(n_pixels * 3, dtype=torch.int64, device=rt.dev)
+    # N = 1: the kernels add into `fixed`, srt_resolve_fixed resolves and clears it.  N > 1: the tiled exchange
+    # (multigpu.exchange_tiles): reduce-scatter of the int64 buffers, resolve per tile, all-gather of the 8-bit tiles
+    ex = multigpu.TileExchange(n_pixels, rt.world, rt.dev)
+    fixed = ex.fixed
     rgb8 = torch.zeros(n_pixels * 3, dtype=torch.uint8, device=rt.dev)
 
-    def step(out):
-        # the whole frame: this rank's shard into the int64 buffer, ONE exact reduce, resolve (+ clear) on rank 0
-        sc.render_fixed(params, fixed)
-        multigpu.reduce_accum(fixed, 0)
-        if rt.rank == 0:
-            rt.ctx.resolve_fixed(fixed, n_pixels, ns, out, None, clear=True)
+    def resolve_tile(tile, n_tile_pixels, n_samples, rgb_tile):
+        rt.ctx.resolve_fixed(tile, n_tile_pixels, n_samples, rgb_tile, None, clear=False)
+
+    def exchange(out):
+        if rt.world > 1:
+            multigpu.exchange_tiles(ex, ns, resolve_tile)
         else:
-            fixed.zero_()
+            rt.ctx.resolve_fixed(fixed, n_pixels, ns, out, None, clear=True)
+
+    def step(out):
+        # the whole frame: this rank's shard into the int64 buffer, the exchange step, the resolved image
+        sc.render_fixed(params, fixed)
+        exchange(out)
 
     clk = None
     with torch.cuda.stream(rt.stream):
@@ -394,11 +403,7 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
             kev[k][0].record(rt.stream)
             sc.render_fixed(params, fixed)
             kev[k][1].record(rt.stream)
-            multigpu.reduce_accum(fixed, 0)
-            if rt.rank == 0:
-                rt.ctx.resolve_fixed(fixed, n_pixels, ns, rgb8, None, clear=True)
-            else:
-                fixed.zero_()
+            exchange(rgb8)
             ev[k][1].record(rt.stream)
         rt.sync_all()
         if clocks:
@@ -428,12 +433,10 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
         parts["scene_create_ms"] += (tb - ta) * 1e3
         if rt.world > 1:
             sc2.render_fixed(params, fixed)
-            multigpu.reduce_accum(fixed, 0)
+            exchange(None)
             if rt.rank == 0:
-                rt.ctx.resolve_fixed(fixed, n_pixels, ns, host_rgb.numpy(), None, clear=True)  # d2h + sync inside
-            else:
-                fixed.zero_()
-                torch.cuda.synchronize(rt.dev)
+                host_rgb.copy_(ex.image(), non_blocking=True)  # d2h of the gathered 8-bit image
+            torch.cuda.synchronize(rt.dev)
         else:
             sc2.render_image(params, rgb8=host_rgb.numpy())  # d2h + sync inside
         parts["render_ms"] += (time.perf_counter() - tb) * 1e3
@@ -454,7 +457,7 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
     e2e_s = rt.max_over_ranks(e2e_s)
     overflow = rt.ctx.counters()["stack_overflows"]
     sc.close()
-    del fixed, rgb8
+    del fixed, rgb8, ex
 
     res = None
     if rt.rank == 0:
@@ -607,7 +610,8 @@ def main():
             "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": head["workload"], "nx": head["nx"], "ny": head["ny"], "spp": head["spp"],
-                       "max_depth": 50, "parallelism": f"sample-range x{rt.world}, one int64 ncclReduce",
+                       "max_depth": 50, "parallelism": (f"sample-range x{rt.world}, int64 reduce-scatter + per-tile resolve + uint8 all-gather"
+                                       if rt.world > 1 else "one GPU"),
                        "l2": "flushed between timed steps (256 MiB write)",
                        "scene_device_bytes": head["scene"]["device_bytes"], "bvh_nodes": head["scene"]["bvh_nodes"]},
             "mrays_per_s": head["mrays_per_s"], "rays_per_path": head["rays_per_path"],

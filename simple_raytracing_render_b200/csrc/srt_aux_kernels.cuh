@@ -32,7 +32,7 @@ __global__ void __launch_bounds__(128) k_trace_closest(DScene S, const float* __
     prim[i] = h.prim;
     t[i] = h.t;
     if (rec) {
-        HitRecord hr = make_record<FM, true>(W, r, h);
+        HitRecord hr = make_record<FM>(W, r, h, true);
         float* o = rec + 8 * i;
         o[0] = hr.u;
         o[1] = hr.v;

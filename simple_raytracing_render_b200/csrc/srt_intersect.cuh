@@ -644,11 +644,22 @@ SRT_DEV bool entry_geom_hit(const View& W, const DEntry* ep, const DEntry& e, co
 template <uint32_t F, bool COUNT>
 SRT_DEV bool medium_hit(const View& W, const DEntry* ep, const DEntry& e, const Ray& r, const RayK& qw, float t_min,
                         float t_max, Philox& rng, float& t, Tally<COUNT> tl) {
-    float t1, t2;
-    int32_t p1, p2;
-    if (!entry_geom_hit<F>(W, ep, e, r, qw, -kFltMax, kFltMax, true, t1, p1, tl)) return false;
-    float t_min2 = (float)((double)t1 + 0.0001);
-    if (!entry_geom_hit<F>(W, ep, e, r, qw, t_min2, kFltMax, true, t2, p2, tl)) return false;
+    // the two boundary hits (constant_medium.h:22-25) through ONE call site: two inlined copies of the list walk and
+    // of the traversal were a fifth of the code of the variants with media
+    float t1 = 0.f, t2 = 0.f;
+    float lo = -kFltMax;
+#pragma unroll 1
+    for (int k = 0; k < 2; k++) {
+        float tk;
+        int32_t pk;
+        if (!entry_geom_hit<F>(W, ep, e, r, qw, lo, kFltMax, true, tk, pk, tl)) return false;
+        if (k == 0) {
+            t1 = tk;
+            lo = (float)((double)t1 + 0.0001);
+        } else {
+            t2 = tk;
+        }
+    }
     if (t1 < t_min) t1 = t_min;
     if (t2 > t_max) t2 = t_max;
     if (t1 >= t2) return false;
@@ -684,12 +695,9 @@ SRT_DEV Hit world_hit(const View& W, const Ray& r, float t_min, float t_max, Phi
         if ((F & F_MEDIA) && e.medium >= 0) {
             got = medium_hit<F>(W, ep, e, r, qw, t_min, closest, rng, t, tl);
             prim = W.S.n_prims + e.medium;
-        } else if (e.op_count == 0 && e.geom_kind == SRT_GEOM_GROUP) {
-            // fast path: untransformed list of primitives shares the world-frame ray constants
-            if ((e.flags & DENTRY_CULL) && !entry_bounds_hit(ep, qw, t_min, closest, (e.flags & DENTRY_TCULL) != 0))
-                continue;
-            got = group_hit<F>(W, e.first_prim, e.prim_count, qw, t_min, closest, false, t, prim, tl);
         } else {
+            // one call site for every kind of entry (an untransformed one reuses qw inside): a second inlined copy
+            // of the list walk with all its primitive tests was ~3 % of every variant's code
             got = entry_geom_hit<F>(W, ep, e, r, qw, t_min, closest, false, t, prim, tl);
         }
         if (got) {
@@ -713,8 +721,9 @@ SRT_DEV void get_sphere_uv(V3 p, float& u, float& v) {
 
 // Re-runs the winning primitive's arithmetic to fill u, v, p, normal exactly as its hit() does,
 // then unwinds flip_normals and the instance chain (aarect.h:152-159, hitable.h:44-52, :109-132).
-template <uint32_t F, bool WANT_UV>
-SRT_DEV HitRecord make_record(const View& W, const Ray& world_ray, const Hit& h) {
+// `want_uv` is a run-time flag (one copy of this routine per kernel, not one per value: srt_shade.cuh asked for both).
+template <uint32_t F>
+SRT_DEV HitRecord make_record(const View& W, const Ray& world_ray, const Hit& h, bool want_uv) {
     const DScene& S = W.S;
     HitRecord rec;
     rec.t = h.t;
@@ -734,7 +743,7 @@ SRT_DEV HitRecord make_record(const View& W, const Ray& world_ray, const Hit& h)
     if (type >= SRT_PRIM_XY_RECT && type <= SRT_PRIM_YZ_RECT) {
         int aa = type == SRT_PRIM_YZ_RECT ? 1 : 0;
         int ab = type == SRT_PRIM_XY_RECT ? 1 : 2;
-        if (WANT_UV) {
+        if (want_uv) {
             float a = xadd(comp(r.o, aa), xmul(h.t, comp(r.d, aa)));
             float b = xadd(comp(r.o, ab), xmul(h.t, comp(r.d, ab)));
             rec.u = xdiv(xsub(a, pr.g.x), xsub(pr.g.y, pr.g.x));
@@ -747,7 +756,7 @@ SRT_DEV HitRecord make_record(const View& W, const Ray& world_ray, const Hit& h)
         V3 c = v3(pr.g.x, pr.g.y, pr.g.z);
         rec.p = point_at(r, h.t);
         V3 qn = (rec.p - c) / pr.g.w;
-        if (WANT_UV) get_sphere_uv(qn, rec.u, rec.v);
+        if (want_uv) get_sphere_uv(qn, rec.u, rec.v);
         rec.normal = type == SRT_PRIM_SPHERE ? qn : (c - rec.p) / pr.g.w;
     } else if ((F & (F_TRI | F_BVH_TRI)) && type == SRT_PRIM_TRIANGLE) {
         size_t row = pr.flags_aux >> 1;
@@ -758,7 +767,7 @@ SRT_DEV HitRecord make_record(const View& W, const Ray& world_ray, const Hit& h)
         // a hit found through a medium boundary may be the back-face variant
         tri_hit(p0, p1, p2, r.o, tri_dir(r), true, t, u, v);
         float w = xsub(xsub(1.0f, u), v);
-        if (WANT_UV) {
+        if (want_uv) {
             const float* uv = S.tri_uv + 6 * row;
             rec.u = xadd(xadd(xmul(w, uv[0]), xmul(u, uv[2])), xmul(v, uv[4]));
             rec.v = xadd(xadd(xmul(w, uv[1]), xmul(u, uv[3])), xmul(v, uv[5]));

@@ -364,12 +364,18 @@ SRT_DEV ShadeStatus shade_hit(const View& W, Path& P, const Hit& h, int max_dept
         mat_index = load_prim(W.dprims + h.prim).material;
     if (mat_index < 0) return SHADE_ENDED;  // no material: the reference would dereference null
     DMaterial m = load_material(S.materials + mat_index);
-    HitRecord rec = material_needs_uv<F>(m) ? make_record<F, true>(W, P.r, h) : make_record<F, false>(W, P.r, h);
+    HitRecord rec = make_record<F>(W, P.r, h, material_needs_uv<F>(m));
     const Ray r = P.r;
+    // the texture of the material at the hit, evaluated at ONE place for emission / attenuation / albedo below (three
+    // inlined copies of the texture code — image lookup, checker chain, seven octaves of perlin — were 5-10 % of the
+    // variants that have them); brdfmaterial and metal keep their colour in the record itself
+    const V3 mcol = (m.type == SRT_MAT_BRDF || m.type == SRT_MAT_METAL || m.type == SRT_MAT_DIELECTRIC)
+                        ? v3(m.c[0], m.c[1], m.c[2])
+                        : material_color<F>(S, m, rec);
 
     if (m.type == SRT_MAT_DIFFUSE_LIGHT) {  // material.h:348-354: one-sided; scatter() returns false
         if (fm::dot(rec.normal, r.d) < 0.f) {
-            V3 e = material_color<F>(S, m, rec);
+            V3 e = mcol;
             P.L = v3(fmaf(P.thr.x, e.x, P.L.x), fmaf(P.thr.y, e.y, P.L.y), fmaf(P.thr.z, e.z, P.L.z));
         } else {
             P.L = fm::madd(P.thr, 0.f, P.L);
@@ -419,7 +425,7 @@ SRT_DEV ShadeStatus shade_hit(const View& W, Path& P, const Hit& h, int max_dept
     if ((F & F_MEDIA) && m.type == SRT_MAT_ISOTROPIC) {  // material.h:362-367
         philox_fresh(rng);
         V3 dir = random_in_unit_sphere(rng);
-        P.thr = fm::mul(P.thr, material_color<F>(S, m, rec));
+        P.thr = fm::mul(P.thr, mcol);
         P.r = Ray{rec.p, dir, 0.f};
         P.depth++;
         return SHADE_CONTINUES;
@@ -439,7 +445,7 @@ SRT_DEV ShadeStatus shade_hit(const View& W, Path& P, const Hit& h, int max_dept
         C.attenuation = v3(m.c[0], m.c[1], m.c[2]);
         B.kind = SRT_MAT_LAMBERTIAN;
     } else {
-        C.attenuation = material_color<F>(S, m, rec);
+        C.attenuation = mcol;
         B.kind = (F & (F_ORENNAYAR | F_BECKMANN)) ? m.type : SRT_MAT_LAMBERTIAN;
     }
     B.uvw = onb_fast(rec.normal);
@@ -632,7 +638,7 @@ SRT_DEV V3 emitted_at(const View& W, const Ray& r, const Hit& h) {
     if (mat_index < 0) return v3(0.f, 0.f, 0.f);
     DMaterial m = load_material(S.materials + mat_index);
     if (m.type != SRT_MAT_DIFFUSE_LIGHT) return v3(0.f, 0.f, 0.f);
-    HitRecord rec = material_needs_uv<F>(m) ? make_record<F, true>(W, r, h) : make_record<F, false>(W, r, h);
+    HitRecord rec = make_record<F>(W, r, h, material_needs_uv<F>(m));
     if (!(fm::dot(rec.normal, r.d) < 0.f)) return v3(0.f, 0.f, 0.f);
     return material_color<F>(S, m, rec);
 }
@@ -653,7 +659,7 @@ SRT_DEV bool shade_bounce_corrected(const View& W, Path& P, const Hit& h, int ma
         mat_index = load_prim(W.dprims + h.prim).material;
     if (mat_index < 0) return false;
     DMaterial m = load_material(S.materials + mat_index);
-    HitRecord rec = material_needs_uv<F>(m) ? make_record<F, true>(W, P.r, h) : make_record<F, false>(W, P.r, h);
+    HitRecord rec = make_record<F>(W, P.r, h, material_needs_uv<F>(m));
     const Ray r = P.r;
     if (m.type == SRT_MAT_DIFFUSE_LIGHT) {
         if (fm::dot(rec.normal, r.d) < 0.f) {

@@ -12,6 +12,11 @@ reduce order in the last float bits) and int64 fixed point (`render_sharded_fixe
 an exact integer reduce + srt_resolve_fixed — the form bench.py times: no clear pass, no conversion
 kernel, and the N-GPU image is bit-identical to the 1-GPU image).
 
+The exchange step bench.py times is the TILED form of the same sum (`TileExchange`, `exchange_tiles`): one
+reduce-scatter of the int64 buffers (rank g ends up with the exact sums of pixel tile g: every link carries 1/N of
+the buffer instead of rank 0 receiving all of it), the resolve of that tile on its rank, and one all-gather of the
+8-bit tiles — 0.35 -> ~0.1 ms of a 3.7 ms C2 frame on 8 GPUs, and every rank holds the finished image.
+
 The shard arithmetic and the reduce are device-agnostic (tests/test_multigpu_cpu.py runs them over
 gloo with CPU tensors); rendering and resolving need the CUDA backend.
 """
@@ -80,3 +85,38 @@ def render_sharded_fixed(scene, nx: int, ny: int, ns: int, fixed, rgb8=None, max
     else:
         fixed.zero_()
     return s0, s1
+
+
+class TileExchange:
+    """Buffers of the tiled exchange step for images of `n_pixels` pixels on `world_size` ranks: the pixel range is
+    padded to a multiple of world_size and cut into equal tiles, tile g belongs to rank g.
+      fixed    int64 [padded_pixels * 3]  this rank's fixed-point sums (srt_render_fixed adds into its first n_pixels * 3)
+      tile     int64 [tile_pixels * 3]    the summed tile after the reduce-scatter
+      rgb_tile uint8 [tile_pixels * 3]    the resolved tile
+      rgb      uint8 [padded_pixels * 3]  the gathered image (its first n_pixels * 3 values)"""
+
+    def __init__(self, n_pixels: int, world_size: int, device):
+        import torch
+        self.n_pixels, self.world_size = int(n_pixels), int(world_size)
+        self.tile_pixels = -(-self.n_pixels // self.world_size)
+        self.padded_pixels = self.tile_pixels * self.world_size
+        self.fixed = torch.zeros(self.padded_pixels * 3, dtype=torch.int64, device=device)
+        self.tile = torch.empty(self.tile_pixels * 3, dtype=torch.int64, device=device)
+        self.rgb_tile = torch.empty(self.tile_pixels * 3, dtype=torch.uint8, device=device)
+        self.rgb = torch.empty(self.padded_pixels * 3, dtype=torch.uint8, device=device)
+
+    def image(self):
+        return self.rgb[: self.n_pixels * 3]
+
+
+def exchange_tiles(ex: TileExchange, n_samples: int, resolve_tile, group=None):
+    """The exchange step in tiles.  `ex.fixed` holds this rank's sums on entry and is ZERO on return;
+    `resolve_tile(tile_int64, n_tile_pixels, n_samples, rgb_tile_uint8)` is the backend's mean -> sqrt -> 8-bit
+    (Context.resolve_fixed on the GPU; the CPU test passes a numpy restatement).  Every rank returns with the whole
+    image in ex.image()."""
+    import torch.distributed as dist
+    dist.reduce_scatter_tensor(ex.tile, ex.fixed, op=dist.ReduceOp.SUM, group=group)
+    resolve_tile(ex.tile, ex.tile_pixels, n_samples, ex.rgb_tile)
+    ex.fixed.zero_()
+    dist.all_gather_into_tensor(ex.rgb, ex.rgb_tile, group=group)
+    return ex.image()

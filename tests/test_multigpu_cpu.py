@@ -30,6 +30,17 @@ def _contribution(s, n):
     return (((i * 7 + s * 13) % 32) / 8.0).astype(np.float32)
 
 
+def _resolve_numpy(fixed, n_samples):
+    """Raytracing_n.cpp:848-862 on 2^-31 fixed-point sums: mean, sqrt, int(255.99 c)."""
+    c = np.sqrt(fixed.astype(np.float64) / 2.0 ** 31 / n_samples)
+    return np.clip((255.99 * c).astype(np.int64), 0, 255).astype(np.uint8)
+
+
+def _resolve_tile_numpy(tile, n_tile_pixels, n_samples, rgb_tile):
+    import torch
+    rgb_tile.copy_(torch.from_numpy(_resolve_numpy(tile.numpy(), n_samples)))
+
+
 def _worker(rank, world, port, ns, n, out_dir):
     import torch
     import torch.distributed as dist
@@ -49,6 +60,12 @@ def _worker(rank, world, port, ns, n, out_dir):
         multigpu.reduce_accum(fx, dst=0)
         np.save(os.path.join(out_dir, f"fixed{rank}.npy"), fx.numpy())
         np.save(os.path.join(out_dir, f"own{rank}.npy"), acc)
+        # the tiled exchange bench.py times: reduce-scatter, resolve per tile, all-gather of the 8-bit tiles
+        ex = multigpu.TileExchange(n // 3, world, "cpu")
+        ex.fixed[:n] = torch.from_numpy(np.round(acc.astype(np.float64) * 2.0 ** 31).astype(np.int64))
+        img = multigpu.exchange_tiles(ex, ns, _resolve_tile_numpy)
+        np.save(os.path.join(out_dir, f"tiles{rank}.npy"), img.numpy())
+        assert int(ex.fixed.abs().sum()) == 0
     finally:
         dist.destroy_process_group()
 
@@ -69,6 +86,11 @@ def test_two_rank_reduce_equals_unsharded(tmp_path):
     assert fixed.dtype == np.int64 and np.array_equal(fixed, np.round(whole.astype(np.float64) * 2.0 ** 31).astype(np.int64))
     own = [np.load(tmp_path / f"own{r}.npy") for r in range(world)]
     assert np.array_equal(own[0] + own[1], whole)
+    # tiled exchange: every rank ends with the image the unsharded sums resolve to (37 * 21 pixels do not divide by 2:
+    # the last tile is padded)
+    want = _resolve_numpy(np.round(whole.astype(np.float64) * 2.0 ** 31).astype(np.int64), ns)
+    for r in range(world):
+        assert np.array_equal(np.load(tmp_path / f"tiles{r}.npy"), want)
 
 
 def test_reduce_is_a_noop_without_a_process_group():
