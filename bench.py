@@ -11,8 +11,8 @@ the reference's resolve (mean -> sqrt -> 8-bit, Raytracing_n.cpp:848-862).  `val
 is the same metric through the C-ABI calls that take HOST buffers (srt_scene_create from the host
 scene description, render, 8-bit image into pinned host memory), copies inside the timed region.
 With N > 1 (torchrun) the Sobol index range [0, ns) is split across ranks and the int64 fixed-point
-accumulation buffers are summed exactly with one NCCL reduce-scatter, resolved per tile, and the 8-bit tiles
-gathered.
+accumulation buffers are summed exactly, resolved per pixel tile and the 8-bit tiles distributed by ONE kernel
+over NVLink peer memory (NCCL reduce-scatter / all-gather as the fallback).
 
 The ONE JSON line describes the headline workload (BASELINE.json:configs[1], C2 random spheres) and
 carries `per_config`: the same measurement (value, e2e, cpu_baseline, kernel, roofline, counters) for
@@ -373,15 +373,33 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
     def resolve_tile(tile, n_tile_pixels, n_samples, rgb_tile):
         rt.ctx.resolve_fixed(tile, n_tile_pixels, n_samples, rgb_tile, None, clear=False)
 
-    def exchange(out):
-        if rt.world > 1:
+    # N > 1, default: the exchange as ONE kernel over NVLink peer memory (multigpu.PeerExchange); SRT_PEER_EXCHANGE=0, or a
+    # box without peer mappings, falls back to the NCCL form (reduce-scatter + per-tile resolve + all-gather)
+    peer = None
+    if rt.world > 1 and os.environ.get("SRT_PEER_EXCHANGE", "1") != "0":
+        try:
+            with torch.cuda.stream(rt.stream):
+                peer = multigpu.PeerExchange(rt.ctx, n_pixels)
+        except Exception as e:  # noqa: BLE001 — every rank fails alike (same box), so the fallback is collective too
+            log(f"{name}: peer-memory exchange unavailable ({e}); NCCL tiles instead")
+            peer = None
+    exchange_kind = "one kernel over NVLink peer memory" if peer is not None else \
+        ("NCCL int64 reduce-scatter + per-tile resolve + uint8 all-gather" if rt.world > 1 else "none (one GPU)")
+
+    def render_into(scene):
+        scene.render_fixed(params, peer.fixed() if peer is not None else fixed)
+
+    def exchange(out, host=None):
+        if peer is not None:
+            peer.run(ns, host)
+        elif rt.world > 1:
             multigpu.exchange_tiles(ex, ns, resolve_tile)
         else:
             rt.ctx.resolve_fixed(fixed, n_pixels, ns, out, None, clear=True)
 
     def step(out):
         # the whole frame: this rank's shard into the int64 buffer, the exchange step, the resolved image
-        sc.render_fixed(params, fixed)
+        render_into(sc)
         exchange(out)
 
     clk = None
@@ -401,7 +419,7 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
                 dist.barrier()
             ev[k][0].record(rt.stream)
             kev[k][0].record(rt.stream)
-            sc.render_fixed(params, fixed)
+            render_into(sc)
             kev[k][1].record(rt.stream)
             exchange(rgb8)
             ev[k][1].record(rt.stream)
@@ -432,10 +450,13 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
         tb = time.perf_counter()
         parts["scene_create_ms"] += (tb - ta) * 1e3
         if rt.world > 1:
-            sc2.render_fixed(params, fixed)
-            exchange(None)
-            if rt.rank == 0:
-                host_rgb.copy_(ex.image(), non_blocking=True)  # d2h of the gathered 8-bit image
+            render_into(sc2)
+            if peer is not None:
+                exchange(None, host_rgb.numpy() if rt.rank == 0 else None)  # d2h of the finished image + sync inside
+            else:
+                exchange(None)
+                if rt.rank == 0:
+                    host_rgb.copy_(ex.image(), non_blocking=True)  # d2h of the gathered 8-bit image
             torch.cuda.synchronize(rt.dev)
         else:
             sc2.render_image(params, rgb8=host_rgb.numpy())  # d2h + sync inside
@@ -457,6 +478,8 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
     e2e_s = rt.max_over_ranks(e2e_s)
     overflow = rt.ctx.counters()["stack_overflows"]
     sc.close()
+    if peer is not None:
+        peer.close()
     del fixed, rgb8, ex
 
     res = None
@@ -479,7 +502,7 @@ def measure_config(rt, name, steps, warmup, want_cpu, want_clocks=False):
                       "bvh_nodes": int(info["bvh_nodes"]), "bvh_max_depth": int(info["bvh_max_depth"]),
                       "bvh_builder": "device LBVH" if info.get("bvh_builder") else "host binned SAH",
                       "host_scene_s": host_scene_s, "scene_create_s": first_create_s},
-            "gpu_launches": int(launches),
+            "gpu_launches": int(launches), "exchange": exchange_kind,
         }
         if clk is not None:
             res["clocks"] = clk
@@ -610,8 +633,7 @@ def main():
             "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "strong",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": head["workload"], "nx": head["nx"], "ny": head["ny"], "spp": head["spp"],
-                       "max_depth": 50, "parallelism": (f"sample-range x{rt.world}, int64 reduce-scatter + per-tile resolve + uint8 all-gather"
-                                       if rt.world > 1 else "one GPU"),
+                       "max_depth": 50, "parallelism": (f"sample-range x{rt.world}; exchange: {head['exchange']}" if rt.world > 1 else "one GPU"),
                        "l2": "flushed between timed steps (256 MiB write)",
                        "scene_device_bytes": head["scene"]["device_bytes"], "bvh_nodes": head["scene"]["bvh_nodes"]},
             "mrays_per_s": head["mrays_per_s"], "rays_per_path": head["rays_per_path"],

@@ -353,6 +353,27 @@ int srt_render_fixed(SrtScene* scene, const SrtRenderParams* params, int64_t* fi
 int srt_resolve_fixed(SrtContext* ctx, int64_t* fixed_device, int64_t n_pixels, int32_t n_samples, uint8_t* rgb8_out,
                       float* accum_out_device, int clear);
 
+/* The exchange step of the multi-GPU path as ONE kernel over NVLink peer memory, replacing the
+ * ncclReduce + srt_resolve_fixed pair above for the ranks of one box.  Every rank creates its side (one device block:
+ * two int64 accumulation buffers that alternate by frame, the 8-bit image, flags), publishes a 64-byte IPC handle,
+ * and connects to the handles of all ranks (in rank order, its own included).  Per frame: srt_render_fixed into
+ * srt_exchange_fixed(), then srt_exchange_run(): rank g waits INSIDE the kernel until every rank has finished
+ * rendering, sums pixel tile g over the buffers of all ranks with peer loads, resolves it
+ * (Raytracing_n.cpp:848-862) and stores the 8-bit tile into the image of every rank; when the call's work has run on
+ * the stream the whole image is in srt_exchange_image() on every rank (copied to rgb8_host when that is non-NULL,
+ * which synchronises).  The accumulation buffer of the NEXT frame is zero on return.  Every rank must make the same
+ * sequence of calls; a rank that does not arrive within a few seconds makes the others return SRT_E_CUDA instead of
+ * hanging.  n_ranks <= 16. */
+typedef struct SrtExchange SrtExchange;
+#define SRT_EXCHANGE_HANDLE_BYTES 64
+int srt_exchange_create(SrtContext* ctx, int64_t n_pixels, int32_t n_ranks, int32_t rank, SrtExchange** out);
+int srt_exchange_handle(SrtExchange* ex, uint8_t* handle_out);
+int srt_exchange_connect(SrtExchange* ex, const uint8_t* handles_of_all_ranks);
+int64_t* srt_exchange_fixed(SrtExchange* ex);
+uint8_t* srt_exchange_image(SrtExchange* ex);
+int srt_exchange_run(SrtExchange* ex, int32_t n_samples, uint8_t* rgb8_host);
+int srt_exchange_destroy(SrtExchange* ex);
+
 /* Whole-image convenience with HOST buffers: zero an internal accumulation buffer, srt_render
  * over [s_begin, s_end), srt_resolve, copy back.  rgb8_host: nx*ny*3 bytes; accum_host (optional,
  * may be NULL): nx*ny*3 floats of linear radiance sums.

@@ -1719,6 +1719,135 @@ int srt_resolve_fixed(SrtContext* c, int64_t* fixed_device, int64_t n_pixels, in
     return 0;
 }
 
+
+// ---- peer-memory exchange (srt_aux_kernels.cuh: k_exchange_peers) ------------------------------------------------
+struct SrtExchange {
+    SrtContext* ctx = nullptr;
+    int n_ranks = 0, rank = 0;
+    long long n_pixels = 0, tile_values = 0, n_values = 0, padded_values = 0;
+    size_t off_fixed[2] = {0, 0}, off_rgb = 0, off_flags = 0, bytes = 0;
+    uint8_t* block = nullptr;                   // this rank's block (cudaMalloc)
+    uint8_t* base[srt::kExMaxRanks] = {};       // every rank's block as mapped here (base[rank] == block)
+    unsigned* d_cta_counter = nullptr;
+    unsigned frame = 0;
+    bool connected = false;
+};
+
+int srt_exchange_create(SrtContext* ctx, int64_t n_pixels, int32_t n_ranks, int32_t rank, SrtExchange** out) {
+    if (!ctx || !out) return fail(SRT_E_INVALID, "null argument");
+    *out = nullptr;
+    if (n_pixels <= 0 || n_ranks < 1 || n_ranks > srt::kExMaxRanks || rank < 0 || rank >= n_ranks)
+        return fail(SRT_E_INVALID, "srt_exchange_create: bad sizes");
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    SrtExchange* ex = new SrtExchange();
+    ex->ctx = ctx;
+    ex->n_ranks = n_ranks;
+    ex->rank = rank;
+    ex->n_pixels = n_pixels;
+    ex->n_values = 3 * n_pixels;
+    ex->tile_values = ((ex->n_values + n_ranks - 1) / n_ranks + 3) & ~3ll;  // a multiple of 4: one word of 8-bit values per thread
+    ex->padded_values = ex->tile_values * n_ranks;
+    const size_t fixed_bytes = ((size_t)ex->padded_values * 8 + 255) & ~(size_t)255;
+    ex->off_fixed[0] = 0;
+    ex->off_fixed[1] = fixed_bytes;
+    ex->off_rgb = 2 * fixed_bytes;
+    ex->off_flags = ex->off_rgb + (((size_t)ex->padded_values + 255) & ~(size_t)255);
+    ex->bytes = ex->off_flags + 256;
+    cudaError_t e = cudaMalloc(&ex->block, ex->bytes);
+    if (e == cudaSuccess) e = cudaMalloc(&ex->d_cta_counter, sizeof(unsigned));
+    if (e == cudaSuccess) e = cudaMemsetAsync(ex->block, 0, ex->bytes, ctx->stream);
+    if (e == cudaSuccess) e = cudaMemsetAsync(ex->d_cta_counter, 0, sizeof(unsigned), ctx->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(ctx->stream);
+    if (e != cudaSuccess) {
+        cudaFree(ex->block);
+        cudaFree(ex->d_cta_counter);
+        delete ex;
+        return fail(SRT_E_CUDA, "srt_exchange_create: %s", cudaGetErrorString(e));
+    }
+    ex->base[rank] = ex->block;
+    *out = ex;
+    return 0;
+}
+
+int srt_exchange_handle(SrtExchange* ex, uint8_t* handle_out) {
+    if (!ex || !handle_out) return fail(SRT_E_INVALID, "null argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == SRT_EXCHANGE_HANDLE_BYTES, "IPC handle size");
+    CUDA_TRY(cudaSetDevice(ex->ctx->device));
+    cudaIpcMemHandle_t h;
+    CUDA_TRY(cudaIpcGetMemHandle(&h, ex->block));
+    std::memcpy(handle_out, &h, sizeof h);
+    return 0;
+}
+
+int srt_exchange_connect(SrtExchange* ex, const uint8_t* handles) {
+    if (!ex || !handles) return fail(SRT_E_INVALID, "null argument");
+    CUDA_TRY(cudaSetDevice(ex->ctx->device));
+    for (int r = 0; r < ex->n_ranks; r++) {
+        if (r == ex->rank) continue;
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + (size_t)r * SRT_EXCHANGE_HANDLE_BYTES, sizeof h);
+        void* p = nullptr;
+        cudaError_t e = cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess);
+        if (e != cudaSuccess) return fail(SRT_E_CUDA, "srt_exchange_connect: rank %d: %s", r, cudaGetErrorString(e));
+        ex->base[r] = static_cast<uint8_t*>(p);
+    }
+    ex->connected = true;
+    return 0;
+}
+
+int64_t* srt_exchange_fixed(SrtExchange* ex) {
+    return ex ? reinterpret_cast<int64_t*>(ex->block + ex->off_fixed[(ex->frame + 1) & 1]) : nullptr;  // the NEXT frame's buffer
+}
+
+uint8_t* srt_exchange_image(SrtExchange* ex) { return ex ? ex->block + ex->off_rgb : nullptr; }
+
+int srt_exchange_run(SrtExchange* ex, int32_t n_samples, uint8_t* rgb8_host) {
+    if (!ex) return fail(SRT_E_INVALID, "null argument");
+    if (!ex->connected && ex->n_ranks > 1) return fail(SRT_E_INVALID, "srt_exchange_run before srt_exchange_connect");
+    SrtContext* c = ex->ctx;
+    CUDA_TRY(cudaSetDevice(c->device));
+    ex->frame++;
+    srt::ExArgs a = {};
+    for (int r = 0; r < ex->n_ranks; r++) a.base[r] = ex->base[r];
+    a.n_ranks = ex->n_ranks;
+    a.rank = ex->rank;
+    a.tile_values = ex->tile_values;
+    a.n_values = ex->n_values;
+    a.off_fixed = (long long)ex->off_fixed[ex->frame & 1];
+    a.off_rgb = (long long)ex->off_rgb;
+    a.off_flags = (long long)ex->off_flags;
+    a.ns = (float)n_samples;
+    a.frame = ex->frame;
+    const unsigned grid = (unsigned)((ex->tile_values / 4 + 255) / 256);
+    srt::k_exchange_peers<<<grid, 256, 0, c->stream>>>(a, ex->d_cta_counter);
+    srt::k_exchange_wait<<<1, 32, 0, c->stream>>>(reinterpret_cast<unsigned*>(ex->block + ex->off_flags), ex->n_ranks, ex->frame);
+    c->launches += 2;
+    CUDA_TRY(cudaGetLastError());
+    // the sums of the PREVIOUS frame: every rank has finished reading them (it arrived at this frame's barrier after its
+    // previous exchange kernel), so their owner clears them for the next frame
+    CUDA_TRY(cudaMemsetAsync(ex->block + ex->off_fixed[(ex->frame + 1) & 1], 0, (size_t)ex->padded_values * 8, c->stream));
+    if (rgb8_host) {
+        CUDA_TRY(cudaMemcpyAsync(rgb8_host, ex->block + ex->off_rgb, (size_t)ex->n_values, cudaMemcpyDeviceToHost, c->stream));
+        CUDA_TRY(cudaStreamSynchronize(c->stream));
+        unsigned err = 0;
+        CUDA_TRY(cudaMemcpy(&err, ex->block + ex->off_flags + 128, sizeof err, cudaMemcpyDeviceToHost));
+        if (err) return fail(SRT_E_CUDA, "srt_exchange_run: a rank did not arrive (time-out inside the exchange kernel)");
+    }
+    return 0;
+}
+
+int srt_exchange_destroy(SrtExchange* ex) {
+    if (!ex) return 0;
+    cudaSetDevice(ex->ctx->device);
+    cudaStreamSynchronize(ex->ctx->stream);
+    for (int r = 0; r < ex->n_ranks; r++)
+        if (r != ex->rank && ex->base[r]) cudaIpcCloseMemHandle(ex->base[r]);
+    cudaFree(ex->block);
+    cudaFree(ex->d_cta_counter);
+    delete ex;
+    return 0;
+}
+
 int srt_primary_rays(SrtScene* s, const SrtRenderParams* p, float* rays_out) {
     if (!s || !rays_out) return fail(SRT_E_INVALID, "null argument");
     int rc = check_params(p);

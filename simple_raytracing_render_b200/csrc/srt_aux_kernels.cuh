@@ -123,6 +123,102 @@ __global__ void __launch_bounds__(256) k_resolve_fixed(long long* __restrict__ f
     }
 }
 
+// ---- the exchange step of the multi-GPU path over NVLink PEER MEMORY --------------------
+// Every rank holds one block [fixed 0 | fixed 1 | rgb | flags] that all ranks of the box have mapped
+// (cudaIpcOpenMemHandle).  Frame f accumulates in `fixed (f & 1)`.  k_exchange_peers on rank g:
+//   1. ARRIVE: tells every rank "g has finished rendering frame f" (a 4-byte remote store per rank), then waits until
+//      every rank has told it the same — the only synchronisation of the step, inside the kernel, no host, no NCCL;
+//   2. for ITS pixel tile: loads the int64 sums of all ranks (local + peer loads over NVLink, 16 bytes per load), adds
+//      them exactly, resolves (mean -> sqrt -> int(255.99 c) -> clamp, Raytracing_n.cpp:848-862) and stores the four
+//      8-bit values of a thread as one word into the image of EVERY rank;
+//   3. DONE: the last CTA tells every rank that tile g of frame f is complete in its image.
+// k_exchange_wait then holds the stream until the tiles of all ranks have arrived.  The sums of frame f are cleared by
+// their owner after ITS frame-(f+1) kernel has passed step 1: by then every rank has finished reading them.
+// The waits are bounded (a rank that died must not hang the others' GPUs): a time-out raises a flag the host reads.
+constexpr int kExMaxRanks = 16;
+struct ExArgs {
+    uint8_t* base[kExMaxRanks];  // the block of every rank, as mapped into THIS process
+    int n_ranks, rank;
+    long long tile_values, n_values;  // values per tile (a multiple of 4), values of the image
+    long long off_fixed, off_rgb, off_flags;  // byte offsets inside a block; off_fixed is that of THIS frame's buffer
+    float ns;
+    unsigned frame;
+};
+constexpr long long kExSpinLimit = 1ll << 24;  // x (64 ns sleep + one load): several seconds
+
+__device__ __forceinline__ bool ex_wait_all(const volatile unsigned* flags, int n, unsigned frame) {
+    for (int r = 0; r < n; r++) {
+        long long spins = 0;
+        while ((int)(flags[r] - frame) < 0) {
+            if (++spins > kExSpinLimit) return false;
+            __nanosleep(64);
+        }
+    }
+    return true;
+}
+
+__global__ void __launch_bounds__(256) k_exchange_peers(ExArgs a, unsigned* __restrict__ cta_counter) {
+    __shared__ int s_ok;
+    unsigned* my_flags = reinterpret_cast<unsigned*>(a.base[a.rank] + a.off_flags);  // [0..15] arrive, [16..31] done, [32] error
+    if (threadIdx.x == 0) {
+        // every CTA announces the arrival (idempotent): no CTA's wait depends on another CTA having been scheduled
+        __threadfence_system();  // this rank's render is complete (stream order) and visible
+        for (int r = 0; r < a.n_ranks; r++)
+            *reinterpret_cast<volatile unsigned*>(a.base[r] + a.off_flags + 4 * a.rank) = a.frame;
+        const bool ok = ex_wait_all(my_flags, a.n_ranks, a.frame);
+        if (!ok) atomicExch(my_flags + 32, 1u);
+        s_ok = ok ? 1 : 0;
+        __threadfence_system();
+    }
+    __syncthreads();
+    if (s_ok) {
+        const long long v0 = a.rank * a.tile_values;
+        const long long i = v0 + 4 * ((long long)blockIdx.x * blockDim.x + threadIdx.x);
+        if (i < v0 + a.tile_values && i < a.n_values) {
+            long long s[4] = {0, 0, 0, 0};
+            for (int r = 0; r < a.n_ranks; r++) {
+                const longlong2* src = reinterpret_cast<const longlong2*>(a.base[r] + a.off_fixed) + (i >> 1);
+                const longlong2 x = __ldcv(src), y = __ldcv(src + 1);  // never from a stale cache line
+                s[0] += x.x;
+                s[1] += x.y;
+                s[2] += y.x;
+                s[3] += y.y;
+            }
+            const float k = (float)(1.0 / (double)a.ns);
+            unsigned packed = 0;
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float sum = (float)((double)s[j] * 4.656612873077392578125e-10);
+                const float c = xsqrt(xmul(sum, k));
+                int v = (int)(255.99 * (double)c);
+                v = v > 255 ? 255 : v;
+                v = v < 0 ? 0 : v;
+                packed |= (unsigned)v << (8 * j);
+            }
+            for (int r = 0; r < a.n_ranks; r++) *reinterpret_cast<unsigned*>(a.base[r] + a.off_rgb + i) = packed;
+        }
+    }
+    // DONE: the last CTA of this rank, after every CTA's stores have been fenced
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned n = atomicAdd(cta_counter, 1u);
+        if (n == gridDim.x - 1) {
+            *cta_counter = 0;
+            __threadfence_system();
+            for (int r = 0; r < a.n_ranks; r++)
+                *reinterpret_cast<volatile unsigned*>(a.base[r] + a.off_flags + 64 + 4 * a.rank) = a.frame;
+        }
+    }
+}
+
+__global__ void k_exchange_wait(unsigned* __restrict__ my_flags, int n_ranks, unsigned frame) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) {
+        if (!ex_wait_all(my_flags + 16, n_ranks, frame)) atomicExch(my_flags + 32, 1u);
+        __threadfence_system();
+    }
+}
+
 __global__ void k_merl_lookup(const double* __restrict__ table, const double* __restrict__ angles, long long n,
                               double* __restrict__ rgb) {
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;

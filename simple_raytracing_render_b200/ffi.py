@@ -34,6 +34,7 @@ TEX_CONSTANT, TEX_CHECKER, TEX_NOISE, TEX_IMAGE = range(4)
 
 COMPAT_PIXEL_MOD_NY = 1
 RENDER_WAVEFRONT = 2
+EXCHANGE_HANDLE_BYTES = 64
 RENDER_CORRECTED = 4  # corrected-transport mode (outside parity; include/srt_ffi.h)
 
 MERL_DOUBLES = 3 * 90 * 90 * 180
@@ -349,6 +350,13 @@ _SIGNATURES = {
     "srt_render": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
     "srt_render_fixed": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
     "srt_resolve_fixed": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p, C.c_void_p, C.c_int]),
+    "srt_exchange_create": (C.c_int, [C.c_void_p, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_void_p)]),
+    "srt_exchange_handle": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "srt_exchange_connect": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "srt_exchange_fixed": (C.c_void_p, [C.c_void_p]),
+    "srt_exchange_image": (C.c_void_p, [C.c_void_p]),
+    "srt_exchange_run": (C.c_int, [C.c_void_p, C.c_int32, C.c_void_p]),
+    "srt_exchange_destroy": (C.c_int, [C.c_void_p]),
     "srt_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "srt_render_image": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p, C.c_void_p]),
     "srt_render_counted": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p, C.POINTER(SrtCounters)]),

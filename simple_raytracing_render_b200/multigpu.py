@@ -120,3 +120,54 @@ def exchange_tiles(ex: TileExchange, n_samples: int, resolve_tile, group=None):
     ex.fixed.zero_()
     dist.all_gather_into_tensor(ex.rgb, ex.rgb_tile, group=group)
     return ex.image()
+
+
+class PeerExchange:
+    """The exchange step as ONE kernel over NVLink peer memory (include/srt_ffi.h: srt_exchange_*): every
+    rank's accumulation buffers and image live in a block all ranks of the box have mapped (CUDA IPC); rank g waits
+    inside the kernel until every rank has rendered, sums pixel tile g with peer loads, resolves it and stores the 8-bit
+    tile into every rank's image.  No NCCL call per frame: torch.distributed is used once, to pass the IPC handles round.
+
+        ex = PeerExchange(ctx, n_pixels)          # collective: every rank of the group
+        scene.render_fixed(params, ex.fixed())    # this rank's shard into this frame's buffer
+        ex.run(ns, host_rgb)                      # collective; host_rgb (optional): the finished image, synchronises
+    """
+
+    def __init__(self, ctx, n_pixels: int, group=None):
+        import ctypes as C
+        import torch
+        import torch.distributed as dist
+        from . import ffi
+        self.ctx, self.lib = ctx, ctx.lib
+        self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
+        self.n_pixels = int(n_pixels)
+        h = C.c_void_p()
+        ffi.check(self.lib, self.lib.srt_exchange_create(ctx.h, self.n_pixels, self.world, self.rank, C.byref(h)))
+        self.h = h
+        mine = (C.c_uint8 * ffi.EXCHANGE_HANDLE_BYTES)()
+        ffi.check(self.lib, self.lib.srt_exchange_handle(self.h, mine))
+        dev = torch.device("cuda", torch.cuda.current_device())
+        t = torch.tensor(list(mine), dtype=torch.uint8, device=dev)
+        allh = torch.empty(self.world * ffi.EXCHANGE_HANDLE_BYTES, dtype=torch.uint8, device=dev)
+        dist.all_gather_into_tensor(allh, t, group=group)
+        blob = bytes(allh.cpu().numpy().tobytes())
+        ffi.check(self.lib, self.lib.srt_exchange_connect(self.h, blob))
+        dist.barrier(group=group)  # nobody starts a frame before every rank has mapped every block
+
+    def fixed(self) -> int:
+        """Device address of the int64 buffer the NEXT run() will exchange (zero on entry): pass it to render_fixed."""
+        return int(self.lib.srt_exchange_fixed(self.h))
+
+    def image(self) -> int:
+        """Device address of the finished 8-bit image (valid once run()'s work has executed on the stream)."""
+        return int(self.lib.srt_exchange_image(self.h))
+
+    def run(self, n_samples: int, rgb8_host=None):
+        from . import ffi
+        from .render import _ptr
+        ffi.check(self.lib, self.lib.srt_exchange_run(self.h, int(n_samples), _ptr(rgb8_host)))
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.srt_exchange_destroy(self.h)
+            self.h = None
