@@ -370,3 +370,54 @@ def test_merl_lookup_matches_golden(gpu_ctx):
           f"{int(same[degenerate].sum())} of {int(degenerate.sum())} degenerate ones")
     assert same[~degenerate].mean() >= 0.999
     assert np.allclose(got, g["rgb"], rtol=0.2)  # a neighbouring bin / another phi bin of the smooth table at worst
+
+
+def test_peer_exchange_kernel_single_rank(gpu_ctx):
+    """srt_exchange_* (the multi-GPU exchange step as one kernel over peer memory) with ONE rank: the
+    kernel's own arithmetic — exact int64 sum of the tile, resolve, image store, alternating accumulation buffers that
+    come back zero — against srt_resolve_fixed, over several frames and an image size that is not a multiple of 4.
+    The N > 1 form (CUDA IPC, peer loads / stores, the in-kernel barrier) is exercised by tools/peer_exchange_check.py
+    under torchrun and by the multi-GPU test below."""
+    import ctypes as C
+    import torch
+    lib = gpu_ctx.lib
+    sc = render.Scene.from_objects(gpu_ctx, *get_scene("cornell"))
+    nx, ny, ns = 37, 23, 8
+    n = nx * ny
+    h = C.c_void_p()
+    ffi.check(lib, lib.srt_exchange_create(gpu_ctx.h, n, 1, 0, C.byref(h)))
+    handle = (C.c_uint8 * ffi.EXCHANGE_HANDLE_BYTES)()
+    ffi.check(lib, lib.srt_exchange_handle(h, handle))
+    ffi.check(lib, lib.srt_exchange_connect(h, bytes(handle)))
+    fixed = torch.zeros(n * 3, dtype=torch.int64, device="cuda")
+    want = torch.zeros(n * 3, dtype=torch.uint8, device="cuda")
+    seen = set()
+    for frame in range(4):
+        p = render.render_params(nx, ny, ns, seed=100 + frame)
+        buf = int(lib.srt_exchange_fixed(h))
+        seen.add(buf)
+        sc.render_fixed(p, buf)
+        got = np.zeros(n * 3, np.uint8)
+        ffi.check(lib, lib.srt_exchange_run(h, ns, got.ctypes.data))
+        sc.render_fixed(p, fixed)
+        gpu_ctx.resolve_fixed(fixed, n, ns, want, None, clear=True)
+        gpu_ctx.synchronize()
+        assert np.array_equal(got, want.cpu().numpy()), f"frame {frame}"
+    assert len(seen) == 2  # the two accumulation buffers alternate
+    lib.srt_exchange_destroy(h)
+    sc.close()
+
+
+def test_peer_exchange_on_two_gpus():
+    """The N > 1 form, when the box has at least two GPUs: tools/peer_exchange_check.py under torchrun (peer-memory
+    exchange == NCCL tiled exchange == unsharded render, bit for bit, on every rank)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+                        "127.0.0.1", "--master-port", "29531", os.path.join(root, "tools", "peer_exchange_check.py")],
+                       capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
