@@ -141,18 +141,33 @@ class PeerExchange:
         self.ctx, self.lib = ctx, ctx.lib
         self.rank, self.world = dist.get_rank(group), dist.get_world_size(group)
         self.n_pixels = int(n_pixels)
-        h = C.c_void_p()
-        ffi.check(self.lib, self.lib.srt_exchange_create(ctx.h, self.n_pixels, self.world, self.rank, C.byref(h)))
-        self.h = h
-        mine = (C.c_uint8 * ffi.EXCHANGE_HANDLE_BYTES)()
-        ffi.check(self.lib, self.lib.srt_exchange_handle(self.h, mine))
         dev = torch.device("cuda", torch.cuda.current_device())
-        t = torch.tensor(list(mine), dtype=torch.uint8, device=dev)
+        self.h = None
+        err = None
+        # every step that can fail locally (allocation, IPC export, peer mapping) is followed by a COLLECTIVE verdict:
+        # either every rank has an exchange or every rank raises — a rank must not be left waiting for the others
+        try:
+            h = C.c_void_p()
+            ffi.check(self.lib, self.lib.srt_exchange_create(ctx.h, self.n_pixels, self.world, self.rank, C.byref(h)))
+            self.h = h
+            mine = (C.c_uint8 * ffi.EXCHANGE_HANDLE_BYTES)()
+            ffi.check(self.lib, self.lib.srt_exchange_handle(self.h, mine))
+            t = torch.tensor(list(mine), dtype=torch.uint8, device=dev)
+        except Exception as e:  # noqa: BLE001
+            err = e
+            t = torch.zeros(ffi.EXCHANGE_HANDLE_BYTES, dtype=torch.uint8, device=dev)
         allh = torch.empty(self.world * ffi.EXCHANGE_HANDLE_BYTES, dtype=torch.uint8, device=dev)
         dist.all_gather_into_tensor(allh, t, group=group)
-        blob = bytes(allh.cpu().numpy().tobytes())
-        ffi.check(self.lib, self.lib.srt_exchange_connect(self.h, blob))
-        dist.barrier(group=group)  # nobody starts a frame before every rank has mapped every block
+        if err is None:
+            try:
+                ffi.check(self.lib, self.lib.srt_exchange_connect(self.h, bytes(allh.cpu().numpy().tobytes())))
+            except Exception as e:  # noqa: BLE001
+                err = e
+        ok = torch.tensor([0 if err is not None else 1], dtype=torch.int32, device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)  # also: nobody starts a frame before every rank has mapped every block
+        if int(ok.item()) == 0:
+            self.close()
+            raise RuntimeError(f"peer-memory exchange unavailable on this box ({err if err is not None else 'another rank failed'})")
 
     def fixed(self) -> int:
         """Device address of the int64 buffer the NEXT run() will exchange (zero on entry): pass it to render_fixed."""

@@ -1,4 +1,4 @@
-# A/B of library builds: tools/run12.sh "<libs>" "<configs>"   (default = the shipped library)
+# A/B of library builds: tools/ab_libs.sh "<libs>" "<configs>"   (default = the shipped library)
 mkdir -p gpurun_out
 B=simple_raytracing_render_b200/csrc/build
 for cfg in ${2:-spheres teapot soldier tessellated}; do

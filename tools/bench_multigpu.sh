@@ -1,4 +1,4 @@
-# multi-GPU check: tools/run14.sh <N> [extra bench flags]; the JSON line lands in gpurun_out/r02_bench_n<N>.json
+# multi-GPU check: tools/bench_multigpu.sh <N> [extra bench flags]; the JSON line lands in gpurun_out/r02_bench_n<N>.json
 N=$1; shift
 mkdir -p gpurun_out
 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 bench.py --gpus $N --steps 10 --warmup 3 "$@" > gpurun_out/r02_bench_n$N.json 2> gpurun_out/r02_bench_n$N.err
