@@ -381,6 +381,24 @@ int srt_exchange_destroy(SrtExchange* ex);
 int srt_render_image(SrtScene* scene, const SrtRenderParams* params, uint8_t* rgb8_host,
                      float* accum_host);
 
+/* The allocation-free form of srt_render_image for small frames, device output.
+ * No counterpart in the reference: added for callers that cannot call
+ * cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Renders [s_begin, s_end) of an nx x ny frame with the fused kernel (k_render) and writes the resolved 8-bit
+ * image to rgb8_device (nx*ny*3 bytes of DEVICE memory, the caller's).  The kernel's scratch — the fixed-point
+ * radiance sums and the Sobol table — is a file-scope device array of the library (6 MiB + 8 KiB, held by
+ * every GPU that loads libsrt_b200.so until the process exits), so the call makes no cudaMalloc / cudaFree and
+ * calls no allocating library routine.  Limits: nx*ny <= SRT_STATIC_MAX_PIXELS and s_end <=
+ * SRT_STATIC_MAX_SAMPLES, else SRT_E_INVALID with a message naming the limit.  Same bytes as srt_render_image
+ * for the same scene and params (SRT_RENDER_WAVEFRONT is ignored: the wavefront scheduler needs its slot pool).
+ * The FIRST call on a device also looks the array up and uploads the Sobol table (synchronous, once per
+ * device): make it outside graph capture.  Every call on a device shares the one array (it is cleared at the
+ * start of each call), so calls that overlap on the GPU — two streams, two contexts, two threads — race:
+ * serialise them.  Work is issued on the context's stream and not waited for. */
+#define SRT_STATIC_MAX_PIXELS (512 * 512)
+#define SRT_STATIC_MAX_SAMPLES 1024
+int srt_render_image_static(SrtScene* scene, const SrtRenderParams* params, uint8_t* rgb8_device);
+
 /* Counters of the last instrumented render (params.flags has no effect on them; they are
  * gathered by srt_render_counted, an untimed replay). */
 int srt_render_counted(SrtScene* scene, const SrtRenderParams* params, float* accum_rgb_device,

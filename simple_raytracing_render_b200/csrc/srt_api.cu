@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -1668,6 +1669,137 @@ int launch_render(SrtScene* s, const SrtRenderParams* p, float* accum, bool coun
     return finish();
 }
 
+// ---- srt_render_image_static: the fused kernel on scratch that is part of the library image ----------------------
+// k_render's scratch — the [n_pixels][3] fixed-point radiance sums it accumulates into and the Sobol numerators
+// it reads — lives in two file-scope device arrays instead of cudaMalloc'ed buffers of the context, so that the
+// call allocates nothing.  Every GPU that loads the library holds them (6 MiB + 8 KiB) until the process exits.
+// In host code the names below are host-side stand-ins, NOT device addresses: the addresses the kernels get
+// come from cudaGetSymbolAddress, looked up once per device with that device current (static_scratch).
+static __device__ __align__(256) long long g_static_fixed[3 * (size_t)SRT_STATIC_MAX_PIXELS];
+static __device__ __align__(256) uint32_t g_static_sobol[2 * (size_t)SRT_STATIC_MAX_SAMPLES];
+
+struct StaticScratch {
+    long long* fixed = nullptr;  // device address of g_static_fixed on this device
+    uint32_t* sobol = nullptr;   // device address of g_static_sobol on this device, filled
+    bool ready = false;
+};
+constexpr int kStaticMaxDevices = 64;
+StaticScratch g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mutex;
+
+// Set-up of the static scratch of the CURRENT device (the caller has made c->device current): symbol look-up and
+// the one upload of the Sobol table (the same numerators ensure_sobol uploads: the sequence is a prefix
+// property of the generator, srt_sobol_points_u32).  Synchronous; runs on the first call per device only.
+int static_scratch(SrtContext* c, StaticScratch** out) {
+    if (c->device < 0 || c->device >= kStaticMaxDevices) return fail(SRT_E_INVALID, "device ordinal %d beyond %d", c->device, kStaticMaxDevices);
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    StaticScratch& S = g_static_dev[c->device];
+    if (!S.ready) {
+        long long* fixed = nullptr;
+        uint32_t* sobol = nullptr;
+        CUDA_TRY(cudaGetSymbolAddress((void**)&fixed, g_static_fixed));
+        CUDA_TRY(cudaGetSymbolAddress((void**)&sobol, g_static_sobol));
+        if (!fixed || !sobol) return fail(SRT_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        static uint32_t pts[2 * (size_t)SRT_STATIC_MAX_SAMPLES];  // under g_static_mutex
+        int rc = srt_sobol_points_u32(SRT_STATIC_MAX_SAMPLES, pts);
+        if (rc) return rc;
+        CUDA_TRY(cudaMemcpy(sobol, pts, sizeof pts, cudaMemcpyHostToDevice));
+        S.fixed = fixed;
+        S.sobol = sobol;
+        S.ready = true;
+    }
+    *out = &S;
+    return 0;
+}
+
+// One frame on the fused kernel with the static scratch, then k_resolve_fixed into the caller's device buffer.
+// Same variant pick, same RenderArgs and same grid as launch_render's fused branch: the two produce the same
+// fixed-point sums (integer adds, any order), hence the same bytes.
+int launch_render_static(SrtScene* s, const SrtRenderParams* p, uint8_t* rgb8_device) {
+    SrtContext* c = s->ctx;
+    const long long n_pixels = (long long)p->nx * p->ny;
+    const int count = p->s_end - p->s_begin;
+    if (n_pixels > (long long)SRT_STATIC_MAX_PIXELS)
+        return fail(SRT_E_INVALID, "srt_render_image_static: %d x %d = %lld pixels exceed the static scratch of %d pixels "
+                                   "(SRT_STATIC_MAX_PIXELS); use srt_render_image",
+                    p->nx, p->ny, n_pixels, (int)SRT_STATIC_MAX_PIXELS);
+    if (p->s_end > (int)SRT_STATIC_MAX_SAMPLES)
+        return fail(SRT_E_INVALID, "srt_render_image_static: sample index %d exceeds the static Sobol table of %d points "
+                                   "(SRT_STATIC_MAX_SAMPLES); use srt_render_image",
+                    p->s_end, (int)SRT_STATIC_MAX_SAMPLES);
+    if (count <= 0) return fail(SRT_E_INVALID, "srt_render_image_static: empty sample range");
+    if (!is_device_pointer(rgb8_device)) return fail(SRT_E_INVALID, "srt_render_image_static: rgb8_device is not device memory");
+    const bool corrected = (p->flags & SRT_RENDER_CORRECTED) != 0;
+    if (corrected && (s->dev.features & (F_LIGHT_ENV | F_LIGHT_NONE)))
+        return fail(SRT_E_UNSUPPORTED, "corrected-transport mode: the light list holds a shape without a sampling density "
+                                       "(env_sphere, or a class without pdf_value / random)");
+    StaticScratch* S = nullptr;
+    int rc = static_scratch(c, &S);
+    if (rc) return rc;
+
+    const int v = pick_variant(s, false, corrected);
+    if (v < 0) return fail(SRT_E_UNSUPPORTED, "no render-kernel variant covers feature mask 0x%x", s->dev.features);
+    const size_t smem = (kVariantMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;
+    RenderLaunch L;
+    L.scene = &s->dev;
+    L.sobol = S->sobol;
+    L.counters = c->d_counters;
+    L.smem_bytes = smem;
+    L.stream = c->stream;
+    L.grid = 0;
+    int blocks_per_sm = c->variant_blocks[v];
+    if (blocks_per_sm <= 0 || smem > c->variant_smem[v]) {  // occupancy query (no allocation), cached as launch_render does
+        RenderVariantInfo info = {};
+        L.args = nullptr;
+        L.out = nullptr;
+        cudaError_t e = kVariants[v](L, &info);
+        if (e != cudaSuccess) return fail(SRT_E_CUDA, "render variant %d: %s", v, cudaGetErrorString(e));
+        c->variant_blocks[v] = info.blocks_per_sm;
+        c->variant_regs[v] = info.registers;
+        c->variant_smem[v] = smem;
+        blocks_per_sm = info.blocks_per_sm;
+    }
+    blocks_per_sm = std::max(1, blocks_per_sm);
+
+    const int chunk = std::max(1, std::min(count, env_int("SRT_CHUNK", 1)));
+    const int n_chunks = (count + chunk - 1) / chunk;
+    srt::RenderArgs A;
+    A.nx = p->nx;
+    A.ny = p->ny;
+    A.s_begin = p->s_begin;
+    A.s_end = p->s_end;
+    A.max_depth = p->max_depth;
+    A.seed = p->seed;
+    A.mod_ny = (p->flags & SRT_COMPAT_PIXEL_MOD_NY) ? 1 : 0;
+    A.chunk = chunk;
+    A.n_chunks = n_chunks;
+    A.n_items = (unsigned long long)n_pixels * (unsigned long long)n_chunks;
+    A.fx_clamp = 4.0e9f / (float)std::max(count, p->ns);
+    A.regen_threshold = std::max(1, std::min(32, env_int("SRT_REGEN", 8)));
+    A.grab = std::max(32, env_int("SRT_GRAB", 128));
+    A.cta_sync = std::max(0, std::min(2, env_int("SRT_CTA_SYNC", 0)));
+    A.dbg_pixel = -1;
+    A.dbg_sample = -1;
+
+    // the array keeps the previous call's sums (every call shares it): the part this frame adds into starts at zero
+    const size_t nv = 3 * (size_t)n_pixels;
+    CUDA_TRY(cudaMemsetAsync(S->fixed, 0, sizeof(long long) * nv, c->stream));
+    CUDA_TRY(cudaMemsetAsync(c->d_counters + 7, 0, sizeof(unsigned long long), c->stream));
+    const long long warps_needed = ((long long)A.n_items + 31) / 32;
+    const long long blocks_needed = (warps_needed + (srt::kRenderThreads / 32) - 1) / (srt::kRenderThreads / 32);
+    L.args = &A;
+    L.out = S->fixed;
+    L.grid = (int)std::max<long long>(1, std::min<long long>(blocks_needed, (long long)c->sm_count * blocks_per_sm));
+    cudaError_t e = kVariants[v](L, nullptr);
+    c->launches++;
+    if (e != cudaSuccess) return fail(SRT_E_CUDA, "k_render (variant %d, static scratch): %s", v, cudaGetErrorString(e));
+    srt::k_resolve_fixed<<<(unsigned)((nv + 255) / 256), 256, 0, c->stream>>>(S->fixed, (long long)nv, (float)count,
+                                                                              rgb8_device, nullptr, 0);
+    c->launches++;
+    CUDA_TRY(cudaGetLastError());
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -1985,6 +2117,16 @@ int srt_render_image(SrtScene* s, const SrtRenderParams* p, uint8_t* rgb8_host, 
         CUDA_TRY(cudaStreamSynchronize(c->stream));
     }
     return 0;
+}
+
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+int srt_render_image_static(SrtScene* s, const SrtRenderParams* p, uint8_t* rgb8_device) {
+    if (!s || !rgb8_device) return fail(SRT_E_INVALID, "null argument");
+    int rc = check_params(p);
+    if (rc) return rc;
+    CUDA_TRY(cudaSetDevice(s->ctx->device));
+    return launch_render_static(s, p, rgb8_device);
 }
 
 }  // extern "C"

@@ -35,6 +35,8 @@ TEX_CONSTANT, TEX_CHECKER, TEX_NOISE, TEX_IMAGE = range(4)
 COMPAT_PIXEL_MOD_NY = 1
 RENDER_WAVEFRONT = 2
 EXCHANGE_HANDLE_BYTES = 64
+STATIC_MAX_PIXELS = 512 * 512  # srt_ffi.h SRT_STATIC_MAX_PIXELS (srt_render_image_static)
+STATIC_MAX_SAMPLES = 1024      # srt_ffi.h SRT_STATIC_MAX_SAMPLES
 RENDER_CORRECTED = 4  # corrected-transport mode (outside parity; include/srt_ffi.h)
 
 MERL_DOUBLES = 3 * 90 * 90 * 180
@@ -359,6 +361,7 @@ _SIGNATURES = {
     "srt_exchange_destroy": (C.c_int, [C.c_void_p]),
     "srt_resolve": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int64, C.c_int32, C.c_void_p]),
     "srt_render_image": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p, C.c_void_p]),
+    "srt_render_image_static": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p]),
     "srt_render_counted": (C.c_int, [C.c_void_p, C.POINTER(SrtRenderParams), C.c_void_p, C.POINTER(SrtCounters)]),
     "srt_counters_get": (C.c_int, [C.c_void_p, C.POINTER(SrtCounters)]),
     "srt_sobol_points_u32": (C.c_int, [C.c_uint32, C.c_void_p]),

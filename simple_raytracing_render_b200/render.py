@@ -196,6 +196,12 @@ class Scene:
         ffi.check(self.lib, self.lib.srt_render_image(self.h, C.byref(params), _ptr(rgb8), _ptr(accum)))
         return (rgb8, accum) if want_accum else rgb8
 
+    def render_image_static(self, params: ffi.SrtRenderParams, rgb8_dev):
+        """srt_render_image_static: the frame into a DEVICE uint8 buffer of nx*ny*3 bytes (async), on the library's
+        static scratch — no allocation inside the call; at most ffi.STATIC_MAX_PIXELS pixels and
+        ffi.STATIC_MAX_SAMPLES samples.  No counterpart in the reference."""
+        ffi.check(self.lib, self.lib.srt_render_image_static(self.h, C.byref(params), _ptr(rgb8_dev)))
+
     def close(self):
         if getattr(self, "h", None):
             self.lib.srt_scene_destroy(self.h)
