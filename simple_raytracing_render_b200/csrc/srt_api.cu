@@ -1463,8 +1463,12 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v) 
     const WfVariantInfo& info = c->wf_info[v];
     const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 6144)) & ~31;
     const int threads = std::max(32, info.threads);
-    const int per_thread = std::max(1, std::min(slots_per_sm / threads, srt::kSortCap / threads));
-    const int grid = c->sm_count;
+    // several smaller CTAs per SM share its slots, one fills the other's barrier waits (srt_variants.h:
+    // SRT_WF_VARIANT_CTAS_PER_SM; SRT_WF_CTAS_PER_SM overrides for experiments — a CTA that does not fit beside the
+    // others simply runs after them)
+    const int ctas = std::max(1, std::min(8, env_int("SRT_WF_CTAS_PER_SM", std::max(1, info.ctas_per_sm))));
+    const int per_thread = std::max(1, std::min(slots_per_sm / ctas / threads, srt::kSortCap / threads));
+    const int grid = c->sm_count * ctas;
     const int n_slots = grid * per_thread * threads;
     const size_t need = (size_t)n_slots * (size_t)info.slot_bytes;
     if (c->wf_cap < need) {

@@ -398,8 +398,14 @@ SRT_DEV ShadeStatus shade_hit(const View& W, Path& P, const Hit& h, int max_dept
     }
     if ((F & F_DIELECTRIC) && m.type == SRT_MAT_DIELECTRIC) {  // material.h:285-324
         float ref_idx = m.p[0];
-        V3 outward_normal, refracted;
+        V3 outward_normal;
         V3 reflected = reflect(r.d, rec.normal);  // the un-normalised direction, as in the reference
+        // Under total internal reflection the reference leaves `refracted` unset and reflect_prob = 1
+        // (material.h:292, :306-312; vec3() {} sets nothing, vec3.h:14), and its float rand01() CAN return 1.0f
+        // (material.h:37): `1.0f < 1.0f` (:314) then takes the unset vector (:320) — undefined in the reference,
+        // 2^-25 of the TIR events.  Here that case reflects: an unset
+        // register made three of the 2.1 G paths of C5-like differ from run to run (profiles/r02_notes.md, capture AB).
+        V3 refracted = reflected;
         float ni_over_nt, cosine, reflect_prob;
         float dn = fm::dot(r.d, rec.normal);
         float rl = fm::rlength(r.d);

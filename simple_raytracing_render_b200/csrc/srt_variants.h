@@ -78,6 +78,7 @@ struct WfLaunch {
 struct WfVariantInfo {
     uint32_t features;
     int blocks_per_sm, registers, threads;
+    int ctas_per_sm;  // CTAs the launch puts on one SM (SRT_WF_VARIANT_CTAS_PER_SM)
     int slot_bytes;  // bytes of one slot record (srt_wavefront.cuh: kSlotQuads x 16)
 };
 
@@ -108,7 +109,13 @@ typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
 // capture K): the sphere-BVH variant needs 107 registers and is best at 640 threads (96 registers, 20
 // warps); the mesh and full variants spill there and are best at 512 (128 registers); the two lean mesh
 // variants (6, 7) fit 96 registers with 32-96 bytes of spills and gain 1-3 % from the four extra warps.
-#define SRT_WF_VARIANT_PERSIST_THREADS(n) ((n) <= 1 || (n) >= 6 ? 640 : 512)
+#define SRT_WF_VARIANT_PERSIST_THREADS(n) ((n) == 7 ? 320 : ((n) <= 1 || (n) == 6 ? 640 : 512))
+// CTAs per SM.  One everywhere but on the triangle-bvh + constant_medium variant (7), whose frames spend 36-39 % of
+// their stall samples at the barrier that closes the trace phase (a group lasts as long as its longest traversal):
+// two CTAs of 320 threads share the SM's slots, and one traces while the other waits.  Measured (profiles/
+// r02_notes.md, capture AA): C5 at 10 M triangles -9.5 %, C5-like -0.6 %; the same split is +2.5 % on the sphere
+// variant, -4 % on C3 but +13 % on C4 (both variant 6: two CTAs in different phases miss the instruction cache more).
+#define SRT_WF_VARIANT_CTAS_PER_SM(n) ((n) == 7 ? 2 : 1)
 
 cudaError_t srt_wavefront_variant_0(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_1(const WfLaunch&, WfVariantInfo*);

@@ -9,6 +9,9 @@
 #ifndef SRT_WFP_THREADS
 #define SRT_WFP_THREADS SRT_WF_VARIANT_PERSIST_THREADS(SRT_WF_VARIANT)
 #endif
+#ifndef SRT_WFP_MINBLOCKS
+#define SRT_WFP_MINBLOCKS SRT_WF_VARIANT_CTAS_PER_SM(SRT_WF_VARIANT)
+#endif
 #include "srt_wavefront.cuh"
 
 #define SRT_CAT2(a, b) a##b
@@ -29,6 +32,7 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         e = cudaFuncSetAttribute((const void*)sorted, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)L.smem_bytes);
         if (e != cudaSuccess) return e;
         info->threads = SRT_WFP_THREADS;
+        info->ctas_per_sm = SRT_WFP_MINBLOCKS;
         info->slot_bytes = srt::SlotQuads<kMask>::value * 16;
         e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&info->blocks_per_sm, sorted, SRT_WFP_THREADS, L.smem_bytes);
         if (e != cudaSuccess) return e;

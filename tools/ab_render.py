@@ -26,3 +26,5 @@ with torch.cuda.stream(stream):
         e1.record(stream)
         torch.cuda.synchronize()
         print(name, mode, os.environ.get("SRT_B200_LIB", "default"), "ms", e0.elapsed_time(e1), flush=True)
+if mode == "fixed":  # integer sums: builds that render the same paths print the same number
+    print(name, "checksum", int(buf.sum().item()), int((buf * torch.arange(buf.numel(), device="cuda") % 1000003).sum().item()), flush=True)
