@@ -1462,11 +1462,15 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v) 
     }
     const WfVariantInfo& info = c->wf_info[v];
     const int slots_per_sm = std::max(256, env_int("SRT_WF_SLOTS_PER_SM", 6144)) & ~31;
-    const int threads = std::max(32, info.threads);
-    // several smaller CTAs per SM share its slots, one fills the other's barrier waits (srt_variants.h:
-    // SRT_WF_VARIANT_CTAS_PER_SM; SRT_WF_CTAS_PER_SM overrides for experiments — a CTA that does not fit beside the
-    // others simply runs after them)
-    const int ctas = std::max(1, std::min(8, env_int("SRT_WF_CTAS_PER_SM", std::max(1, info.ctas_per_sm))));
+    // CTAs per SM: several smaller CTAs share an SM's slots and one fills the other's barrier waits.  Fixed per variant
+    // (srt_variants.h: SRT_WF_VARIANT_CTAS_PER_SM), except that variant 6 splits its CTA in two for scenes with large BVHs
+    // (SRT_WF_SPLIT_CTA_MIN_NODES).  SRT_WF_CTAS_PER_SM overrides for experiments.  A launch may use fewer threads than
+    // the variant's launch bound, never more; a CTA that does not fit beside the others simply runs after them.
+    int ctas = std::max(1, info.ctas_per_sm);
+    if (v == 6 && s->info.bvh_nodes >= SRT_WF_SPLIT_CTA_MIN_NODES) ctas = 2;
+    ctas = std::max(1, std::min(8, env_int("SRT_WF_CTAS_PER_SM", ctas)));
+    const int threads_per_sm = std::max(32, info.threads) * std::max(1, info.ctas_per_sm);
+    const int threads = std::max(32, std::min(std::max(32, info.threads), (threads_per_sm / ctas) & ~31));
     const int per_thread = std::max(1, std::min(slots_per_sm / ctas / threads, srt::kSortCap / threads));
     const int grid = c->sm_count * ctas;
     const int n_slots = grid * per_thread * threads;
@@ -1506,6 +1510,7 @@ int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v) 
     st.n_slots = n_slots;
     L.state = &st;
     L.per_thread = per_thread;
+    L.threads = threads;
     L.smem_bytes = smem_hot16 + (size_t)srt::Q_N * per_thread * threads * sizeof(unsigned short);
     L.grid = grid;
     c->launches++;

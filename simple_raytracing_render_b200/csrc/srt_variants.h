@@ -71,6 +71,7 @@ struct WfLaunch {
     unsigned long long* counters;
     int per_thread;  // slots per thread of the CTA
     int grid;
+    int threads;  // threads per CTA (<= the variant's SRT_WF_VARIANT_PERSIST_THREADS); 0: that maximum
     size_t smem_bytes;
     cudaStream_t stream;
 };
@@ -116,6 +117,11 @@ typedef cudaError_t (*WfVariantFn)(const WfLaunch& L, WfVariantInfo* info);
 // r02_notes.md, capture AA): C5 at 10 M triangles -9.5 %, C5-like -0.6 %; the same split is +2.5 % on the sphere
 // variant, -4 % on C3 but +13 % on C4 (both variant 6: two CTAs in different phases miss the instruction cache more).
 #define SRT_WF_VARIANT_CTAS_PER_SM(n) ((n) == 7 ? 2 : 1)
+// Variant 6 (list classes + triangle bvh + Beckmann + image textures) decides per scene, at launch: its 640-thread CTA is
+// launched as two CTAs of 320 threads (same registers, same slots per SM) when the scene's wide BVHs hold at least this
+// many nodes — deep traversals of very different lengths, a long wait at the trace barrier (C3: -4.4 %) — and as one
+// CTA for small meshes among many materials, where two CTAs in different phases miss the instruction cache (C4: +13 %).
+#define SRT_WF_SPLIT_CTA_MIN_NODES 65536
 
 cudaError_t srt_wavefront_variant_0(const WfLaunch&, WfVariantInfo*);
 cudaError_t srt_wavefront_variant_1(const WfLaunch&, WfVariantInfo*);

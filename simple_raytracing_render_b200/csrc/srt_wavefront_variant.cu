@@ -42,6 +42,6 @@ cudaError_t SRT_CAT(srt_wavefront_variant_, SRT_WF_VARIANT)(const WfLaunch& L, W
         return cudaSuccess;
     }
     const srt::WfState& st = *static_cast<const srt::WfState*>(L.state);
-    sorted<<<L.grid, SRT_WFP_THREADS, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters, L.per_thread);
+    sorted<<<L.grid, L.threads > 0 ? L.threads : SRT_WFP_THREADS, L.smem_bytes, L.stream>>>(*L.scene, *L.args, st, L.sobol, L.out, L.counters, L.per_thread);
     return cudaGetLastError();
 }
