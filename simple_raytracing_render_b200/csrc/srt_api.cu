@@ -1709,9 +1709,29 @@ int static_scratch(SrtContext* c, StaticScratch** out) {
         CUDA_TRY(cudaGetSymbolAddress((void**)&fixed, g_static_fixed));
         CUDA_TRY(cudaGetSymbolAddress((void**)&sobol, g_static_sobol));
         if (!fixed || !sobol) return fail(SRT_E_CUDA, "cudaGetSymbolAddress returned a null address");
+        // the numerators of srt_sobol_points_u32 (Raytracing_n.cpp:721-812, D = 2) with fixed-size direction tables:
+        // no heap allocation on this path either.  A prefix of the table ensure_sobol uploads.
         static uint32_t pts[2 * (size_t)SRT_STATIC_MAX_SAMPLES];  // under g_static_mutex
-        int rc = srt_sobol_points_u32(SRT_STATIC_MAX_SAMPLES, pts);
-        if (rc) return rc;
+        uint32_t V1[34], V2[34];
+        uint32_t L = 0;
+        while ((1ull << L) < (unsigned long long)SRT_STATIC_MAX_SAMPLES) L++;
+        static_assert(SRT_STATIC_MAX_SAMPLES > 2 && SRT_STATIC_MAX_SAMPLES <= (1u << 31), "direction tables hold 32 bits");
+        for (uint32_t i = 1; i <= L; i++) V1[i] = 1u << (32 - i);
+        V2[1] = 1u << 31;
+        for (uint32_t i = 2; i <= L; i++) V2[i] = V2[i - 1] ^ (V2[i - 1] >> 1);
+        uint32_t x0 = 0, x1 = 0;
+        pts[0] = pts[1] = 0;
+        for (uint32_t i = 1; i < (uint32_t)SRT_STATIC_MAX_SAMPLES; i++) {
+            uint32_t cbit = 1, v = i - 1;
+            while (v & 1) {
+                v >>= 1;
+                cbit++;
+            }
+            x0 ^= V1[cbit];
+            x1 ^= V2[cbit];
+            pts[2 * i] = x0;
+            pts[2 * i + 1] = x1;
+        }
         CUDA_TRY(cudaMemcpy(sobol, pts, sizeof pts, cudaMemcpyHostToDevice));
         S.fixed = fixed;
         S.sobol = sobol;

@@ -54,3 +54,33 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h", ".hpp")):
                 text = open(os.path.join(dirpath, f), errors="replace").read()
                 assert "from oracle" not in text and "import oracle" not in text and "libsrt_ref" not in text, f
+
+
+def test_header_constants_match_the_python_mirror():
+    src = open(os.path.join(ROOT, "include", "srt_ffi.h")).read()
+
+    def macro(name):
+        m = re.search(rf"#define\s+{name}\s+(.+)", src)
+        assert m, name
+        return eval(m.group(1).split("/*")[0].strip().rstrip("u"), {"__builtins__": {}})
+
+    assert macro("SRT_STATIC_MAX_PIXELS") == ffi.STATIC_MAX_PIXELS
+    assert macro("SRT_STATIC_MAX_SAMPLES") == ffi.STATIC_MAX_SAMPLES
+    assert macro("SRT_EXCHANGE_HANDLE_BYTES") == ffi.EXCHANGE_HANDLE_BYTES
+    assert macro("SRT_RENDER_CORRECTED") == ffi.RENDER_CORRECTED
+
+
+def test_static_entry_point_allocates_nothing():
+    """srt_render_image_static promises no cudaMalloc / cudaFree inside the call: the functions it is made of
+    (launch_render_static, static_scratch in srt_api.cu) name neither, and its scratch is a static device array
+    whose address comes from cudaGetSymbolAddress."""
+    src = open(os.path.join(ROOT, "simple_raytracing_render_b200", "csrc", "srt_api.cu")).read()
+    a = src.index("static __device__ __align__(256) long long g_static_fixed")
+    b = src.index("}  // namespace", a)
+    body = re.sub(r"//.*", "", src[a:b])
+    assert "cudaGetSymbolAddress((void**)&fixed, g_static_fixed)" in body
+    for banned in ("cudaMalloc", "cudaFree", "cudaHostAlloc", "std::vector", "new "):
+        assert banned not in body, banned
+    entry = src[src.index("int srt_render_image_static("):]
+    entry = entry[:entry.index("\n}\n")]
+    assert "launch_render_static" in entry and "cudaMalloc" not in entry
