@@ -1440,7 +1440,7 @@ int pick_wf_variant(const SrtScene* s, bool counting, bool corrected = false) {
 }
 
 // The wavefront form of one render (srt_wavefront.cuh): ONE launch of the persistent sorted kernel, one CTA
-// per SM, every CTA owning per_thread x threads slots of the pool.
+// per SM (two for some variants and scenes, below), every CTA owning per_thread x threads slots of the pool.
 int run_wavefront(SrtScene* s, const srt::RenderArgs& A, long long* out, int v) {
     SrtContext* c = s->ctx;
     const size_t smem = (kWfMask[v] & F_SMEM_TABLES) ? s->dev.hot_bytes : 0;

@@ -5,7 +5,9 @@
 // sit at unrelated program counters — while the closest-hit code run on its own sustains five times the
 // fused rate.  Here a bounce is split into a TRACE phase (world->hit only) and a SHADE phase (color()'s
 // material / pdf / light-sampling step), both inside ONE persistent kernel, one CTA per SM; barriers keep
-// all warps of the SM in the same phase, so the instruction cache holds one stage's code at a time.
+// all warps of the CTA in the same phase, so the instruction cache holds one stage's code at a time.
+// (Two smaller CTAs per SM where the wait at the trace barrier costs more than the second stage's code in the
+// cache: srt_variants.h SRT_WF_VARIANT_CTAS_PER_SM / SRT_WF_SPLIT_CTA_MIN_NODES, srt_api.cu run_wavefront.)
 //
 // State: one record per path slot in global memory (the pool is sized to stay in L2 and carries a
 // persisting access-policy window, srt_api.cu).  A record is kSlotQuads 16-byte words, array-of-structures:
